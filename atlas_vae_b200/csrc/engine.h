@@ -1,0 +1,70 @@
+// Host-side state behind an oevae_t handle.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdarg>
+#include <string>
+#include <vector>
+#include "../../include/oevae.h"
+
+namespace oevae {
+
+constexpr int kMaxSlots = 48;          // split-K partial-gradient slots (3 passes x 16)
+
+struct Layer { int in, out; long w, b; };   // offsets of kernel [in,out] and bias [out] in the flat vector
+
+// one call = up to three row groups of B jets each (SURVEY 7.1 / ref_kernels.cuh combine_kernel)
+struct Pass {
+    long B = 0;
+    int R = 1;                // row groups that run the encoder
+    int Rd = 1;               // leading groups that also run the decoder
+    const float* x[3] = {nullptr, nullptr, nullptr};
+    const float* eps = nullptr; int n_eps = 0;
+    bool want_rec = true;
+    bool encoder_only = false;
+};
+
+struct Engine {
+    oevae_config cfg{};
+    std::string err;
+    int D = 0, L = 0, n = 0, maxH = 0, n_sm = 0;
+    std::vector<int> hid;
+    std::vector<Layer> layers;
+    long P = 0, Ppad = 0;
+    float *theta = nullptr, *m = nullptr, *v = nullptr;
+    long long step = 0;           // Adam t
+    long long calls = 0;          // forward-call counter (Philox step in PER_STEP mode)
+    unsigned long long row_offset = 0;
+
+    // workspace
+    float* arena = nullptr; long cap_rows = 0;
+    float* parts = nullptr;
+    std::vector<float*> act_e, act_d;
+    float *mu = nullptr, *lv = nullptr, *z = nullptr, *eps_buf = nullptr, *g_mu = nullptr, *g_lv = nullptr;
+    float *y = nullptr, *ysum = nullptr, *gA = nullptr, *gB = nullptr;
+    float *kld = nullptr, *rec = nullptr, *g_rec = nullptr, *g_kld = nullptr;
+    int Sg = 1, chunk_rows = 0, n_slots_used = 0;
+
+    ~Engine();
+    int fail(int code, const char* fmt, ...);
+    int cuda_check(cudaError_t e, const char* what);
+    int init(const oevae_config& c);
+    int reserve(long rows);
+    int mse_type() const { return cfg.oe_type == OEVAE_OE_MSE || cfg.oe_type == OEVAE_OE_MSE_MARGIN; }
+
+    int gemm_fwd(const float* A, int li, float* C, long rows, bool relu, cudaStream_t s);
+    int gemm_dx(const float* G, int li, float* C, long rows, bool accumulate, const float* mask, cudaStream_t s);
+    int gemm_dw(const float* A, const float* G, int li, long rows, long B, int slot0, int n_slots, cudaStream_t s);
+
+    int plan(Pass& p, const float* x_bkg, const float* x_ood, const float* eps, int n_eps, long B);
+    int forward(const Pass& p, cudaStream_t s);
+    int forward_encoder(const Pass& p, cudaStream_t s);
+    int backward(const Pass& p, cudaStream_t s);
+    int losses(const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood, const float* eps, int n_eps,
+               long B, float beta, float lamb, float margin, float* per_jet, double* sums, bool want_grad, cudaStream_t s);
+    int reduce_and_update(float* grad_out, const float* grad_in, bool apply, float lr, cudaStream_t s);
+    int score(const float* x, long N, int n_iter, const float* eps, float* o_mse, float* o_mae, float* o_kld, float* o_jsd,
+              float* o_lat, unsigned char* o_fin, float* o_xhat, cudaStream_t s);
+    int encode(const float* x, long N, const float* eps, float* o_mu, float* o_lv, float* o_z, cudaStream_t s);
+};
+
+}  // namespace oevae

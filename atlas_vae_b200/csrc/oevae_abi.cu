@@ -1,0 +1,595 @@
+// liboevae.so: C ABI (include/oevae.h) over the sm_100a kernels.  Host orchestration only; no torch types.
+#include "../../include/oevae.h"
+#include "common.cuh"
+#include "ref_kernels.cuh"
+#include "prep_hist_kernels.cuh"
+#include "engine.h"
+
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace oevae;
+
+std::atomic<long long> g_launches{0};
+static thread_local std::string g_create_error;
+
+#define LAUNCHED() (g_launches.fetch_add(1, std::memory_order_relaxed))
+
+static inline unsigned cdiv(long a, long b) { return (unsigned)((a + b - 1) / b); }
+
+// ------------------------------------------------------------------------------------------------
+int Engine::fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    err = buf;
+    return code;
+}
+
+int Engine::cuda_check(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return 0;
+    return fail(OEVAE_ECUDA, "%s: %s", what, cudaGetErrorString(e));
+}
+
+#define CK(call) do { int _r = cuda_check((call), #call); if (_r) return _r; } while (0)
+#define CKL() do { LAUNCHED(); int _r = cuda_check(cudaGetLastError(), "kernel launch"); if (_r) return _r; } while (0)
+#define TRY(call) do { int _r = (call); if (_r) return _r; } while (0)
+
+int Engine::init(const oevae_config& c) {
+    cfg = c;
+    if (c.input_dim <= 0 || c.latent_dim <= 0 || c.n_hidden < 0 || c.n_hidden > 8) return fail(OEVAE_EINVAL, "bad layer configuration");
+    if (c.oe_type < 0 || c.oe_type > 4) return fail(OEVAE_EINVAL, "bad oe_type %d", c.oe_type);
+    if (c.noise_mode < 0 || c.noise_mode > 2) return fail(OEVAE_EINVAL, "bad noise_mode %d", c.noise_mode);
+    if (c.precision < 0 || c.precision > 3) return fail(OEVAE_EINVAL, "bad precision %d", c.precision);
+    D = c.input_dim; L = c.latent_dim; n = c.n_hidden;
+    for (int k = 0; k < n; ++k) { if (c.hidden[k] <= 0) return fail(OEVAE_EINVAL, "bad hidden width"); hid.push_back(c.hidden[k]); }
+    // Keras trainable_weights order (models.py:22-28,43-48)
+    long off = 0; int d = D;
+    auto add = [&](int i, int o) { Layer l; l.in = i; l.out = o; l.w = off; off += (long)i * o; l.b = off; off += o; layers.push_back(l); };
+    for (int k = 0; k < n; ++k) { add(d, hid[k]); d = hid[k]; }
+    add(d, L); add(d, L);
+    d = L;
+    for (int k = n - 1; k >= 0; --k) { add(d, hid[k]); d = hid[k]; }
+    add(d, D);
+    P = off;
+    maxH = L;
+    for (int h : hid) maxH = std::max(maxH, h);
+    CK(cudaSetDevice(c.device));
+    int cc_major = 0;
+    CK(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, c.device));
+    if (cc_major != 10) return fail(OEVAE_EUNSUPPORTED, "liboevae is built for sm_100a only (device has compute capability %d.x)", cc_major);
+    CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, c.device));
+    CK(cudaMalloc(&theta, 3 * P * sizeof(float)));
+    m = theta + P; v = m + P;
+    CK(cudaMemset(theta, 0, 3 * P * sizeof(float)));
+    step = 0; calls = 0;
+    if (c.max_batch > 0) TRY(reserve(c.max_batch * 2));
+    return 0;
+}
+
+Engine::~Engine() {
+    if (theta) cudaFree(theta);
+    if (arena) cudaFree(arena);
+}
+
+// workspace for `rows` total rows (all passes of one call)
+int Engine::reserve(long rows) {
+    if (rows <= cap_rows) return 0;
+    if (arena) { CK(cudaDeviceSynchronize()); CK(cudaFree(arena)); arena = nullptr; }
+    long sumH = 0; for (int h : hid) sumH += h;
+    long per_row = 2 * sumH + 6L * L + 2L * D + 2L * maxH + 4;
+    Ppad = (P + 3) / 4 * 4;
+    size_t floats = (size_t)per_row * rows + (size_t)kMaxSlots * Ppad + 64;
+    cudaError_t e = cudaMalloc(&arena, floats * sizeof(float));
+    if (e != cudaSuccess) { arena = nullptr; cap_rows = 0; return fail(OEVAE_ENOMEM, "workspace of %zu MB: %s", floats * 4 >> 20, cudaGetErrorString(e)); }
+    cap_rows = rows;
+    float* p = arena;
+    auto take = [&](size_t nflt) { float* q = p; p += (nflt + 3) / 4 * 4; return q; };
+    parts = take((size_t)kMaxSlots * Ppad);
+    act_e.assign(n + 1, nullptr); act_d.assign(n + 1, nullptr);
+    for (int k = 1; k <= n; ++k) act_e[k] = take((size_t)rows * hid[k - 1]);
+    mu = take((size_t)rows * L); lv = take((size_t)rows * L);
+    z = take((size_t)rows * L); eps_buf = take((size_t)rows * L);
+    g_mu = take((size_t)rows * L); g_lv = take((size_t)rows * L);
+    for (int k = 1; k <= n; ++k) act_d[k] = take((size_t)rows * hid[n - k]);
+    y = take((size_t)rows * D); ysum = take((size_t)rows * D);
+    gA = take((size_t)rows * maxH); gB = take((size_t)rows * maxH);
+    kld = take(rows); rec = take(rows); g_rec = take(rows); g_kld = take(rows);
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- GEMM launchers
+int Engine::gemm_fwd(const float* A, int li, float* C, long rows, bool relu, cudaStream_t s) {
+    const Layer& l = layers[li];
+    GemmArgs g{};
+    g.A = A; g.B = theta + l.w; g.C = C;
+    g.sAr = l.in; g.sAt = 1; g.sBt = l.out; g.sBc = 1;
+    g.R = (int)rows; g.Cn = l.out; g.ldc = l.out;
+    g.bias = theta + l.b; g.relu = relu;
+    g.t_base = 0; g.t_end = l.in;
+    dim3 grid(cdiv(rows, 64), cdiv(l.out, 64), 1);
+    gemm64_kernel<true, false><<<grid, 256, 0, s>>>(g);
+    CKL();
+    return 0;
+}
+
+// C[rows, in] = G[rows, out] . W^T  (+= C) (* mask>0)
+int Engine::gemm_dx(const float* G, int li, float* C, long rows, bool accumulate, const float* mask, cudaStream_t s) {
+    const Layer& l = layers[li];
+    GemmArgs g{};
+    g.A = G; g.B = theta + l.w; g.C = C;
+    g.sAr = l.out; g.sAt = 1; g.sBt = 1; g.sBc = l.out;
+    g.R = (int)rows; g.Cn = l.in; g.ldc = l.in;
+    g.accumulate = accumulate; g.mask = mask; g.ldmask = l.in;
+    g.t_base = 0; g.t_end = l.out;
+    dim3 grid(cdiv(rows, 64), cdiv(l.in, 64), 1);
+    gemm64_kernel<true, true><<<grid, 256, 0, s>>>(g);
+    CKL();
+    return 0;
+}
+
+// parts[slot][w_off + i*out + j] = sum_{rows of slot} [A,1][row][i] * G[row][j]
+// A/G point at the first row of the launch; rows are split as n_groups groups of B rows, Sg slots per group.
+int Engine::gemm_dw(const float* A, const float* G, int li, long rows, long B, int slot0, int n_slots, cudaStream_t s) {
+    const Layer& l = layers[li];
+    GemmArgs g{};
+    g.A = A; g.B = G; g.C = parts + (size_t)slot0 * Ppad + l.w;
+    g.sAr = 1; g.sAt = l.in; g.sBt = l.out; g.sBc = 1;
+    g.R = l.in + 1; g.Cn = l.out; g.ldc = l.out;
+    g.ones_row = 1;
+    g.chunk = chunk_rows; g.slots_per_group = Sg; g.group_rows = (int)B;
+    g.t_base = 0; g.t_end = (int)rows; g.slot_stride = Ppad;
+    dim3 grid(cdiv(l.in + 1, 64), cdiv(l.out, 64), n_slots);
+    gemm64_kernel<false, false><<<grid, 256, 0, s>>>(g);
+    CKL();
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- forward
+int Engine::forward(const Pass& p, cudaStream_t s) {
+    const long B = p.B, Rt = (long)p.R * B, Rd = (long)p.Rd * B;
+    // encoder (models.py:30-36)
+    const float* a = nullptr;
+    for (int k = 0; k < n; ++k) {
+        if (k == 0) { for (int g = 0; g < p.R; ++g) TRY(gemm_fwd(p.x[g], 0, act_e[1] + (size_t)g * B * hid[0], B, true, s)); }
+        else TRY(gemm_fwd(a, k, act_e[k + 1], Rt, true, s));
+        a = act_e[k + 1];
+    }
+    if (n == 0) {
+        for (int g = 0; g < p.R; ++g) {
+            TRY(gemm_fwd(p.x[g], 0, mu + (size_t)g * B * L, B, false, s));
+            TRY(gemm_fwd(p.x[g], 1, lv + (size_t)g * B * L, B, false, s));
+        }
+    } else {
+        TRY(gemm_fwd(a, n, mu, Rt, false, s));
+        TRY(gemm_fwd(a, n + 1, lv, Rt, false, s));
+    }
+    // Sampling + KLD (models.py:9-15,81-85)
+    LatentArgs la{};
+    la.mu = mu; la.lv = lv; la.z = z; la.eps_out = eps_buf; la.kld = kld;
+    la.eps_ext = p.eps; la.n_eps = p.n_eps; la.n_rows = Rt; la.n_dec = Rd; la.B = B; la.L = L;
+    la.seed = cfg.seed; la.row_offset = row_offset;
+    la.step_base = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
+    la.per_group_step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP);
+    latent_fwd_kernel<<<cdiv(Rt, 128), 128, 0, s>>>(la);
+    CKL();
+    ++calls;
+    if (Rd == 0) return 0;
+    // decoder (models.py:49-52) + clip + reconstruction loss (models.py:66,72-78)
+    const float* d = z;
+    for (int k = 0; k < n; ++k) { TRY(gemm_fwd(d, n + 2 + k, act_d[k + 1], Rd, true, s)); d = act_d[k + 1]; }
+    TRY(gemm_fwd(d, 2 * n + 2, y, Rd, false, s));
+    if (p.want_rec) {
+        for (int g = 0; g < p.Rd; ++g) {
+            rec_fwd_kernel<<<cdiv(B * 32, 256), 256, 0, s>>>(p.x[g], y + (size_t)g * B * D, rec + (size_t)g * B, B, D, mse_type());
+            CKL();
+        }
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- backward
+int Engine::backward(const Pass& p, cudaStream_t s) {
+    const long B = p.B, Rt = (long)p.R * B, Rd = (long)p.Rd * B;
+    Sg = (int)std::min<long>(kMaxSlots / 3, std::max<long>(1, (B + 255) / 256));
+    chunk_rows = (int)((B + Sg - 1) / Sg);
+    const int S = Sg * p.R;
+    n_slots_used = S;
+    float* g = nullptr; float* gn = nullptr;
+    // decoder side
+    for (int gi = 0; gi < p.Rd; ++gi) {
+        rec_bwd_kernel<<<cdiv(B * D, 256), 256, 0, s>>>(p.x[gi], y + (size_t)gi * B * D, g_rec + (size_t)gi * B, B, D, mse_type());
+        CKL();
+    }
+    g = y;
+    for (int k = n; k >= 0; --k) {
+        int li = n + 2 + k;
+        const float* inp = (k == 0) ? z : act_d[k];
+        TRY(gemm_dw(inp, g, li, Rd, B, 0, S, s));
+        gn = (g == gA) ? gB : gA;
+        TRY(gemm_dx(g, li, gn, Rd, false, k > 0 ? inp : nullptr, s));
+        g = gn;
+    }
+    // g == g_z [Rd, L]
+    latent_bwd_kernel<<<cdiv(Rt * L, 256), 256, 0, s>>>(mu, lv, eps_buf, g, g_kld, g_mu, g_lv, Rt, Rd, L);
+    CKL();
+    if (n == 0) {
+        for (int gi = 0; gi < p.R; ++gi) {
+            TRY(gemm_dw(p.x[gi], g_mu + (size_t)gi * B * L, 0, B, B, gi * Sg, Sg, s));
+            TRY(gemm_dw(p.x[gi], g_lv + (size_t)gi * B * L, 1, B, B, gi * Sg, Sg, s));
+        }
+        return 0;
+    }
+    TRY(gemm_dw(act_e[n], g_mu, n, Rt, B, 0, S, s));
+    TRY(gemm_dw(act_e[n], g_lv, n + 1, Rt, B, 0, S, s));
+    gn = (g == gA) ? gB : gA;
+    TRY(gemm_dx(g_mu, n, gn, Rt, false, nullptr, s));
+    TRY(gemm_dx(g_lv, n + 1, gn, Rt, true, act_e[n], s));
+    g = gn;
+    for (int k = n - 1; k >= 0; --k) {
+        if (k == 0) {
+            for (int gi = 0; gi < p.R; ++gi) TRY(gemm_dw(p.x[gi], g + (size_t)gi * B * hid[0], 0, B, B, gi * Sg, Sg, s));
+        } else {
+            TRY(gemm_dw(act_e[k], g, k, Rt, B, 0, S, s));
+            gn = (g == gA) ? gB : gA;
+            TRY(gemm_dx(g, k, gn, Rt, false, act_e[k], s));
+            g = gn;
+        }
+    }
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------- pass planning
+int Engine::plan(Pass& p, const float* x_bkg, const float* x_ood, const float* eps, int n_eps, long B) {
+    if (B <= 0) return fail(OEVAE_EINVAL, "empty batch");
+    if (!x_bkg) return fail(OEVAE_EINVAL, "x_bkg is null");
+    p = Pass{};
+    p.B = B; p.want_rec = true;
+    p.x[0] = x_bkg; p.R = 1; p.Rd = 1;
+    if (x_ood) {
+        if (cfg.oe_type == OEVAE_OE_KLD) { p.x[1] = x_ood; p.R = 2; p.Rd = 1; }
+        else {
+            bool fresh = cfg.noise_mode == OEVAE_NOISE_PER_STEP || (cfg.noise_mode == OEVAE_NOISE_EXTERNAL && n_eps == 3);
+            if (fresh) { p.x[1] = x_bkg; p.x[2] = x_ood; p.R = 3; p.Rd = 3; }
+            else { p.x[1] = x_ood; p.R = 2; p.Rd = 2; }
+        }
+    }
+    if (cfg.noise_mode == OEVAE_NOISE_EXTERNAL) {
+        if (!eps) return fail(OEVAE_EINVAL, "noise_mode EXTERNAL needs eps");
+        if (n_eps != 1 && n_eps < p.Rd) return fail(OEVAE_EINVAL, "n_eps must be 1 or >= %d", p.Rd);
+        p.eps = eps; p.n_eps = n_eps;
+    } else if (eps) {
+        return fail(OEVAE_EINVAL, "eps given but noise_mode is not EXTERNAL");
+    }
+    return reserve((long)p.R * B);
+}
+
+int Engine::losses(const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood, const float* eps, int n_eps,
+                   long B, float beta, float lamb, float margin, float* per_jet, double* sums, bool want_grad, cudaStream_t s) {
+    if (!w_bkg) return fail(OEVAE_EINVAL, "w_bkg is null");
+    if ((x_ood == nullptr) != (w_ood == nullptr)) return fail(OEVAE_EINVAL, "x_ood and w_ood must be given together");
+    Pass p;
+    TRY(plan(p, x_bkg, x_ood, eps, n_eps, B));
+    TRY(forward(p, s));
+    CombineArgs ca{};
+    ca.rec = rec; ca.kld = kld; ca.w = w_bkg; ca.w_ood = w_ood;
+    ca.g_rec = want_grad ? g_rec : nullptr; ca.g_kld = want_grad ? g_kld : nullptr;
+    ca.per_jet = per_jet; ca.sums = sums;
+    ca.B = B; ca.n_groups = p.R; ca.oe_type = cfg.oe_type; ca.have_ood = x_ood != nullptr;
+    ca.beta = beta; ca.lamb = lamb; ca.margin = margin;
+    combine_kernel<<<cdiv(B, 256), 256, 0, s>>>(ca);
+    CKL();
+    if (want_grad) TRY(backward(p, s));
+    return 0;
+}
+
+int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply, float lr, cudaStream_t s) {
+    AdamArgs a{};
+    if (grad_in) { a.grad_in = grad_in; }
+    else { a.parts = parts; a.n_parts = n_slots_used; a.part_stride = Ppad; a.grad_out = grad_out; }
+    a.theta = theta; a.m = m; a.v = v; a.n = P;
+    a.b1 = 0.9f; a.b2 = 0.999f; a.eps = 1e-7f; a.apply = apply;
+    if (apply) {
+        ++step;
+        double t = (double)step;
+        a.alpha = (float)((double)lr * std::sqrt(1.0 - std::pow(0.999, t)) / (1.0 - std::pow(0.9, t)));
+    }
+    adam_kernel<<<cdiv(P, 256), 256, 0, s>>>(a);
+    CKL();
+    return 0;
+}
+
+int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o_mse, float* o_mae, float* o_kld, float* o_jsd,
+                  float* o_lat, unsigned char* o_fin, float* o_xhat, cudaStream_t s) {
+    if (N < 0 || n_iter < 1) return fail(OEVAE_EINVAL, "bad N / n_iter");
+    if (cfg.noise_mode == OEVAE_NOISE_EXTERNAL && !eps) return fail(OEVAE_EINVAL, "noise_mode EXTERNAL needs eps");
+    long chunk = std::min<long>(N, std::max<long>(cap_rows, 65536));
+    if (N == 0) return 0;
+    TRY(reserve(chunk));
+    for (long r0 = 0; r0 < N; r0 += chunk) {
+        long nr = std::min(chunk, N - r0);
+        for (int it = 0; it < n_iter; ++it) {
+            Pass p{};
+            p.B = nr; p.R = 1; p.Rd = 1; p.x[0] = x + (size_t)r0 * D; p.want_rec = false;
+            if (eps) { p.eps = eps + ((size_t)it * N + r0) * L; p.n_eps = 1; }
+            unsigned long long save = row_offset; row_offset += (unsigned long long)r0;
+            int rc = forward(p, s);
+            row_offset = save;
+            if (rc) return rc;
+            if (n_iter > 1) { accum_clip_kernel<<<cdiv(nr * D, 256), 256, 0, s>>>(y, ysum, nr * D, it == 0); CKL(); }
+        }
+        bool need = o_mse || o_mae || o_kld || o_jsd || o_fin || o_xhat;
+        if (need) {
+            MetricOut mo{};
+            mo.mse = o_mse ? o_mse + r0 : nullptr; mo.mae = o_mae ? o_mae + r0 : nullptr;
+            mo.kld = o_kld ? o_kld + r0 : nullptr; mo.jsd = o_jsd ? o_jsd + r0 : nullptr;
+            mo.finite = o_fin ? o_fin + r0 : nullptr; mo.xhat = o_xhat ? o_xhat + (size_t)r0 * D : nullptr;
+            score_metrics_kernel<<<cdiv(nr * 32, 256), 256, 0, s>>>(x + (size_t)r0 * D, n_iter > 1 ? ysum : y, 1.f / (float)n_iter, n_iter == 1, nr, D, mo);
+            CKL();
+        }
+        if (o_lat) { latent_out_kernel<<<cdiv(nr, 256), 256, 0, s>>>(kld, o_lat + r0, nr); CKL(); }
+    }
+    return 0;
+}
+
+int Engine::encode(const float* x, long N, const float* eps, float* o_mu, float* o_lv, float* o_z, cudaStream_t s) {
+    if (N <= 0) return fail(OEVAE_EINVAL, "bad N");
+    if (cfg.noise_mode == OEVAE_NOISE_EXTERNAL && !eps && o_z) return fail(OEVAE_EINVAL, "noise_mode EXTERNAL needs eps");
+    long chunk = std::min<long>(N, std::max<long>(cap_rows, 65536));
+    TRY(reserve(chunk));
+    for (long r0 = 0; r0 < N; r0 += chunk) {
+        long nr = std::min(chunk, N - r0);
+        Pass p{};
+        p.B = nr; p.R = 1; p.Rd = 1; p.x[0] = x + (size_t)r0 * D; p.want_rec = false; p.encoder_only = true;
+        if (eps) { p.eps = eps + (size_t)r0 * L; p.n_eps = 1; }
+        unsigned long long save = row_offset; row_offset += (unsigned long long)r0;
+        int rc = forward_encoder(p, s);
+        row_offset = save;
+        if (rc) return rc;
+        if (o_mu) CK(cudaMemcpyAsync(o_mu + (size_t)r0 * L, mu, (size_t)nr * L * 4, cudaMemcpyDeviceToDevice, s));
+        if (o_lv) CK(cudaMemcpyAsync(o_lv + (size_t)r0 * L, lv, (size_t)nr * L * 4, cudaMemcpyDeviceToDevice, s));
+        if (o_z) CK(cudaMemcpyAsync(o_z + (size_t)r0 * L, z, (size_t)nr * L * 4, cudaMemcpyDeviceToDevice, s));
+    }
+    return 0;
+}
+
+// encoder + sampling only (vae.encoder(X), models.py:30-36)
+int Engine::forward_encoder(const Pass& p, cudaStream_t s) {
+    const long B = p.B;
+    const float* a = p.x[0];
+    for (int k = 0; k < n; ++k) { TRY(gemm_fwd(a, k, act_e[k + 1], B, true, s)); a = act_e[k + 1]; }
+    TRY(gemm_fwd(a, n, mu, B, false, s));
+    TRY(gemm_fwd(a, n + 1, lv, B, false, s));
+    LatentArgs la{};
+    la.mu = mu; la.lv = lv; la.z = z; la.eps_out = eps_buf; la.kld = kld;
+    la.eps_ext = p.eps; la.n_eps = 1; la.n_rows = B; la.n_dec = B; la.B = B; la.L = L;
+    la.seed = cfg.seed; la.row_offset = row_offset;
+    la.step_base = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
+    la.per_group_step = 0;
+    if (cfg.noise_mode == OEVAE_NOISE_EXTERNAL && !p.eps) { la.n_dec = 0; }
+    latent_fwd_kernel<<<cdiv(B, 128), 128, 0, s>>>(la);
+    CKL();
+    ++calls;
+    return 0;
+}
+
+// ================================================================================================ C ABI
+#define H(h) if (!(h)) return OEVAE_EINVAL; Engine* e = reinterpret_cast<Engine*>(h); cudaSetDevice(e->cfg.device)
+
+extern "C" {
+
+int oevae_version(void) { return OEVAE_VERSION; }
+
+int oevae_create(const oevae_config* cfg, oevae_t* out) {
+    if (!cfg || !out) { g_create_error = "null argument"; return OEVAE_EINVAL; }
+    Engine* e = new (std::nothrow) Engine();
+    if (!e) { g_create_error = "out of host memory"; return OEVAE_ENOMEM; }
+    int rc = e->init(*cfg);
+    if (rc) { g_create_error = e->err; delete e; *out = nullptr; return rc; }
+    *out = reinterpret_cast<oevae_t>(e);
+    return 0;
+}
+
+int oevae_destroy(oevae_t h) {
+    if (!h) return OEVAE_EINVAL;
+    Engine* e = reinterpret_cast<Engine*>(h);
+    cudaSetDevice(e->cfg.device);
+    cudaDeviceSynchronize();
+    delete e;
+    return 0;
+}
+
+const char* oevae_last_error(oevae_t h) {
+    if (!h) return g_create_error.c_str();
+    return reinterpret_cast<Engine*>(h)->err.c_str();
+}
+
+int64_t oevae_n_params(oevae_t h) { return h ? reinterpret_cast<Engine*>(h)->P : -1; }
+
+int oevae_param_layout(oevae_t h, int64_t* offsets, int32_t* dims_in, int32_t* dims_out, int32_t cap) {
+    if (!h) return OEVAE_EINVAL;
+    Engine* e = reinterpret_cast<Engine*>(h);
+    int nl = (int)e->layers.size();
+    for (int i = 0; i < nl && i < cap; ++i) {
+        if (offsets) { offsets[2 * i] = e->layers[i].w; offsets[2 * i + 1] = e->layers[i].b; }
+        if (dims_in) dims_in[i] = e->layers[i].in;
+        if (dims_out) dims_out[i] = e->layers[i].out;
+    }
+    return nl;
+}
+
+int oevae_set_params_host(oevae_t h, const float* flat, int64_t nn) {
+    H(h);
+    if (!flat || nn != e->P) return e->fail(OEVAE_EINVAL, "set_params: expected %ld floats, got %ld", e->P, (long)nn);
+    return e->cuda_check(cudaMemcpy(e->theta, flat, nn * 4, cudaMemcpyHostToDevice), "set_params");
+}
+int oevae_get_params_host(oevae_t h, float* flat, int64_t nn) {
+    H(h);
+    if (!flat || nn != e->P) return e->fail(OEVAE_EINVAL, "get_params: expected %ld floats, got %ld", e->P, (long)nn);
+    return e->cuda_check(cudaMemcpy(flat, e->theta, nn * 4, cudaMemcpyDeviceToHost), "get_params");
+}
+int oevae_set_opt_state_host(oevae_t h, const float* mh, const float* vh, int64_t nn, int64_t step) {
+    H(h);
+    if (!mh || !vh || nn != e->P || step < 0) return e->fail(OEVAE_EINVAL, "set_opt_state: bad arguments");
+    int rc = e->cuda_check(cudaMemcpy(e->m, mh, nn * 4, cudaMemcpyHostToDevice), "set_opt_state m");
+    if (rc) return rc;
+    rc = e->cuda_check(cudaMemcpy(e->v, vh, nn * 4, cudaMemcpyHostToDevice), "set_opt_state v");
+    if (rc) return rc;
+    e->step = step;
+    return 0;
+}
+int oevae_get_opt_state_host(oevae_t h, float* mh, float* vh, int64_t nn, int64_t* step) {
+    H(h);
+    if (nn != e->P) return e->fail(OEVAE_EINVAL, "get_opt_state: bad size");
+    if (mh) { int rc = e->cuda_check(cudaMemcpy(mh, e->m, nn * 4, cudaMemcpyDeviceToHost), "get_opt_state m"); if (rc) return rc; }
+    if (vh) { int rc = e->cuda_check(cudaMemcpy(vh, e->v, nn * 4, cudaMemcpyDeviceToHost), "get_opt_state v"); if (rc) return rc; }
+    if (step) *step = e->step;
+    return 0;
+}
+float* oevae_params_device(oevae_t h) { return h ? reinterpret_cast<Engine*>(h)->theta : nullptr; }
+
+int oevae_set_noise_offset(oevae_t h, uint64_t row_offset) { H(h); e->row_offset = row_offset; return 0; }
+int oevae_set_oe_type(oevae_t h, int32_t t) { H(h); if (t < 0 || t > 4) return e->fail(OEVAE_EINVAL, "bad oe_type %d", t); e->cfg.oe_type = t; return 0; }
+
+int oevae_train_step(oevae_t h, const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood,
+                     const float* eps, int32_t n_eps, int64_t B, float lr, float beta, float lamb, float margin,
+                     float* per_jet_out, double* sums_acc, void* stream) {
+    H(h);
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = e->losses(x_bkg, w_bkg, x_ood, w_ood, eps, n_eps, B, beta, lamb, margin, per_jet_out, sums_acc, true, s);
+    if (rc) return rc;
+    return e->reduce_and_update(nullptr, nullptr, true, lr, s);
+}
+
+int oevae_loss_and_grad(oevae_t h, const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood,
+                        const float* eps, int32_t n_eps, int64_t B, float beta, float lamb, float margin,
+                        float* per_jet_out, double* sums_acc, float* grad_out, void* stream) {
+    H(h);
+    if (!grad_out) return e->fail(OEVAE_EINVAL, "grad_out is null");
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = e->losses(x_bkg, w_bkg, x_ood, w_ood, eps, n_eps, B, beta, lamb, margin, per_jet_out, sums_acc, true, s);
+    if (rc) return rc;
+    return e->reduce_and_update(grad_out, nullptr, false, 0.f, s);
+}
+
+int oevae_apply_update(oevae_t h, const float* grad, float lr, void* stream) {
+    H(h);
+    if (!grad) return e->fail(OEVAE_EINVAL, "grad is null");
+    return e->reduce_and_update(nullptr, grad, true, lr, (cudaStream_t)stream);
+}
+
+int oevae_eval_losses(oevae_t h, const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood,
+                      const float* eps, int32_t n_eps, int64_t B, float beta, float lamb, float margin,
+                      float* per_jet_out, double* sums_acc, void* stream) {
+    H(h);
+    return e->losses(x_bkg, w_bkg, x_ood, w_ood, eps, n_eps, B, beta, lamb, margin, per_jet_out, sums_acc, false, (cudaStream_t)stream);
+}
+
+int oevae_encode(oevae_t h, const float* x, int64_t N, const float* eps, float* mu, float* log_var, float* z, void* stream) {
+    H(h);
+    if (!x) return e->fail(OEVAE_EINVAL, "x is null");
+    return e->encode(x, N, eps, mu, log_var, z, (cudaStream_t)stream);
+}
+
+int oevae_score(oevae_t h, const float* x, int64_t N, int32_t n_iter, const float* eps, float* mse, float* mae, float* kld,
+                float* jsd, float* latent, uint8_t* finite, float* xhat, void* stream) {
+    H(h);
+    if (!x && N > 0) return e->fail(OEVAE_EINVAL, "x is null");
+    return e->score(x, N, n_iter, eps, mse, mae, kld, jsd, latent, finite, xhat, (cudaStream_t)stream);
+}
+
+// ---- handle-free kernels
+static thread_local std::string g_free_error;
+static int free_fail(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return 0;
+    g_create_error = std::string(what) + ": " + cudaGetErrorString(e);
+    return OEVAE_ECUDA;
+}
+
+int oevae_preprocess(const void* raw, int32_t raw_dtype, int64_t N, int32_t n_raw, int32_t n_const, int32_t n_dims,
+                     const double* center, const double* scale, int32_t sort, float* x_out, float* pt_out, float* m_out,
+                     int32_t device, void* stream) {
+    if (N == 0) return 0;
+    if (!raw || !x_out || N < 0 || n_raw <= 0 || n_const <= 0 || (n_dims != 3 && n_dims != 4) || (raw_dtype != 0 && raw_dtype != 1) || (center && !scale)) {
+        g_create_error = "preprocess: bad arguments"; return OEVAE_EINVAL;
+    }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    int n_pad = 32; while (n_pad < n_raw) n_pad <<= 1;
+    size_t per_warp = (size_t)n_pad * 8 + (size_t)n_raw * 16;
+    int warps = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)(200 * 1024) / per_warp));
+    if (per_warp > 200 * 1024) { g_create_error = "preprocess: n_raw too large"; return OEVAE_EUNSUPPORTED; }
+    size_t smem = per_warp * warps;
+    cudaStream_t s = (cudaStream_t)stream;
+    unsigned grid = cdiv(N, warps);
+    if (raw_dtype == 0) {
+        if (smem > 48 * 1024) { rc = free_fail(cudaFuncSetAttribute(preprocess_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "smem attr"); if (rc) return rc; }
+        preprocess_kernel<float><<<grid, warps * 32, smem, s>>>((const float*)raw, N, n_raw, n_pad, n_const, n_dims, center, scale, sort, x_out, pt_out, m_out);
+    } else {
+        if (smem > 48 * 1024) { rc = free_fail(cudaFuncSetAttribute(preprocess_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "smem attr"); if (rc) return rc; }
+        preprocess_kernel<__half><<<grid, warps * 32, smem, s>>>((const __half*)raw, N, n_raw, n_pad, n_const, n_dims, center, scale, sort, x_out, pt_out, m_out);
+    }
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "preprocess launch");
+}
+
+int oevae_affine(const float* x, float* y, int64_t N, int32_t D, const double* center, const double* scale, int32_t device, void* stream) {
+    if (N == 0) return 0;
+    if (!x || !y || N < 0 || D <= 0 || !scale) { g_create_error = "affine: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    affine_kernel<<<cdiv(N * D, 256), 256, 0, (cudaStream_t)stream>>>(x, y, N, D, center, scale);
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "affine launch");
+}
+
+int oevae_pair_metrics(const float* P, const float* Q, int64_t N, int32_t D, float* mse, float* mae, float* mare, float* kld,
+                       float* jsd, float* xs, int32_t device, void* stream) {
+    if (N == 0) return 0;
+    if (!P || !Q || N < 0 || D <= 0) { g_create_error = "pair_metrics: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    MetricOut mo{};
+    mo.mse = mse; mo.mae = mae; mo.mare = mare; mo.kld = kld; mo.jsd = jsd; mo.xs = xs;
+    score_metrics_kernel<<<cdiv(N * 32, 256), 256, 0, (cudaStream_t)stream>>>(P, Q, 1.f, 0, N, D, mo);
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "pair_metrics launch");
+}
+
+int oevae_minmax(const float* v, const uint8_t* keep, int64_t N, double* minmax_out, int32_t device, void* stream) {
+    if (!minmax_out || (N > 0 && !v)) { g_create_error = "minmax: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    if (N <= 0) return 0;
+    unsigned grid = std::min<unsigned>(cdiv(N, 256), 148 * 8);
+    minmax_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(v, keep, N, minmax_out);
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "minmax launch");
+}
+
+int oevae_loss_map(float* v, int64_t N, int32_t branch, int32_t device, void* stream) {
+    if ((N > 0 && !v) || branch < 0 || branch > 4) { g_create_error = "loss_map: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    if (N <= 0) return 0;
+    loss_map_kernel<<<cdiv(N, 256), 256, 0, (cudaStream_t)stream>>>(v, N, branch);
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "loss_map launch");
+}
+
+int oevae_hist(const float* var, const float* w, const float* jzw, const float* score, const uint8_t* keep, int64_t N, float cut,
+               const double* edges, int32_t n_edges, int64_t* counts, double* wsums, int32_t device, void* stream) {
+    if (n_edges < 2 || !edges || !counts || (w && !wsums) || (N > 0 && (!var || !jzw))) { g_create_error = "hist: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    if (N <= 0) return 0;
+    size_t smem = (size_t)n_edges * 8 + (size_t)(n_edges - 1) * 2 * (8 + 4);
+    if (smem > 200 * 1024) { g_create_error = "hist: too many bins"; return OEVAE_EUNSUPPORTED; }
+    if (smem > 48 * 1024) { rc = free_fail(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "smem attr"); if (rc) return rc; }
+    unsigned grid = std::min<unsigned>(cdiv(N, 256 * 8), 148 * 4);
+    hist_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(var, w, jzw, score, keep, N, cut, edges, n_edges,
+                                                           reinterpret_cast<unsigned long long*>(counts), wsums);
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "hist launch");
+}
+
+int64_t oevae_launch_count(void) { return g_launches.load(); }
+
+}  // extern "C"

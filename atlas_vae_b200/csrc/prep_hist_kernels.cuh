@@ -1,0 +1,202 @@
+// K0 (constituent preprocessing) and K5 (cut + per-class histogram): HBM-bound byte/compare work.
+#pragma once
+#include "common.cuh"
+#include <cuda_fp16.h>
+
+namespace oevae {
+
+// ------------------------------------------------------------------------------------------------
+// K0: jets_sorting (utils.py:564-571) + keep n_const / zero-pad (utils.py:89-97) + n_dims slice
+// (utils.py:115-119) + get_4v (utils.py:300-308) + affine scaler (utils.py:406-417), one warp per jet.
+// Sort key: (fp32 bits of pT, constituent index): descending pT, ties in DESCENDING index order, i.e.
+// np.argsort(pt, kind='stable')[::-1].  (The reference's default introsort leaves the order of exact non-zero
+// ties platform-defined; ties inside the all-zero padding block do not change the output.)
+// All arithmetic that feeds a comparison or the jet mass is done with explicit round-to-nearest
+// intrinsics (no FMA contraction) and in NumPy's evaluation order so that pt/m are bit-identical.
+// ------------------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+
+template <typename T>
+__global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, int n_pad, int n_const, int n_dims,
+                                  const double* __restrict__ center, const double* __restrict__ scale, int do_sort,
+                                  float* __restrict__ x_out, float* __restrict__ pt_out, float* __restrict__ m_out) {
+    extern __shared__ unsigned char smem_raw[];
+    const int warps = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // per warp: n_raw*4 floats + n_pad u64 keys
+    const size_t per_warp = (size_t)n_pad * 8 + (size_t)n_raw * 16;
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw + per_warp * wid);
+    float* v = reinterpret_cast<float*>(keys + n_pad);
+    long jet = (long)blockIdx.x * warps + wid;
+    if (jet >= N) return;
+    const T* src = raw + jet * 4L * n_raw;
+    for (int i = lane; i < 4 * n_raw; i += 32) v[i] = to_f32<T>(src[i]);
+    __syncwarp();
+    for (int c = lane; c < n_pad; c += 32) {
+        unsigned long long k = 0ull;
+        if (c < n_raw) {
+            float px = v[4 * c + 1], py = v[4 * c + 2];
+            float pt = __fsqrt_rn(__fadd_rn(__fmul_rn(px, px), __fmul_rn(py, py)));
+            k = ((unsigned long long)__float_as_uint(pt) << 32) | (unsigned)(c + 1);
+        }
+        keys[c] = k;
+    }
+    __syncwarp();
+    // bitonic sort, descending (do_sort == 0: keep the stored order, e.g. get_4v on already sorted jets)
+    if (!do_sort) {
+        for (int c = lane; c < n_pad; c += 32) keys[c] = c < n_raw ? (unsigned long long)(c + 1) : 0ull;
+        __syncwarp();
+    }
+    for (int k = 2; do_sort && k <= n_pad; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = lane; i < n_pad; i += 32) {
+                int p = i ^ j;
+                if (p > i) {
+                    unsigned long long a = keys[i], b = keys[p];
+                    bool desc = (i & k) == 0;
+                    if (desc ? (a < b) : (a > b)) { keys[i] = b; keys[p] = a; }
+                }
+            }
+            __syncwarp();
+        }
+    }
+    const int D = n_dims * n_const, skip = 4 - n_dims;
+    float* xo = x_out + jet * (long)D;
+    for (int o = lane; o < D; o += 32) {
+        int c = o / n_dims, d = o - c * n_dims + skip;
+        float val = 0.f;
+        if (c < n_raw) {
+            unsigned idx = (unsigned)(keys[c] & 0xffffffffull);
+            if (idx) val = v[4 * (idx - 1) + d];
+        }
+        if (scale) {
+            double t = (double)val;
+            if (center) t = (double)(float)(t - center[o]);
+            val = (float)(t / scale[o]);
+        }
+        xo[o] = val;
+    }
+    if (pt_out || m_out) {
+        // sequential sum over the kept constituents, one lane per 4-vector component (np.sum(axis=1) order)
+        float s = 0.f;
+        if (lane < 4) {
+            int nk = min(n_const, n_raw);
+            for (int c = 0; c < nk; ++c) {
+                unsigned idx = (unsigned)(keys[c] & 0xffffffffull);
+                s = __fadd_rn(s, v[4 * (idx - 1) + lane]);
+            }
+        }
+        float E = __shfl_sync(0xffffffffu, s, 0), px = __shfl_sync(0xffffffffu, s, 1);
+        float py = __shfl_sync(0xffffffffu, s, 2), pz = __shfl_sync(0xffffffffu, s, 3);
+        if (lane == 0) {
+            float px2 = __fmul_rn(px, px), py2 = __fmul_rn(py, py);
+            if (pt_out) pt_out[jet] = __fsqrt_rn(__fadd_rn(px2, py2));
+            if (m_out) {
+                float m2 = __fsub_rn(__fsub_rn(__fsub_rn(__fmul_rn(E, E), px2), py2), __fmul_rn(pz, pz));
+                m_out[jet] = __fsqrt_rn(fmaxf(0.f, m2));
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// loss_mapping (plots.py:15-20): global min/max (decides the branch) and the elementwise map.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void atomic_min_double(double* addr, double val) {
+    unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
+    unsigned long long old = *a, assumed;
+    do {
+        assumed = old;
+        if (__longlong_as_double((long long)assumed) <= val) break;
+        old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(val));
+    } while (assumed != old);
+}
+__device__ __forceinline__ void atomic_max_double(double* addr, double val) {
+    unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
+    unsigned long long old = *a, assumed;
+    do {
+        assumed = old;
+        if (__longlong_as_double((long long)assumed) >= val) break;
+        old = atomicCAS(a, assumed, (unsigned long long)__double_as_longlong(val));
+    } while (assumed != old);
+}
+
+// minmax[0] = min, minmax[1] = max, minmax[2] += number of NaN entries; caller initialises {+inf,-inf,0}
+__global__ void minmax_kernel(const float* __restrict__ v, const unsigned char* __restrict__ keep, long N, double* minmax) {
+    float lo = INFINITY, hi = -INFINITY; int nan = 0;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (long)gridDim.x * blockDim.x) {
+        if (keep && !keep[i]) continue;
+        float x = v[i];
+        if (isnan(x)) { nan++; continue; }
+        lo = fminf(lo, x); hi = fmaxf(hi, x);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+        nan += __shfl_xor_sync(0xffffffffu, nan, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (lo <= hi) { atomic_min_double(minmax, (double)lo); atomic_max_double(minmax + 1, (double)hi); }
+        if (nan) atomicAdd(minmax + 2, (double)nan);
+    }
+}
+
+__global__ void loss_map_kernel(float* __restrict__ v, long N, int branch) {
+    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    float x = v[i], y;
+    switch (branch) {
+        case 0: y = x; break;
+        case 1: y = x + 1.f; break;
+        case 2: y = x / (fabsf(x) + 1.f); break;
+        case 3: y = x / (fabsf(x) + 1.f) + 1.f; break;
+        default: y = (x / (fabsf(x) + 1.f) + 1.f) / 2.f; break;
+    }
+    v[i] = y;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5: make_cut mask (plots.py:259: X_loss > loss_cut) + per-class histogram of plot_distributions
+// (plots.py:697-715; np.histogram semantics with float64 edges: bin k = [e_k, e_k+1), last bin closed,
+// out-of-range and NaN values dropped).  Shared-memory privatised integer counts and fp64 weighted sums
+// per CTA, flushed with one atomic per non-empty bin.
+// ------------------------------------------------------------------------------------------------
+__global__ void hist_kernel(const float* __restrict__ var, const float* __restrict__ w, const float* __restrict__ jzw,
+                            const float* __restrict__ score, const unsigned char* __restrict__ keep, long N, float cut,
+                            const double* __restrict__ edges, int n_edges,
+                            unsigned long long* __restrict__ counts, double* __restrict__ wsums) {
+    extern __shared__ unsigned char smem_raw[];
+    const int nb = n_edges - 1;
+    double* s_edges = reinterpret_cast<double*>(smem_raw);
+    double* s_w = s_edges + n_edges;                       // [2*nb]
+    unsigned int* s_c = reinterpret_cast<unsigned int*>(s_w + 2 * nb);   // [2*nb]
+    for (int i = threadIdx.x; i < n_edges; i += blockDim.x) s_edges[i] = edges[i];
+    for (int i = threadIdx.x; i < 2 * nb; i += blockDim.x) { s_w[i] = 0.0; s_c[i] = 0u; }
+    __syncthreads();
+    const double e0 = s_edges[0], e1 = s_edges[nb];
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (long)gridDim.x * blockDim.x) {
+        if (keep && !keep[i]) continue;
+        if (score && !(score[i] > cut)) continue;          // NaN scores fail the cut
+        float z = jzw[i];
+        int cls = (z == -1.f) ? 0 : (z >= 0.f ? 1 : -1);
+        if (cls < 0) continue;
+        double x = (double)var[i];
+        if (!(x >= e0 && x <= e1)) continue;               // also drops NaN
+        int lo = 0, hi = nb;                               // largest k with edges[k] <= x  (searchsorted right - 1)
+        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (s_edges[mid] <= x) lo = mid; else hi = mid; }
+        int bin = lo;                                      // x == last edge lands in the last bin (lo == nb-1)
+        atomicAdd(&s_c[cls * nb + bin], 1u);
+        if (w) atomicAdd(&s_w[cls * nb + bin], (double)w[i]);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * nb; i += blockDim.x) {
+        if (s_c[i]) {
+            atomicAdd(&counts[i], (unsigned long long)s_c[i]);
+            if (w) atomicAdd(&wsums[i], s_w[i]);
+        }
+    }
+}
+
+}  // namespace oevae

@@ -1,0 +1,171 @@
+/* oevae.h -- C ABI of liboevae.so: the B200-native OE-VAE hot path.
+ *
+ * The reference (dominiquegodin/ATLAS-VAE) is pure Python on TensorFlow-Keras and has NO FFI
+ * layer of its own; the drop-in boundary is the Python contract between OE-VAE/vae.py and
+ * OE-VAE/models.py / utils.py / plots.py.  atlas_vae_b200/{models,utils,cuts}.py keeps that
+ * Python surface and binds the entry points below through ctypes (atlas_vae_b200/_ffi.py).
+ * Every entry point cites the reference code it replaces (paths relative to /root/reference).
+ *
+ * Conventions
+ *   - return 0 on success, a negative OEVAE_E* code on failure; text via oevae_last_error().
+ *     Nothing throws or aborts; CUDA errors are mapped to OEVAE_ECUDA.
+ *   - every data pointer is a DEVICE pointer owned by the caller unless the name ends in _host.
+ *   - all work is enqueued on `stream` (a cudaStream_t passed as void*); no hidden host sync
+ *     except in the *_host getters/setters.
+ *   - a handle is not thread-safe.  One handle per (process, GPU).
+ *   - matrices are row-major fp32; kernels are Keras [in,out]; the flat parameter vector is
+ *     Keras trainable_weights order (models.py:22-28,43-48): encoder hidden (kernel,bias)...,
+ *     dense_mean, dense_log_var, decoder hidden..., dense_output.
+ */
+#ifndef OEVAE_H
+#define OEVAE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OEVAE_VERSION 100
+#if defined(__GNUC__)
+#define OEVAE_API __attribute__((visibility("default")))
+#else
+#define OEVAE_API
+#endif
+
+enum { OEVAE_OK = 0, OEVAE_EINVAL = -1, OEVAE_ECUDA = -2, OEVAE_ENOMEM = -3, OEVAE_EUNSUPPORTED = -4 };
+
+/* OE_type of models.py:72-105 */
+enum { OEVAE_OE_KLD = 0, OEVAE_OE_MSE = 1, OEVAE_OE_MAE = 2, OEVAE_OE_MSE_MARGIN = 3, OEVAE_OE_MAE_MARGIN = 4 };
+
+/* arithmetic of the Dense contractions */
+enum { OEVAE_PREC_FP32 = 0,      /* CUDA-core fp32 FMA: the reference-dtype mode and parity anchor   */
+       OEVAE_PREC_BF16X3 = 1,    /* tcgen05 kind::f16, operands split hi+lo bf16, 3 MMAs, fp32 accum */
+       OEVAE_PREC_TF32 = 2,      /* tcgen05 kind::tf32, fp32 accumulate                              */
+       OEVAE_PREC_BF16 = 3 };    /* tcgen05 kind::f16 on bf16-rounded operands, fp32 accumulate      */
+
+/* where the reparameterisation noise comes from (models.py:9-15) */
+enum { OEVAE_NOISE_FIXED = 0,    /* reference seed=0 behaviour: same eps tensor for every call of a shape */
+       OEVAE_NOISE_PER_STEP = 1, /* fresh Philox4x32-10 draw per call (reference seed=None) */
+       OEVAE_NOISE_EXTERNAL = 2  /* caller passes eps explicitly (parity tests) */ };
+
+typedef struct oevae_handle* oevae_t;
+
+typedef struct {
+    int32_t  input_dim;          /* D = n_dims*n_const (+HLVs)          vae.py:72-76            */
+    int32_t  n_hidden;           /* len(FC_layers)-1                    models.py:22            */
+    int32_t  hidden[8];          /* FC_layers[:-1]                                              */
+    int32_t  latent_dim;         /* FC_layers[-1]                       models.py:27-28         */
+    int32_t  oe_type;            /* OEVAE_OE_*                                                  */
+    int32_t  precision;          /* OEVAE_PREC_*                                                */
+    int32_t  noise_mode;         /* OEVAE_NOISE_*                                               */
+    int32_t  device;             /* CUDA ordinal                                                */
+    uint64_t seed;               /* Philox key                                                  */
+    int64_t  max_batch;          /* workspace is sized for this many jets per call (grown on demand) */
+} oevae_config;
+
+/* ---- lifecycle: VariationalAutoEncoder.__init__ (models.py:55-61) ------------------------- */
+OEVAE_API int         oevae_create(const oevae_config* cfg, oevae_t* out);
+OEVAE_API int         oevae_destroy(oevae_t h);
+OEVAE_API int         oevae_version(void);
+OEVAE_API const char* oevae_last_error(oevae_t h);           /* h may be NULL: last error of a failed create */
+OEVAE_API int64_t     oevae_n_params(oevae_t h);
+/* (name-less) layout: writes 2*(2*n_hidden+3) offsets [kernel_off, bias_off] per Dense, returns count */
+OEVAE_API int         oevae_param_layout(oevae_t h, int64_t* offsets, int32_t* dims_in, int32_t* dims_out, int32_t cap);
+
+/* OE_type used by the next train/eval calls (get_losses takes it per call, models.py:108) */
+OEVAE_API int oevae_set_oe_type(oevae_t h, int32_t oe_type);
+
+/* ---- weights / optimiser state: save_weights / load_weights (models.py:227, vae.py:101,141) */
+OEVAE_API int oevae_set_params_host(oevae_t h, const float* flat_host, int64_t n);
+OEVAE_API int oevae_get_params_host(oevae_t h, float* flat_host, int64_t n);
+OEVAE_API int oevae_set_opt_state_host(oevae_t h, const float* m_host, const float* v_host, int64_t n, int64_t step);
+OEVAE_API int oevae_get_opt_state_host(oevae_t h, float* m_host, float* v_host, int64_t n, int64_t* step);
+OEVAE_API float* oevae_params_device(oevae_t h);              /* device address of the flat parameters (read-only for callers) */
+/* Philox row counter of row 0 of the next calls: a data-parallel rank passes its offset inside the global
+ * batch so that the noise of a jet does not depend on how the batch is sharded. */
+OEVAE_API int oevae_set_noise_offset(oevae_t h, uint64_t row_offset);
+
+/* ---- training step: train_model batch body (models.py:180-190) ----------------------------
+ * get_losses (models.py:108-132) + tape.gradient of the SUM over the batch (models.py:183) +
+ * clip_values on the gradient (models.py:185) + Keras Adam (models.py:138,186).
+ *   x_bkg [B,D], w_bkg [B];  x_ood [B,D] / w_ood [B] nullable together (then the OE term is 0)
+ *   eps    nullable unless noise_mode==EXTERNAL; [n_eps,B,L], n_eps in {1, number of passes}
+ *   per_jet_out nullable [4,B]: rec*w, beta*kld*w, lamb*oe*w_ood, total  (models.py:132)
+ *   sums_acc    nullable double[4]: the four batch SUMS are ADDED to it (keras.metrics.Mean numerators,
+ *               models.py:187-190); the caller zeroes it per epoch and divides by the jet count.
+ */
+OEVAE_API int oevae_train_step(oevae_t h, const float* x_bkg, const float* w_bkg,
+                     const float* x_ood, const float* w_ood,
+                     const float* eps, int32_t n_eps, int64_t B,
+                     float lr, float beta, float lamb, float margin,
+                     float* per_jet_out, double* sums_acc, void* stream);
+
+/* forward + backward only: leaves d(sum_i total_i)/d(theta) (un-clipped) in grad_out [P] so that a
+ * data-parallel caller can all-reduce(SUM) it before oevae_apply_update. */
+OEVAE_API int oevae_loss_and_grad(oevae_t h, const float* x_bkg, const float* w_bkg,
+                        const float* x_ood, const float* w_ood,
+                        const float* eps, int32_t n_eps, int64_t B,
+                        float beta, float lamb, float margin,
+                        float* per_jet_out, double* sums_acc, float* grad_out, void* stream);
+
+/* clip_values(grad) + Adam with the given (possibly all-reduced) gradient; increments the step. */
+OEVAE_API int oevae_apply_update(oevae_t h, const float* grad, float lr, void* stream);
+
+/* get_losses without the tape: validation loop (models.py:201-211) and the public get_losses(). */
+OEVAE_API int oevae_eval_losses(oevae_t h, const float* x_bkg, const float* w_bkg,
+                      const float* x_ood, const float* w_ood,
+                      const float* eps, int32_t n_eps, int64_t B,
+                      float beta, float lamb, float margin,
+                      float* per_jet_out, double* sums_acc, void* stream);
+
+/* ---- model call surface: vae.encoder(X) / vae(X) (models.py:30-36,62-69) ------------------ */
+OEVAE_API int oevae_encode(oevae_t h, const float* x, int64_t N, const float* eps,
+                 float* mu, float* log_var, float* z, void* stream);
+
+/* ---- anomaly scoring: model.predict x n_iter (vae.py:163-166) + loss_function MSE/MAE/KLD/JSD
+ * (utils.py:346-375) + latent_loss (utils.py:378-386) + filtering flag (utils.py:532-538), one pass.
+ * Outputs are nullable [N] (xhat: nullable [N,D]).  eps: nullable [n_iter,N,L] (EXTERNAL mode). */
+OEVAE_API int oevae_score(oevae_t h, const float* x, int64_t N, int32_t n_iter, const float* eps,
+                float* mse, float* mae, float* kld, float* jsd, float* latent,
+                uint8_t* finite, float* xhat, void* stream);
+
+/* ---- handle-free kernels ---------------------------------------------------------------- */
+/* jets_sorting (utils.py:564-571) + load_data slice/pad/n_dims (utils.py:89-97,115-119) + get_4v
+ * (utils.py:300-308) + affine scaler apply (utils.py:406-417).  raw_dtype: 0 fp32, 1 fp16.
+ * sort: 1 = pT-sort first (jets_sorting); 0 = keep the stored order (get_4v on sorted jets).
+ * raw [N,4*n_raw] (E,px,py,pz); x_out [N,n_dims*n_const]; pt_out, m_out nullable [N];
+ * center/scale nullable double[n_dims*n_const]: fp32(fp32(x-center)/scale), evaluated in fp64 like sklearn's
+ * in-place transform of a float32 array (RobustScaler keeps float64 center_/scale_). */
+OEVAE_API int oevae_preprocess(const void* raw, int32_t raw_dtype, int64_t N, int32_t n_raw, int32_t n_const,
+                     int32_t n_dims, const double* center, const double* scale, int32_t sort,
+                     float* x_out, float* pt_out, float* m_out, int32_t device, void* stream);
+
+/* apply_scaling for affine scalers (utils.py:406-417) on an already sliced [N,D] array; y may alias x */
+OEVAE_API int oevae_affine(const float* x, float* y, int64_t N, int32_t D, const double* center, const double* scale,
+                 int32_t device, void* stream);
+
+/* loss_function (utils.py:346-375) between two given arrays P, Q [N,D]; every output nullable [N]:
+ * MSE, MAE, MARE, KLD, JSD, X-S */
+OEVAE_API int oevae_pair_metrics(const float* P, const float* Q, int64_t N, int32_t D, float* mse, float* mae, float* mare,
+                       float* kld, float* jsd, float* xs, int32_t device, void* stream);
+
+/* loss_mapping global predicates (plots.py:15-20): minmax_out double[3] = {min, max, #NaN} over
+ * rows with keep[i] (keep nullable); the caller initialises it to {+inf, -inf, 0} */
+OEVAE_API int oevae_minmax(const float* v, const uint8_t* keep, int64_t N, double* minmax_out, int32_t device, void* stream);
+/* loss_mapping elementwise branch (0..4) applied in place */
+OEVAE_API int oevae_loss_map(float* v, int64_t N, int32_t branch, int32_t device, void* stream);
+
+/* make_cut mask (plots.py:259) + per-class histogram of plot_distributions (plots.py:697-715):
+ * class 0: JZW == -1, class 1: JZW >= 0.  A jet enters iff keep[i] (nullable) and score[i] > cut
+ * (score nullable => no cut).  edges: double[n_edges] (np.histogram semantics: half-open bins, last bin
+ * closed).  counts int64 [2,n_edges-1] and wsums double [2,n_edges-1] are ADDED to. */
+OEVAE_API int oevae_hist(const float* var, const float* w, const float* jzw, const float* score, const uint8_t* keep,
+               int64_t N, float cut, const double* edges, int32_t n_edges,
+               int64_t* counts, double* wsums, int32_t device, void* stream);
+
+/* number of kernels this library has launched since load (bench.py "gpu_launches") */
+OEVAE_API int64_t oevae_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
