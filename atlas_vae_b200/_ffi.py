@@ -55,6 +55,8 @@ SIGNATURES = {
     'oevae_loss_map': (C.c_int, [_vp, _i64, _i32, _i32, _vp]),
     'oevae_hist': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _i32, _vp, _vp, _i32, _vp]),
     'oevae_launch_count': (_i64, []),
+    'oevae_profile_enable': (C.c_int, [_i32]),
+    'oevae_profile_report': (C.c_int, [C.c_char_p, _i32]),
 }
 
 
@@ -91,3 +93,18 @@ def ptr(t):
 
 def launch_count():
     return int(lib().oevae_launch_count())
+
+
+def profile(on):
+    lib().oevae_profile_enable(1 if on else 0)
+
+
+def profile_report():
+    """[(kernel name, launches, total ms)] of the launches made while profiling was on."""
+    buf = C.create_string_buffer(1 << 16)
+    n = lib().oevae_profile_report(buf, len(buf))
+    rows = []
+    for line in buf.value.decode().splitlines():
+        name, k, ms = line.rsplit(',', 2)
+        rows.append((name, int(k), float(ms)))
+    return rows

@@ -4,8 +4,11 @@
 #include "ref_kernels.cuh"
 #include "prep_hist_kernels.cuh"
 #include "engine.h"
+#include "prof.h"
 
+#include <algorithm>
 #include <atomic>
+#include <map>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -15,6 +18,7 @@
 using namespace oevae;
 
 std::atomic<long long> g_launches{0};
+namespace oevae { Profiler g_prof; }
 static thread_local std::string g_create_error;
 
 #define LAUNCHED() (g_launches.fetch_add(1, std::memory_order_relaxed))
@@ -111,7 +115,7 @@ int Engine::gemm_fwd(const float* A, int li, float* C, long rows, bool relu, cud
     g.bias = theta + l.b; g.relu = relu;
     g.t_base = 0; g.t_end = l.in;
     dim3 grid(cdiv(rows, 64), cdiv(l.out, 64), 1);
-    gemm64_kernel<true, false><<<grid, 256, 0, s>>>(g);
+    { PROF("gemm_fwd", s); gemm64_kernel<true, false><<<grid, 256, 0, s>>>(g); }
     CKL();
     return 0;
 }
@@ -126,7 +130,7 @@ int Engine::gemm_dx(const float* G, int li, float* C, long rows, bool accumulate
     g.accumulate = accumulate; g.mask = mask; g.ldmask = l.in;
     g.t_base = 0; g.t_end = l.out;
     dim3 grid(cdiv(rows, 64), cdiv(l.in, 64), 1);
-    gemm64_kernel<true, true><<<grid, 256, 0, s>>>(g);
+    { PROF("gemm_dx", s); gemm64_kernel<true, true><<<grid, 256, 0, s>>>(g); }
     CKL();
     return 0;
 }
@@ -143,7 +147,7 @@ int Engine::gemm_dw(const float* A, const float* G, int li, long rows, long B, i
     g.chunk = chunk_rows; g.slots_per_group = Sg; g.group_rows = (int)B;
     g.t_base = 0; g.t_end = (int)rows; g.slot_stride = Ppad;
     dim3 grid(cdiv(l.in + 1, 64), cdiv(l.out, 64), n_slots);
-    gemm64_kernel<false, false><<<grid, 256, 0, s>>>(g);
+    { PROF("gemm_dw", s); gemm64_kernel<false, false><<<grid, 256, 0, s>>>(g); }
     CKL();
     return 0;
 }
@@ -174,7 +178,7 @@ int Engine::forward(const Pass& p, cudaStream_t s) {
     la.seed = cfg.seed; la.row_offset = row_offset;
     la.step_base = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
     la.per_group_step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP);
-    latent_fwd_kernel<<<cdiv(Rt, 128), 128, 0, s>>>(la);
+    { PROF("latent_fwd", s); latent_fwd_kernel<<<cdiv(Rt, 128), 128, 0, s>>>(la); }
     CKL();
     ++calls;
     if (Rd == 0) return 0;
@@ -184,7 +188,7 @@ int Engine::forward(const Pass& p, cudaStream_t s) {
     TRY(gemm_fwd(d, 2 * n + 2, y, Rd, false, s));
     if (p.want_rec) {
         for (int g = 0; g < p.Rd; ++g) {
-            rec_fwd_kernel<<<cdiv(B * 32, 256), 256, 0, s>>>(p.x[g], y + (size_t)g * B * D, rec + (size_t)g * B, B, D, mse_type());
+            { PROF("rec_fwd", s); rec_fwd_kernel<<<cdiv(B * 32, 256), 256, 0, s>>>(p.x[g], y + (size_t)g * B * D, rec + (size_t)g * B, B, D, mse_type()); }
             CKL();
         }
     }
@@ -201,7 +205,7 @@ int Engine::backward(const Pass& p, cudaStream_t s) {
     float* g = nullptr; float* gn = nullptr;
     // decoder side
     for (int gi = 0; gi < p.Rd; ++gi) {
-        rec_bwd_kernel<<<cdiv(B * D, 256), 256, 0, s>>>(p.x[gi], y + (size_t)gi * B * D, g_rec + (size_t)gi * B, B, D, mse_type());
+        { PROF("rec_bwd", s); rec_bwd_kernel<<<cdiv(B * D, 256), 256, 0, s>>>(p.x[gi], y + (size_t)gi * B * D, g_rec + (size_t)gi * B, B, D, mse_type()); }
         CKL();
     }
     g = y;
@@ -214,7 +218,7 @@ int Engine::backward(const Pass& p, cudaStream_t s) {
         g = gn;
     }
     // g == g_z [Rd, L]
-    latent_bwd_kernel<<<cdiv(Rt * L, 256), 256, 0, s>>>(mu, lv, eps_buf, g, g_kld, g_mu, g_lv, Rt, Rd, L);
+    { PROF("latent_bwd", s); latent_bwd_kernel<<<cdiv(Rt * L, 256), 256, 0, s>>>(mu, lv, eps_buf, g, g_kld, g_mu, g_lv, Rt, Rd, L); }
     CKL();
     if (n == 0) {
         for (int gi = 0; gi < p.R; ++gi) {
@@ -280,7 +284,7 @@ int Engine::losses(const float* x_bkg, const float* w_bkg, const float* x_ood, c
     ca.per_jet = per_jet; ca.sums = sums;
     ca.B = B; ca.n_groups = p.R; ca.oe_type = cfg.oe_type; ca.have_ood = x_ood != nullptr;
     ca.beta = beta; ca.lamb = lamb; ca.margin = margin;
-    combine_kernel<<<cdiv(B, 256), 256, 0, s>>>(ca);
+    { PROF("combine", s); combine_kernel<<<cdiv(B, 256), 256, 0, s>>>(ca); }
     CKL();
     if (want_grad) TRY(backward(p, s));
     return 0;
@@ -297,7 +301,7 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
         double t = (double)step;
         a.alpha = (float)((double)lr * std::sqrt(1.0 - std::pow(0.999, t)) / (1.0 - std::pow(0.9, t)));
     }
-    adam_kernel<<<cdiv(P, 256), 256, 0, s>>>(a);
+    { PROF("adam", s); adam_kernel<<<cdiv(P, 256), 256, 0, s>>>(a); }
     CKL();
     return 0;
 }
@@ -319,7 +323,7 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
             int rc = forward(p, s);
             row_offset = save;
             if (rc) return rc;
-            if (n_iter > 1) { accum_clip_kernel<<<cdiv(nr * D, 256), 256, 0, s>>>(y, ysum, nr * D, it == 0); CKL(); }
+            if (n_iter > 1) { { PROF("accum_clip", s); accum_clip_kernel<<<cdiv(nr * D, 256), 256, 0, s>>>(y, ysum, nr * D, it == 0); } CKL(); }
         }
         bool need = o_mse || o_mae || o_kld || o_jsd || o_fin || o_xhat;
         if (need) {
@@ -327,10 +331,10 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
             mo.mse = o_mse ? o_mse + r0 : nullptr; mo.mae = o_mae ? o_mae + r0 : nullptr;
             mo.kld = o_kld ? o_kld + r0 : nullptr; mo.jsd = o_jsd ? o_jsd + r0 : nullptr;
             mo.finite = o_fin ? o_fin + r0 : nullptr; mo.xhat = o_xhat ? o_xhat + (size_t)r0 * D : nullptr;
-            score_metrics_kernel<<<cdiv(nr * 32, 256), 256, 0, s>>>(x + (size_t)r0 * D, n_iter > 1 ? ysum : y, 1.f / (float)n_iter, n_iter == 1, nr, D, mo);
+            { PROF("score_metrics", s); score_metrics_kernel<<<cdiv(nr * 32, 256), 256, 0, s>>>(x + (size_t)r0 * D, n_iter > 1 ? ysum : y, 1.f / (float)n_iter, n_iter == 1, nr, D, mo); }
             CKL();
         }
-        if (o_lat) { latent_out_kernel<<<cdiv(nr, 256), 256, 0, s>>>(kld, o_lat + r0, nr); CKL(); }
+        if (o_lat) { { PROF("latent_out", s); latent_out_kernel<<<cdiv(nr, 256), 256, 0, s>>>(kld, o_lat + r0, nr); } CKL(); }
     }
     return 0;
 }
@@ -370,7 +374,7 @@ int Engine::forward_encoder(const Pass& p, cudaStream_t s) {
     la.step_base = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
     la.per_group_step = 0;
     if (cfg.noise_mode == OEVAE_NOISE_EXTERNAL && !p.eps) { la.n_dec = 0; }
-    latent_fwd_kernel<<<cdiv(B, 128), 128, 0, s>>>(la);
+    { PROF("latent_fwd", s); latent_fwd_kernel<<<cdiv(B, 128), 128, 0, s>>>(la); }
     CKL();
     ++calls;
     return 0;
@@ -584,12 +588,38 @@ int oevae_hist(const float* var, const float* w, const float* jzw, const float* 
     if (smem > 200 * 1024) { g_create_error = "hist: too many bins"; return OEVAE_EUNSUPPORTED; }
     if (smem > 48 * 1024) { rc = free_fail(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "smem attr"); if (rc) return rc; }
     unsigned grid = std::min<unsigned>(cdiv(N, 256 * 8), 148 * 4);
-    hist_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(var, w, jzw, score, keep, N, cut, edges, n_edges,
-                                                           reinterpret_cast<unsigned long long*>(counts), wsums);
+    { PROF("hist", (cudaStream_t)stream); hist_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(var, w, jzw, score, keep, N, cut, edges, n_edges,
+                                                           reinterpret_cast<unsigned long long*>(counts), wsums); }
     LAUNCHED();
     return free_fail(cudaGetLastError(), "hist launch");
 }
 
 int64_t oevae_launch_count(void) { return g_launches.load(); }
+
+int oevae_profile_enable(int32_t on) {
+    if (on && !g_prof.on) g_prof.clear();
+    g_prof.on = on != 0;
+    return 0;
+}
+
+// "name,launches,total_ms\n" per kernel name, sorted by total time; returns the number of bytes written
+int oevae_profile_report(char* buf, int32_t cap) {
+    if (!buf || cap <= 0) return OEVAE_EINVAL;
+    cudaDeviceSynchronize();
+    std::map<std::string, std::pair<long, double>> agg;
+    for (auto& r : g_prof.recs) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, r.a, r.b) != cudaSuccess) continue;
+        auto& a = agg[r.name]; a.first++; a.second += ms;
+    }
+    std::vector<std::pair<std::string, std::pair<long, double>>> v(agg.begin(), agg.end());
+    std::sort(v.begin(), v.end(), [](auto& x, auto& y) { return x.second.second > y.second.second; });
+    std::string out;
+    for (auto& e : v) { char line[256]; snprintf(line, sizeof line, "%s,%ld,%.6f\n", e.first.c_str(), e.second.first, e.second.second); out += line; }
+    g_prof.clear();
+    int nb = (int)std::min<size_t>(out.size(), (size_t)cap - 1);
+    memcpy(buf, out.data(), nb); buf[nb] = 0;
+    return nb;
+}
 
 }  // extern "C"

@@ -1,0 +1,184 @@
+"""Hot-path parts of /root/reference/OE-VAE/utils.py on the device (same names and argument meaning).
+
+  jets_sorting    utils.py:564-571      get_4v          utils.py:300-308
+  preprocess      utils.py:89-97,115-119 (load_data's sort / keep n_const / zero-pad / n_dims slice)
+  fit_scaler      utils.py:389-405 (host sklearn fit, unchanged)   apply_scaler   utils.py:406-430
+  loss_function   utils.py:346-375      latent_loss     utils.py:378-386      filtering   utils.py:532-538
+  get_idx         utils.py:541-548
+HDF5 loading, OoD pairing and reweighting (utils.py:36-290) are outside the hot path.
+"""
+import pickle
+
+import numpy as np
+import torch
+
+from . import _ffi
+from ._ffi import check, ptr
+from .models import HostArray, _host
+
+
+def _dev(device=None):
+    if not torch.cuda.is_available():
+        raise _ffi.OevaeError('no CUDA device: the OE-VAE hot path has no CPU fallback')
+    return torch.device('cuda', torch.cuda.current_device() if device is None else device)
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _to_dev(a, dev, dtype=torch.float32):
+    if isinstance(a, torch.Tensor):
+        return a.to(dev, dtype).contiguous()
+    return torch.as_tensor(np.ascontiguousarray(a)).to(dev, dtype).contiguous()
+
+
+def _scaler_affine(scaler, D):
+    """(center, scale) float64 device-ready arrays of an affine sklearn scaler, or None if not affine."""
+    name = type(scaler).__name__
+    if name == 'MaxAbsScaler':
+        return None, np.asarray(scaler.scale_, np.float64)
+    if name == 'RobustScaler':
+        c = np.asarray(scaler.center_, np.float64) if scaler.with_centering else None
+        s = np.asarray(scaler.scale_, np.float64) if scaler.with_scaling else np.ones(D)
+        return c, s
+    return None
+
+
+def preprocess_device(raw, n_const, n_dims=4, scaler=None, sort=True, device=None, want_4v=True):
+    """K0 on device tensors: raw [N, 4*n_raw] (fp32 or fp16; E,px,py,pz) -> (X [N,n_dims*n_const], pt, m)."""
+    dev = _dev(device)
+    if isinstance(raw, torch.Tensor):
+        raw_t = raw.to(dev).contiguous()
+    else:
+        raw_t = torch.as_tensor(np.ascontiguousarray(raw)).to(dev)
+    if raw_t.dtype == torch.float16:
+        code = 1
+    else:
+        raw_t = raw_t.to(torch.float32); code = 0
+    N, n_raw = raw_t.shape[0], raw_t.shape[1] // 4
+    D = n_dims * n_const
+    c_t = s_t = None
+    if scaler is not None:
+        aff = _scaler_affine(scaler, D)
+        if aff is None:
+            raise NotImplementedError('%s is not affine: apply it with sklearn on the host (SURVEY 8(f) f3)' % type(scaler).__name__)
+        c, s = aff
+        c_t = None if c is None else torch.as_tensor(c).to(dev)
+        s_t = torch.as_tensor(s).to(dev)
+    x = torch.empty((N, D), dtype=torch.float32, device=dev)
+    pt = torch.empty(N, dtype=torch.float32, device=dev) if want_4v else None
+    m = torch.empty(N, dtype=torch.float32, device=dev) if want_4v else None
+    check(_ffi.lib().oevae_preprocess(ptr(raw_t), code, N, n_raw, int(n_const), int(n_dims), ptr(c_t), ptr(s_t),
+                                      1 if sort else 0, ptr(x), ptr(pt), ptr(m), dev.index, _stream()))
+    return x, pt, m
+
+
+def jets_sorting(jets, idx=(0, None), return_dict=None):
+    """utils.py:564-571: constituents re-ordered by decreasing pT; same shape as the input, float32."""
+    jets = np.asarray(jets)[idx[0]:idx[1]]
+    x, _, _ = preprocess_device(jets, jets.shape[1] // 4, 4, None, True, want_4v=False)
+    out = _host(x)
+    if idx == (0, None): return out
+    return_dict[idx] = out
+
+
+def get_4v(sample, idx=(0, None), return_dict=None):
+    """utils.py:300-308: jet pt and mass from the 4-vector sum of the given constituents (stored order)."""
+    sample = np.asarray(sample)[idx[0]:idx[1]]
+    _, pt, m = preprocess_device(sample, sample.shape[1] // 4, 4, None, False)
+    out = {'pt_calo': _host(pt), 'm_calo': _host(m)}
+    if idx == (0, None): return out
+    return_dict[idx] = out
+
+
+def preprocess(raw, n_const, n_dims=4, scaler=None):
+    """load_data's constituent path (utils.py:89-97,115-119) + get_4v + affine scaler in one kernel.
+    Returns {'constituents', 'pt', 'm'} as host arrays."""
+    x, pt, m = preprocess_device(raw, n_const, n_dims, scaler, True)
+    return {'constituents': _host(x), 'pt': _host(pt), 'm': _host(m)}
+
+
+def fit_scaler(sample, n_dims, scaler_out, scaler_type='RobustScaler', reshape=False):
+    """utils.py:389-405.  The fit is a one-off host statistic (sklearn, as in the reference)."""
+    from sklearn import preprocessing
+    if reshape: sample = np.reshape(sample, (-1, n_dims))
+    if scaler_type == 'QuantileTransformer':
+        scaler = preprocessing.QuantileTransformer(output_distribution='normal', n_quantiles=10000, random_state=0)
+    elif scaler_type == 'PowerTransformer':
+        scaler = preprocessing.PowerTransformer()
+    elif scaler_type == 'RobustScaler':
+        scaler = preprocessing.RobustScaler()
+    elif scaler_type == 'MaxAbsScaler':
+        scaler = preprocessing.MaxAbsScaler()
+    else:
+        raise ValueError(scaler_type)
+    scaler.fit(sample)
+    if scaler_out:
+        pickle.dump(scaler, open(scaler_out, 'wb'))
+    return scaler
+
+
+def apply_scaler(sample, n_dims, scaler, tag='sample', reshape=False, verbose=False):
+    """utils.py:419-430.  Affine scalers (MaxAbs / Robust) run on the device; Quantile / Power transformers
+    are not on the device path yet and use sklearn's own transform on the host."""
+    if scaler is None: return sample
+    shape = np.shape(sample)
+    x2 = np.reshape(sample, (-1, n_dims)) if reshape else np.asarray(sample)
+    aff = _scaler_affine(scaler, x2.shape[1])
+    if aff is None:
+        return np.reshape(scaler.transform(x2), shape)
+    dev = _dev()
+    c, s = aff
+    x_t = _to_dev(x2, dev)
+    c_t = None if c is None else torch.as_tensor(c).to(dev)
+    s_t = torch.as_tensor(s).to(dev)
+    check(_ffi.lib().oevae_affine(ptr(x_t), ptr(x_t), x_t.shape[0], x_t.shape[1], ptr(c_t), ptr(s_t), dev.index, _stream()))
+    return _host(x_t).reshape(shape)
+
+
+_METRIC_SLOT = {'MSE': 0, 'MAE': 1, 'MARE': 2, 'KLD': 3, 'JSD': 4, 'X-S': 5}
+
+
+def loss_function(P, Q, n_dims, metric, X_losses=None, delta=1e-32, multiloss=True):
+    """utils.py:346-375: per-jet metric between X_true (P) and X_pred (Q), computed in float32 on the device."""
+    dev = _dev()
+    if metric in ('Inputs', 'Inputs_scaled'):
+        loss = _host(_to_dev(P, dev).mean(dim=1))
+    else:
+        if metric not in _METRIC_SLOT: raise ValueError(metric)
+        P_t, Q_t = _to_dev(P, dev), _to_dev(Q, dev)
+        out = torch.empty(P_t.shape[0], dtype=torch.float32, device=dev)
+        args = [None] * 6
+        args[_METRIC_SLOT[metric]] = ptr(out)
+        check(_ffi.lib().oevae_pair_metrics(ptr(P_t), ptr(Q_t), P_t.shape[0], P_t.shape[1], *args, dev.index, _stream()))
+        loss = _host(out)
+    if multiloss: X_losses[metric] = loss
+    else: return loss
+
+
+def latent_loss(X_true, model):
+    """utils.py:378-386: per-jet latent KLD, non-finite -> 0."""
+    out = model.dev.score(X_true, 1, None if model.dev.noise != 'external' else
+                          torch.zeros((len(X_true), model.dev.latent_dim), device=model.dev.device),
+                          metrics=('Latent',), want_finite=False)
+    return _host(out['Latent'])
+
+
+def filtering(y_true, X_true, X_pred, sample):
+    """utils.py:532-538: drop the rows whose prediction has a non-finite value."""
+    keep = np.all(np.isfinite(X_pred), axis=1)
+    if keep.all(): return y_true, X_true, X_pred, sample
+    for key in sample: sample[key] = sample[key][keep]
+    return y_true[keep], X_true[keep], X_pred[keep], sample
+
+
+def get_idx(max_val, n_bins=10, bin_size=None, min_val=0, integer=True, tuples=True):
+    """utils.py:541-548 (host helper: bin edges / index ranges)."""
+    if bin_size is None:
+        n_bins = max(1, min(max_val - min_val, n_bins))
+        bin_size = (max_val - min_val) // n_bins
+    idx_list = np.append(np.arange(min_val, max_val, bin_size), max_val)
+    if integer: idx_list = np.int_(idx_list)
+    if tuples: return list(zip(idx_list[:-1], idx_list[1:]))
+    return idx_list

@@ -1,0 +1,270 @@
+#!/usr/bin/env python
+"""bench.py -- OE-VAE training throughput (jets/s, fwd+bwd+Adam) on N B200s; BASELINE.json config 2.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--precision fp32|...]
+
+A step = one pass of the hot path (get_losses + gradient + clip + Adam, models.py:180-186) over one batch of
+5000 synthetic QCD jets (n_constituents=100 x 4-vectors, FC_layers [80,40,20,10]).  Prints ONE JSON line.
+  value     device-timed whole-job jets/s with the 1M-jet epoch resident in HBM (every step reads a different
+            batch of the 1.6 GB array: inputs larger than L2)
+  e2e       the same steps through the public host API: each step's batch is copied host->device from pinned
+            memory and its loss sums are read back device->host inside the timed region
+  roofline  dominant kernel (per-kernel CUDA-event pass), algorithmic bytes of SURVEY 8(d) vs MEASURED_PEAKS.json
+  cpu_baseline  the reference step restated op-for-op in torch-CPU eager fp32 (oracle/torch_twin.py), timed on
+            the host cores of this box on a bounded sample
+--impl reference times only that CPU restatement (TensorFlow 2.1 cannot be installed here).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FC, N_CONST, N_DIMS, BATCH, N_JETS = [80, 40, 20, 10], 100, 4, 5000, 1_000_000
+D = N_CONST * N_DIMS
+ALG_BYTES_PER_JET = D * 4 + 4                      # X row + weight (1604 B)
+BETA, LR = 1.0, 1e-3
+METRIC, UNIT = 'train jets/s (fwd+bwd+Adam)', 'jets/s'
+WORKLOAD = 'cfg2: OE-VAE train step, n_constituents=100 x 4-vectors (D=400), FC_layers [80,40,20,10], batch 5000, 1M synthetic QCD jets, beta=1, no OoD term'
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+        return float(p['hbm_gbs']), 'measured'
+    except Exception:
+        return 6650.0, 'fallback'
+
+
+class ClockSampler:
+    Q = 'clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+        try:
+            self.p = subprocess.Popen(['nvidia-smi', '-i', str(index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits', '-lms', '100'],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.p.terminate(); self.p.wait()
+        self.f.flush(); self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for line in self.f.read().splitlines():
+            c = [v.strip() for v in line.split(',')]
+            if len(c) < 6: continue
+            try: sm.append(float(c[0])); mx.append(float(c[1]))
+            except ValueError: continue
+            for nme, v in zip(names, c[2:6]):
+                if v.lower().startswith('active'): reasons.add(nme)
+        os.unlink(self.f.name)
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(mx) if mx else None, 'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def cpu_reference_steps(steps, warmup, B=BATCH, budget_s=60.0):
+    """The reference CPU path (oracle/torch_twin.py, kind='port'): returns (jets/s, cores, description)."""
+    import numpy as np
+    import torch
+    from oracle import torch_twin as T, vae_numpy as V
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    rng = np.random.default_rng(0)
+    vae = T.TorchVAE(V.init_params(FC, D, 0), FC, D, torch.float32)
+    n_b = 4
+    Xs = [torch.tensor(rng.normal(0, 0.3, (B, D)).astype(np.float32)) for _ in range(n_b)]
+    w = torch.ones(B); eps = torch.tensor(rng.normal(size=(B, FC[-1])).astype(np.float32))
+    dt = 0.0; done = 0
+    warmup = max(warmup, 5)                          # the first torch-CPU steps pay thread-pool / allocator start-up
+    for s in range(warmup + steps):
+        if dt > budget_s: break
+        X = Xs[s % n_b]
+        t0 = time.perf_counter()
+        # no OoD sample in config 2: the OE term is evaluated on the batch itself with lamb=0, as vae.py does when lamb==0
+        T.train_step(vae, X, w, X, w, eps, 'KLD', BETA, 0.0, 0.0, LR)
+        if s >= warmup: dt += time.perf_counter() - t0; done += 1
+    return done * B / dt, cores, dt, done
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    steps = args.steps
+    jps, cores, dt, steps = cpu_reference_steps(steps, args.warmup)
+    line = {'impl': 'reference', 'metric': METRIC, 'value': jps, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': steps, 'warmup': args.warmup,
+            'ms_per_step': 1e3 * dt / steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': WORKLOAD},
+            'cpu_baseline': {'value': jps, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                             'sample': '%d steps of %d jets: models.py:108-132,181-186 restated op-for-op in torch-CPU eager fp32 (TensorFlow 2.1 is not installable here)' % (steps, BATCH)},
+            'e2e': {'value': jps, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    print(json.dumps(line))
+
+
+def make_workload(device, n_jets, seed):
+    """Synthetic QCD jets -> K0 preprocessing (pT sort, keep 100 constituents, MaxAbs scaling) on the device."""
+    import torch
+    from atlas_vae_b200 import synthetic as S, utils as U
+    X = torch.empty((n_jets, D), dtype=torch.float32, device=device)
+    scaler = None
+    chunk = 250_000
+    for lo in range(0, n_jets, chunk):
+        n = min(chunk, n_jets - lo)
+        raw, _ = S.make_jets('QCD', n, N_CONST, seed=seed + lo, device=device)
+        if scaler is None:
+            x0, _, _ = U.preprocess_device(raw[:100_000], N_CONST, N_DIMS, None, True, want_4v=False)
+            scaler = S.MaxAbs(S.maxabs_scale(x0))
+        x, _, _ = U.preprocess_device(raw, N_CONST, N_DIMS, scaler, True, want_4v=False)
+        X[lo:lo + n] = x
+        del raw, x
+    return X
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as td
+    from atlas_vae_b200 import _ffi, dist as Dd
+    from atlas_vae_b200.engine import DeviceVAE
+    from atlas_vae_b200.models import init_params, _BatchStager
+    rank, world = Dd.init()
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm')
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    K, W = args.steps, max(args.warmup, 3)
+    n_jets = min(N_JETS, (K + W) * BATCH)
+    n_batches = n_jets // BATCH
+    X = make_workload(dev, n_jets, 1234 + 7919 * rank)            # weak scaling: every rank owns its own 1M-jet epoch
+    wts = torch.ones(n_jets, dtype=torch.float32, device=dev)
+    vae = DeviceVAE(FC, D, 'KLD', args.precision, 'fixed', 0, local, BATCH)
+    vae.set_params(init_params(FC, D, 0))
+    sums = torch.zeros(4, dtype=torch.float64, device=dev)
+    grad = torch.empty(vae.n_params, dtype=torch.float32, device=dev)
+
+    def step(i, x=None, w=None):
+        b = i % n_batches
+        xb = X[b * BATCH:(b + 1) * BATCH] if x is None else x
+        wb = wts[b * BATCH:(b + 1) * BATCH] if w is None else w
+        if world == 1:
+            vae.train_step(xb, wb, None, None, None, LR, BETA, 0., 0., None, sums)
+        else:                                                     # data parallel: SUM all-reduce of the flat gradient
+            vae.loss_and_grad(xb, wb, None, None, None, BETA, 0., 0., None, sums, grad)
+            td.all_reduce(grad, op=td.ReduceOp.SUM)
+            vae.apply_update(grad, LR)
+
+    def sync():
+        if world > 1: td.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1: return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        td.all_reduce(t, op=td.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident timing
+    for i in range(W): step(i)
+    sync()
+    clocks = ClockSampler(local) if rank == 0 else None
+    n0 = _ffi.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(W, W + K): step(i)
+    e1.record()
+    sync()
+    launches = _ffi.launch_count() - n0
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    clk = clocks.stop() if clocks else None
+    value = world * K * BATCH / (ms * 1e-3)
+    loss_mean = float(sums[3].item()) / ((K + W) * BATCH)
+
+    # ---- per-kernel pass (CUDA events around every launch) for the roofline leg
+    _ffi.profile(True)
+    kp = min(K, 50)
+    for i in range(kp): step(W + K + i)
+    torch.cuda.synchronize()
+    rows = _ffi.profile_report()
+    _ffi.profile(False)
+    tot = sum(r[2] for r in rows) or 1.0
+    kernels = [{'name': r[0], 'launches_per_step': r[1] / kp, 'us_per_launch': 1e3 * r[2] / r[1], 'share': r[2] / tot} for r in rows]
+    peak, peak_src = peaks()
+    top = kernels[0] if kernels else None
+    roof = None
+    if top:
+        # algorithmic bytes of one launch of the dominant kernel = (bytes/jet of SURVEY 8.0) x jets it processes,
+        # spread over its launches per step
+        alg = ALG_BYTES_PER_JET * BATCH / max(top['launches_per_step'], 1e-9)
+        ach = alg / (top['us_per_launch'] * 1e-6) / 1e9
+        roof = {'bound': 'hbm', 'kernel': top['name'], 'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak,
+                'traffic': None, 'peak_source': peak_src, 'alg_bytes_per_launch': alg, 'us_per_launch': top['us_per_launch'],
+                'share_of_step': top['share'],
+                'step': {'achieved': ALG_BYTES_PER_JET * BATCH / (ms * 1e-3 / K) / 1e9, 'frac': ALG_BYTES_PER_JET * BATCH / (ms * 1e-3 / K) / 1e9 / peak}}
+
+    # ---- end to end through the host API: pinned host arrays, H2D per step, D2H of the loss sums per step
+    n_e2e = min(n_batches, K)
+    Xh = X[:n_e2e * BATCH].cpu().numpy(); wh = np.ones(n_e2e * BATCH, np.float32)
+    stager = _BatchStager([Xh, wh], BATCH, dev)
+    res_host = torch.zeros((n_e2e, 4), dtype=torch.float64).pin_memory()
+    e2e_ms = None
+    for rep in range(2):                                          # first repetition warms the copy path
+        stager.h2d_bytes = 0
+        sums.zero_()
+        sync()
+        e0.record()
+        for b, (xb, wb) in stager:
+            step(b, xb, wb)
+            res_host[b].copy_(sums, non_blocking=True)
+        e1.record()
+        sync()
+        e2e_ms = max_over_ranks(e0.elapsed_time(e1))
+    h2d = stager.h2d_bytes / n_e2e
+    stager.close()
+    e2e_val = world * n_e2e * BATCH / (e2e_ms * 1e-3)
+
+    if rank != 0:
+        return
+    line = {'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': ms / K,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': {'fp32': 'f32', 'tf32': 'tf32', 'bf16': 'bf16', 'bf16x3': 'bf16x3'}[args.precision],
+            'data': 'synthetic', 'config': {'workload': WORKLOAD, 'global_batch': world * BATCH, 'parallelism': 'dp%d' % world,
+                                            'l2': 'inputs larger than L2 (each step reads a fresh 8 MB batch of a 1.6 GB resident epoch)',
+                                            'precision': args.precision, 'mean_train_loss': loss_mean},
+            'clocks': clk, 'gpu_launches': int(launches),
+            'e2e': {'value': e2e_val, 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': 32, 'ms_per_step': e2e_ms / n_e2e},
+            'roofline': roof, 'kernels': kernels[:8]}
+    if world == 1 and not args.no_cpu:
+        jps, cores, dt, done = cpu_reference_steps(args.cpu_steps, 5, budget_s=20.0)
+        line['cpu_baseline'] = {'value': jps, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                                'sample': '%d steps of %d jets (%.1f s): models.py:108-132,181-186 restated op-for-op in torch-CPU eager fp32' % (done, BATCH, dt)}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--warmup', type=int, default=10)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--precision', default='fp32', choices=['fp32', 'bf16x3', 'tf32', 'bf16'])
+    ap.add_argument('--cpu-steps', type=int, default=300)
+    ap.add_argument('--no-cpu', action='store_true')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

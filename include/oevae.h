@@ -165,6 +165,11 @@ OEVAE_API int oevae_hist(const float* var, const float* w, const float* jzw, con
 /* number of kernels this library has launched since load (bench.py "gpu_launches") */
 OEVAE_API int64_t oevae_launch_count(void);
 
+/* per-kernel CUDA-event timing for bench.py's roofline leg: enable, run steps, then read
+ * "name,launches,total_ms" lines (sorted by total time).  Adds two event records per launch while on. */
+OEVAE_API int oevae_profile_enable(int32_t on);
+OEVAE_API int oevae_profile_report(char* buf, int32_t cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,63 @@
+"""CPU tests of the host-side logic that mirrors the reference (no GPU needed)."""
+import json, os
+import numpy as np
+
+
+def test_model_checkpoint_matches_reference(golden_dir):
+    from atlas_vae_b200.models import model_checkpoint, Adam
+
+    class FakeVae:
+        def __init__(s): s.saved = 0
+        def save_weights(s, p): s.saved += 1
+    for case in json.load(open(os.path.join(golden_dir, 'ref_checkpoint.json'))):
+        opt, vae, count = Adam(case['lr0']), FakeVae(), 0
+        sink = open(os.devnull, 'w')
+        for ep, exp in zip(range(1, len(case['series'])), case['trace']):
+            opt, count = model_checkpoint(vae, opt, {'Train loss': case['series'][:ep + 1]}, 'x.h5', count, _out=sink)
+            assert [vae.saved, opt.learning_rate, -1 if count is None else count] == exp
+            if count is None: break
+
+
+def test_init_params_and_layout_match_oracle():
+    from atlas_vae_b200.models import init_params
+    from oracle import vae_numpy as V
+    for FC, D in [([80, 40, 20, 10], 400), ([16], 12), ([1024, 512, 256, 64], 400)]:
+        a = init_params(FC, D, 0)
+        assert a.dtype == np.float32 and np.array_equal(a, V.init_params(FC, D, 0))
+
+
+def test_cut_host_logic_matches_reference(golden_dir):
+    from atlas_vae_b200 import cuts as Cc, utils as U
+    g = np.load(os.path.join(golden_dir, 'ref_scoring.npz'))
+    rates = Cc.get_rates(g['roc_y'], g['roc_score'], g['roc_w'])
+    for a, b in zip(rates, (g['roc_fpr'], g['roc_tpr'], g['roc_thr'])):
+        np.testing.assert_array_equal(a, b)
+    thr, val = Cc.best_threshold(g['roc_y'], rates, g['roc_w'], 'gain')
+    assert thr == g['thr_gain'] and val == g['val_gain']
+    samp = {'weights': g['roc_w'], 'idx': np.arange(len(g['roc_y']))}
+    np.testing.assert_array_equal(Cc.make_cut(g['roc_y'], g['roc_score'], samp, rates, 'MAE', 'gain')['idx'], g['kept_gain'])
+    for tag, bs in [('m', 2.5), ('pt', 10)]:
+        np.testing.assert_array_equal(Cc.bin_edges(g['var_' + tag], bs), g['edges_' + tag])
+    np.testing.assert_array_equal(np.array(U.get_idx(1003, 7)), g['idx_tuples'])
+    for i, (lo, hi) in enumerate([(0.1, 0.9), (-0.8, -0.1), (0.0, 30.), (-30., 0.), (-5., 5.)]):
+        assert Cc.loss_mapping_branch(lo, hi) == i
+    assert Cc.loss_mapping_branch(0.1, 0.9, True) == 4
+
+
+def test_filtering_matches_reference(golden_dir):
+    from atlas_vae_b200 import utils as U
+    g = np.load(os.path.join(golden_dir, 'ref_scoring.npz'))
+    y, Xt, Xp, s = U.filtering(np.arange(len(g['P'])), g['P'].copy(), g['filt_bad'].copy(), {'m': np.arange(len(g['P']))})
+    np.testing.assert_array_equal(y, g['filt_kept'])
+    assert len(Xt) == len(Xp) == len(s['m']) == len(y)
+
+
+def test_synthetic_jets_are_deterministic():
+    from atlas_vae_b200 import synthetic as S
+    a, ja = S.make_jets('W', 300, 60, seed=3)
+    b, jb = S.make_jets('W', 300, 60, seed=3)
+    assert a.shape == (300, 240) and bool((a == b).all()) and float(ja[0]) == -1.0
+    v = a.view(300, 60, 4)
+    assert bool((v[:, :, 0] >= 0).all())
+    m2 = v[:, :, 0] ** 2 - (v[:, :, 1:] ** 2).sum(-1)
+    assert float(m2.abs().max()) < 1e-1 * float((v[:, :, 0] ** 2).max())          # massless constituents
