@@ -8,6 +8,7 @@
 
 namespace oevae {
 
+struct GemmArgs;
 constexpr int kMaxSlots = 48;          // split-K partial-gradient slots (3 passes x 16)
 
 struct Layer { int in, out; long w, b; };   // offsets of kernel [in,out] and bias [out] in the flat vector
@@ -51,6 +52,7 @@ struct Engine {
     int reserve(long rows);
     int mse_type() const { return cfg.oe_type == OEVAE_OE_MSE || cfg.oe_type == OEVAE_OE_MSE_MARGIN; }
 
+    int launch_gemm(const GemmArgs& g, int kind, int n_slots, cudaStream_t s);
     int gemm_fwd(const float* A, int li, float* C, long rows, bool relu, cudaStream_t s);
     int gemm_dx(const float* G, int li, float* C, long rows, bool accumulate, const float* mask, cudaStream_t s);
     int gemm_dw(const float* A, const float* G, int li, long rows, long B, int slot0, int n_slots, cudaStream_t s);

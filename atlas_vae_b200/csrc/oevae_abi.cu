@@ -3,6 +3,7 @@
 #include "common.cuh"
 #include "ref_kernels.cuh"
 #include "prep_hist_kernels.cuh"
+#include "umma_gemm.cuh"
 #include "engine.h"
 #include "prof.h"
 
@@ -48,6 +49,7 @@ int Engine::init(const oevae_config& c) {
     if (c.oe_type < 0 || c.oe_type > 4) return fail(OEVAE_EINVAL, "bad oe_type %d", c.oe_type);
     if (c.noise_mode < 0 || c.noise_mode > 2) return fail(OEVAE_EINVAL, "bad noise_mode %d", c.noise_mode);
     if (c.precision < 0 || c.precision > 3) return fail(OEVAE_EINVAL, "bad precision %d", c.precision);
+    if (c.precision == OEVAE_PREC_TF32) return fail(OEVAE_EUNSUPPORTED, "precision tf32 is not implemented yet (use fp32, bf16x3 or bf16)");
     D = c.input_dim; L = c.latent_dim; n = c.n_hidden;
     for (int k = 0; k < n; ++k) { if (c.hidden[k] <= 0) return fail(OEVAE_EINVAL, "bad hidden width"); hid.push_back(c.hidden[k]); }
     // Keras trainable_weights order (models.py:22-28,43-48)
@@ -106,6 +108,46 @@ int Engine::reserve(long rows) {
 }
 
 // ---------------------------------------------------------------------------------------------- GEMM launchers
+template <bool SPLIT>
+static int umma_smem_bytes(int BN) { return 2 * (128 * 128 + BN * 128) * (SPLIT ? 2 : 1) + 1024; }
+
+template <bool A_TC, bool B_TC, bool SPLIT>
+static cudaError_t umma_launch(const GemmArgs& g, int n_slots, cudaStream_t s) {
+    int BN = std::min(128, (g.Cn + 15) / 16 * 16);
+    int tmem_cols = 32; while (tmem_cols < BN) tmem_cols <<= 1;
+    int smem = umma_smem_bytes<SPLIT>(BN);
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(umma_gemm_kernel<A_TC, B_TC, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, umma_smem_bytes<SPLIT>(128));
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    dim3 grid(cdiv(g.R, 128), cdiv(g.Cn, BN), n_slots);
+    umma_gemm_kernel<A_TC, B_TC, SPLIT><<<grid, 256, smem, s>>>(g, BN, tmem_cols);
+    return cudaSuccess;
+}
+
+// kind: 0 forward (A t-contiguous, B c-contiguous), 1 dX (both t-contiguous), 2 dW (A r-contiguous, B c-contiguous)
+int Engine::launch_gemm(const GemmArgs& g, int kind, int n_slots, cudaStream_t s) {
+    static const char* names[3] = {"gemm_fwd", "gemm_dx", "gemm_dw"};
+    PROF(names[kind], s);
+    if (cfg.precision == OEVAE_PREC_FP32) {
+        dim3 grid(cdiv(g.R, 64), cdiv(g.Cn, 64), n_slots);
+        if (kind == 0) gemm64_kernel<true, false><<<grid, 256, 0, s>>>(g);
+        else if (kind == 1) gemm64_kernel<true, true><<<grid, 256, 0, s>>>(g);
+        else gemm64_kernel<false, false><<<grid, 256, 0, s>>>(g);
+    } else {
+        const bool split = cfg.precision == OEVAE_PREC_BF16X3;
+        cudaError_t e;
+        if (kind == 0) e = split ? umma_launch<true, false, true>(g, n_slots, s) : umma_launch<true, false, false>(g, n_slots, s);
+        else if (kind == 1) e = split ? umma_launch<true, true, true>(g, n_slots, s) : umma_launch<true, true, false>(g, n_slots, s);
+        else e = split ? umma_launch<false, false, true>(g, n_slots, s) : umma_launch<false, false, false>(g, n_slots, s);
+        CK(e);
+    }
+    CKL();
+    return 0;
+}
+
 int Engine::gemm_fwd(const float* A, int li, float* C, long rows, bool relu, cudaStream_t s) {
     const Layer& l = layers[li];
     GemmArgs g{};
@@ -114,10 +156,7 @@ int Engine::gemm_fwd(const float* A, int li, float* C, long rows, bool relu, cud
     g.R = (int)rows; g.Cn = l.out; g.ldc = l.out;
     g.bias = theta + l.b; g.relu = relu;
     g.t_base = 0; g.t_end = l.in;
-    dim3 grid(cdiv(rows, 64), cdiv(l.out, 64), 1);
-    { PROF("gemm_fwd", s); gemm64_kernel<true, false><<<grid, 256, 0, s>>>(g); }
-    CKL();
-    return 0;
+    return launch_gemm(g, 0, 1, s);
 }
 
 // C[rows, in] = G[rows, out] . W^T  (+= C) (* mask>0)
@@ -129,10 +168,7 @@ int Engine::gemm_dx(const float* G, int li, float* C, long rows, bool accumulate
     g.R = (int)rows; g.Cn = l.in; g.ldc = l.in;
     g.accumulate = accumulate; g.mask = mask; g.ldmask = l.in;
     g.t_base = 0; g.t_end = l.out;
-    dim3 grid(cdiv(rows, 64), cdiv(l.in, 64), 1);
-    { PROF("gemm_dx", s); gemm64_kernel<true, true><<<grid, 256, 0, s>>>(g); }
-    CKL();
-    return 0;
+    return launch_gemm(g, 1, 1, s);
 }
 
 // parts[slot][w_off + i*out + j] = sum_{rows of slot} [A,1][row][i] * G[row][j]
@@ -146,10 +182,7 @@ int Engine::gemm_dw(const float* A, const float* G, int li, long rows, long B, i
     g.ones_row = 1;
     g.chunk = chunk_rows; g.slots_per_group = Sg; g.group_rows = (int)B;
     g.t_base = 0; g.t_end = (int)rows; g.slot_stride = Ppad;
-    dim3 grid(cdiv(l.in + 1, 64), cdiv(l.out, 64), n_slots);
-    { PROF("gemm_dw", s); gemm64_kernel<false, false><<<grid, 256, 0, s>>>(g); }
-    CKL();
-    return 0;
+    return launch_gemm(g, 2, n_slots, s);
 }
 
 // ---------------------------------------------------------------------------------------------- forward
