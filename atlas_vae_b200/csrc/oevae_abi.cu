@@ -4,6 +4,7 @@
 #include "ref_kernels.cuh"
 #include "prep_hist_kernels.cuh"
 #include "umma_gemm.cuh"
+#include "umma_probe.cuh"
 #include "engine.h"
 #include "prof.h"
 
@@ -625,6 +626,30 @@ int oevae_hist(const float* var, const float* w, const float* jzw, const float* 
                                                            reinterpret_cast<unsigned long long*>(counts), wsums); }
     LAUNCHED();
     return free_fail(cudaGetLastError(), "hist launch");
+}
+
+// Layered-GEMM building block exposed for kernel-level tests: C[R,Cn] = sum_t A[r*sAr + t*sAt] * B[t*sBt + c*sBc]
+// kind 0/1/2 selects the staging variant used by forward / dX / dW (see Engine::launch_gemm).
+int oevae_gemm(oevae_t h, int32_t kind, const float* A, int64_t sAr, int64_t sAt, const float* B, int64_t sBt, int64_t sBc,
+               float* C, int32_t ldc, int32_t R, int32_t Cn, int32_t T, const float* bias, int32_t relu, void* stream) {
+    H(h);
+    if (kind < 0 || kind > 2 || !A || !B || !C || R <= 0 || Cn <= 0 || T < 0) return e->fail(OEVAE_EINVAL, "gemm: bad arguments");
+    if ((kind != 2 && sAt != 1) || (kind == 2 && sAr != 1) || (kind == 1 && sBt != 1) || (kind != 1 && sBc != 1))
+        return e->fail(OEVAE_EINVAL, "gemm: strides do not match kind %d", kind);
+    GemmArgs g{};
+    g.A = A; g.B = B; g.C = C; g.sAr = sAr; g.sAt = sAt; g.sBt = sBt; g.sBc = sBc;
+    g.R = R; g.Cn = Cn; g.ldc = ldc; g.bias = bias; g.relu = relu; g.t_base = 0; g.t_end = T;
+    return e->launch_gemm(g, kind, 1, (cudaStream_t)stream);
+}
+
+int oevae_probe_mn(const float* A, const float* B, int32_t K, int32_t M, int32_t N, float* raw_out, int32_t device, void* stream) {
+    if (!A || !B || !raw_out || K <= 0 || K > 128 || K % 16 || (M != 64 && M != 128) || N % 16 || N < 16 || N > 128) { g_create_error = "probe: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    int smem = 4 * 128 * 128 + 1024;
+    rc = free_fail(cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem), "smem attr"); if (rc) return rc;
+    umma_probe_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(A, B, K, M, N, raw_out);
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "probe launch");
 }
 
 int64_t oevae_launch_count(void) { return g_launches.load(); }

@@ -145,6 +145,18 @@ class DeviceVAE:
                                          beta, lamb, margin, ptr(per_jet), ptr(sums), _stream()), self.h)
         return per_jet
 
+    def gemm(self, kind, A, B, bias=None, relu=False):
+        """Kernel-level access to the layered contraction (tests): kind 0: A[R,T] @ B[T,C]; 1: A[R,T] @ B[C,T]^T;
+        2: A[T,R]^T @ B[T,C]."""
+        A, B, bias = self._f32(A), self._f32(B), self._f32(bias)
+        if kind == 0: R, T, Cn = A.shape[0], A.shape[1], B.shape[1]; st = (A.shape[1], 1, B.shape[1], 1)
+        elif kind == 1: R, T, Cn = A.shape[0], A.shape[1], B.shape[0]; st = (A.shape[1], 1, 1, B.shape[1])
+        else: R, T, Cn = A.shape[1], A.shape[0], B.shape[1]; st = (1, A.shape[1], B.shape[1], 1)
+        out = torch.empty((R, Cn), dtype=torch.float32, device=self.device)
+        check(self.lib.oevae_gemm(self.h, kind, ptr(A), st[0], st[1], ptr(B), st[2], st[3], ptr(out), Cn, R, Cn, T,
+                                  ptr(bias), 1 if relu else 0, _stream()), self.h)
+        return out
+
     def encode(self, x, eps=None):
         x = self._f32(x); N = x.shape[0]
         eps = self._f32(eps)

@@ -162,6 +162,16 @@ OEVAE_API int oevae_hist(const float* var, const float* w, const float* jzw, con
                int64_t N, float cut, const double* edges, int32_t n_edges,
                int64_t* counts, double* wsums, int32_t device, void* stream);
 
+/* The layered Dense contraction on its own (kernel-level tests): C[R,Cn] = sum_t A[r*sAr+t*sAt] * B[t*sBt+c*sBc]
+ * (+bias[c], ReLU) in the handle's precision.  kind 0: forward (sAt==1, sBc==1), 1: dX (sAt==1, sBt==1),
+ * 2: dW (sAr==1, sBc==1) -- the three operand orientations of models.py:31-34 and its tape gradient. */
+OEVAE_API int oevae_gemm(oevae_t h, int32_t kind, const float* A, int64_t sAr, int64_t sAt, const float* B, int64_t sBt, int64_t sBc,
+               float* C, int32_t ldc, int32_t R, int32_t Cn, int32_t T, const float* bias, int32_t relu, void* stream);
+
+/* Hardware-layout probe (tests): C = A^T B through MN-major SWIZZLE_128B descriptors, A [K,M], B [K,N]; dumps the
+ * raw TMEM accumulator [128 lanes, N] so that the M=64 / M=128 lane mapping can be asserted. */
+OEVAE_API int oevae_probe_mn(const float* A, const float* B, int32_t K, int32_t M, int32_t N, float* raw_out, int32_t device, void* stream);
+
 /* number of kernels this library has launched since load (bench.py "gpu_launches") */
 OEVAE_API int64_t oevae_launch_count(void);
 
