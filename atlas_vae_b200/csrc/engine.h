@@ -9,6 +9,7 @@
 namespace oevae {
 
 struct GemmArgs;
+struct FusedState;
 constexpr int kMaxSlots = 48;          // split-K partial-gradient slots (3 passes x 16)
 
 struct Layer { int in, out; long w, b; };   // offsets of kernel [in,out] and bias [out] in the flat vector
@@ -44,6 +45,7 @@ struct Engine {
     float *y = nullptr, *ysum = nullptr, *gA = nullptr, *gB = nullptr;
     float *kld = nullptr, *rec = nullptr, *g_rec = nullptr, *g_kld = nullptr;
     int Sg = 1, chunk_rows = 0, n_slots_used = 0;
+    FusedState* fz = nullptr;      // fused tcgen05 training kernel (bf16x3, small nets); null when not applicable
 
     ~Engine();
     int fail(int code, const char* fmt, ...);
@@ -63,6 +65,9 @@ struct Engine {
     int backward(const Pass& p, cudaStream_t s);
     int losses(const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood, const float* eps, int n_eps,
                long B, float beta, float lamb, float margin, float* per_jet, double* sums, bool want_grad, cudaStream_t s);
+    int fused_init();
+    int fused_losses(const float* x, const float* w, const float* eps, long B, float beta, float* per_jet, double* sums,
+                     bool want_grad, cudaStream_t s);
     int reduce_and_update(float* grad_out, const float* grad_in, bool apply, float lr, cudaStream_t s);
     int score(const float* x, long N, int n_iter, const float* eps, float* o_mse, float* o_mae, float* o_kld, float* o_jsd,
               float* o_lat, unsigned char* o_fin, float* o_xhat, cudaStream_t s);

@@ -7,6 +7,8 @@
 #include "umma_probe.cuh"
 #include "engine.h"
 #include "prof.h"
+#include "fused_host.cuh"
+#include <cstdlib>
 
 #include <algorithm>
 #include <atomic>
@@ -73,13 +75,78 @@ int Engine::init(const oevae_config& c) {
     m = theta + P; v = m + P;
     CK(cudaMemset(theta, 0, 3 * P * sizeof(float)));
     step = 0; calls = 0;
+    Ppad = (P + 3) / 4 * 4;
+    TRY(fused_init());
     if (c.max_batch > 0) TRY(reserve(c.max_batch * 2));
     return 0;
+}
+
+namespace oevae {
+struct FusedState {
+    FPlan plan{};
+    unsigned char* wimg = nullptr; int* pos = nullptr; float* parts = nullptr;
+    uint32_t img_bytes = 0;
+    bool img_dirty = true, last_fused = false;
+    int last_grid = 0;
+};
 }
 
 Engine::~Engine() {
     if (theta) cudaFree(theta);
     if (arena) cudaFree(arena);
+    if (fz) { if (fz->wimg) cudaFree(fz->wimg); if (fz->pos) cudaFree(fz->pos); if (fz->parts) cudaFree(fz->parts); delete fz; }
+}
+
+// fused kernel set-up: only for bf16x3 and nets that fit one CTA (see build_fused_plan); otherwise layered path
+int Engine::fused_init() {
+    if (cfg.precision != OEVAE_PREC_BF16X3) return 0;
+    const char* env = getenv("OEVAE_FUSED");
+    if (env && atoi(env) == 0) return 0;
+    const char* ert = getenv("OEVAE_FUSED_RT");
+    FusedState* f = new FusedState();
+    std::vector<int> pos;
+    bool ok = false;
+    const int cand[4] = {64, 48, 32, 16};
+    for (int i = 0; i < 4 && !ok; ++i) {
+        if (ert && atoi(ert) != cand[i]) continue;
+        ok = build_fused_plan(*this, cand[i], f->plan, pos);
+    }
+    if (!ok) { delete f; return 0; }
+    const FPlan& P_ = f->plan;
+    f->img_bytes = P_.wop_off[P_.n_wop - 1] + P_.wop_bytes[P_.n_wop - 1];
+    CK(cudaMalloc(&f->wimg, f->img_bytes));
+    CK(cudaMemset(f->wimg, 0, f->img_bytes));
+    CK(cudaMalloc(&f->pos, pos.size() * sizeof(int)));
+    CK(cudaMemcpy(f->pos, pos.data(), pos.size() * sizeof(int), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&f->parts, (size_t)n_sm * Ppad * sizeof(float)));
+    CK(cudaFuncSetAttribute(fused_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_.smem_bytes));
+    fz = f;
+    return 0;
+}
+
+int Engine::fused_losses(const float* x, const float* w, const float* eps, long B, float beta, float* per_jet, double* sums,
+                         bool want_grad, cudaStream_t s) {
+    FusedState& f = *fz;
+    const FPlan& P_ = f.plan;
+    if (f.img_dirty) {                                      // weights were set from the host: rebuild the bf16 images
+        AdamImgArgs ai{};
+        ai.theta = theta; ai.n = P; ai.wimg = f.wimg; ai.pos = f.pos;
+        { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, 256), 256, 0, s>>>(ai); }
+        CKL();
+        f.img_dirty = false;
+    }
+    FusedArgs a{};
+    a.x = x; a.w = w; a.eps = eps; a.wimg = f.wimg; a.parts = f.parts;
+    a.per_jet = per_jet; a.sums = sums; a.kld_out = nullptr;
+    a.B = B; a.n_tiles = (int)((B + P_.Rt - 1) / P_.Rt); a.train = want_grad; a.mse = mse_type();
+    a.beta = beta; a.seed = cfg.seed; a.row_offset = row_offset;
+    a.step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
+    ++calls;
+    const int grid = std::min(a.n_tiles, n_sm);
+    { PROF(want_grad ? "fused_train" : "fused_eval", s); fused_train_kernel<<<grid, 256, P_.smem_bytes, s>>>(P_, a); }
+    CKL();
+    if (want_grad) { f.last_fused = true; f.last_grid = grid; }
+    return 0;
 }
 
 // workspace for `rows` total rows (all passes of one call)
@@ -309,6 +376,13 @@ int Engine::losses(const float* x_bkg, const float* w_bkg, const float* x_ood, c
                    long B, float beta, float lamb, float margin, float* per_jet, double* sums, bool want_grad, cudaStream_t s) {
     if (!w_bkg) return fail(OEVAE_EINVAL, "w_bkg is null");
     if ((x_ood == nullptr) != (w_ood == nullptr)) return fail(OEVAE_EINVAL, "x_ood and w_ood must be given together");
+    if (fz && !x_ood && B > 0 && x_bkg) {
+        if (cfg.noise_mode == OEVAE_NOISE_EXTERNAL) {
+            if (!eps) return fail(OEVAE_EINVAL, "noise_mode EXTERNAL needs eps");
+        } else if (eps) return fail(OEVAE_EINVAL, "eps given but noise_mode is not EXTERNAL");
+        return fused_losses(x_bkg, w_bkg, eps, B, beta, per_jet, sums, want_grad, s);
+    }
+    if (fz && want_grad) fz->last_fused = false;
     Pass p;
     TRY(plan(p, x_bkg, x_ood, eps, n_eps, B));
     TRY(forward(p, s));
@@ -334,6 +408,19 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
         ++step;
         double t = (double)step;
         a.alpha = (float)((double)lr * std::sqrt(1.0 - std::pow(0.999, t)) / (1.0 - std::pow(0.9, t)));
+    }
+    if (fz) {                                               // same update + refresh of the bf16 weight images
+        AdamImgArgs ai{};
+        if (grad_in) ai.grad_in = grad_in;
+        else if (fz->last_fused) { ai.parts = fz->parts; ai.n_parts = fz->last_grid; ai.part_stride = Ppad; ai.grad_out = grad_out; }
+        else { ai.parts = parts; ai.n_parts = n_slots_used; ai.part_stride = Ppad; ai.grad_out = grad_out; }
+        ai.theta = theta; ai.m = m; ai.v = v; ai.n = P;
+        ai.alpha = a.alpha; ai.b1 = a.b1; ai.b2 = a.b2; ai.eps = a.eps; ai.apply = apply;
+        ai.wimg = fz->wimg; ai.pos = fz->pos;
+        { PROF("adam", s); adam_img_kernel<<<cdiv(P, 256), 256, 0, s>>>(ai); }
+        CKL();
+        if (apply) fz->img_dirty = false;
+        return 0;
     }
     { PROF("adam", s); adam_kernel<<<cdiv(P, 256), 256, 0, s>>>(a); }
     CKL();
@@ -462,6 +549,7 @@ int oevae_param_layout(oevae_t h, int64_t* offsets, int32_t* dims_in, int32_t* d
 int oevae_set_params_host(oevae_t h, const float* flat, int64_t nn) {
     H(h);
     if (!flat || nn != e->P) return e->fail(OEVAE_EINVAL, "set_params: expected %ld floats, got %ld", e->P, (long)nn);
+    if (e->fz) e->fz->img_dirty = true;
     return e->cuda_check(cudaMemcpy(e->theta, flat, nn * 4, cudaMemcpyHostToDevice), "set_params");
 }
 int oevae_get_params_host(oevae_t h, float* flat, int64_t nn) {
