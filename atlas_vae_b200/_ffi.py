@@ -56,6 +56,9 @@ SIGNATURES = {
     'oevae_hist': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _i32, _vp, _vp, _i32, _vp]),
     'oevae_gemm': (C.c_int, [_vp, _i32, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp]),
     'oevae_probe_mn': (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _i32, _vp]),
+    'oevae_probe_latency': (C.c_int, [_i32, _i32, C.POINTER(_i64), _i32]),
+    'oevae_probe_issue': (C.c_int, [_i32, _i32, _i32, _i32, _i32, C.POINTER(_i64), _i32]),
+    'oevae_probe_bulk': (C.c_int, [_i32, _i32, _i32, _i32, C.POINTER(_i64), _i32]),
     'oevae_launch_count': (_i64, []),
     'oevae_profile_enable': (C.c_int, [_i32]),
     'oevae_profile_report': (C.c_int, [C.c_char_p, _i32]),

@@ -102,6 +102,7 @@ struct FusedArgs {
     long B; int n_tiles; int train; int mse;
     float beta;
     unsigned long long seed, row_offset; unsigned int step;
+    long long* dbg;                                         // optional: clock64() stamps of CTA 0 (debug)
 };
 
 __global__ void __launch_bounds__(256, 1) fused_train_kernel(const __grid_constant__ FPlan P, FusedArgs a) {
@@ -150,6 +151,9 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const __grid_consta
     };
     if (tid == 0 && (int)blockIdx.x < a.n_tiles) w_issue(0, 0);
 
+    int n_dbg = 0;
+    auto stamp = [&]() { if (a.dbg && blockIdx.x == 0 && tid == 0 && n_dbg < 255) a.dbg[1 + n_dbg++] = clock64(); };
+    stamp();
     int tile_iter = 0;
     for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_iter) {
         const bool more_tiles = tile + (int)gridDim.x < a.n_tiles;
@@ -269,8 +273,10 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const __grid_consta
                 ++kop; ++gk;
             }
             wait_x((P.nX - 1) & 1);
+            stamp();
             epi_act(0);
             publish();
+            stamp();
         }
         // =========================================================== forward chain: layers 1 .. nl-2
         for (int f = 1; f <= nl - 2; ++f) {
@@ -326,6 +332,7 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const __grid_consta
                 kld_r = -(kl / (float)L) / 2.f;
             }
             publish();
+            stamp();
         }
         // =========================================================== output layer in 64-column chunks
         {
@@ -339,12 +346,14 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const __grid_consta
                 unsigned char* wb = nullptr;
                 if (tid == 0) {
                     wb = w_begin(kop, more_tiles);
+                    stamp();
                     tc_fence_after();
                     issue_kk(tm + ACC_Y, smem_u32(tile_hi(f - 1)), a_nblk * blk, blk, smem_u32(wb), fwd_lo, 64 * 128, ly.kb_fwd,
                              (lastk + 15) >> 4, idesc_bf16_major(64, 64, 0, 0), false);
                     mma_commit(&mma_bar);
                 }
                 wait_mma();
+                stamp();
                 // reconstruction loss (models.py:66,72-78) and its gradient through clip_values
                 unsigned char* gh = wide_hi(c & 1); unsigned char* gl = gh + blk;
                 for (int gq = 0; gq < 2; ++gq) {
@@ -379,7 +388,9 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const __grid_consta
                         if (a.train) store16(gh, gl, blk, row, 16 * g, v);
                     }
                 }
+                stamp();
                 publish();
+                stamp();
                 if (a.train) {
                     if (tid == 0) {
                         tc_fence_after();
@@ -393,12 +404,16 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const __grid_consta
                         mma_commit(&mma_bar);
                     }
                     wait_mma();
+                    stamp();
                     epi_dw(f, a_nblk >= 2 ? 128 : 64, 0, 64 * c, min(64, D - 64 * c));
+                    stamp();
                     publish();
                 }
                 ++kop; ++gk;
+                stamp();
             }
             if (a.train) { epi_grad(f); publish(); }
+            stamp();
         }
         // =========================================================== backward chain: layers nl-2 .. 1
         if (a.train) {
@@ -448,6 +463,7 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const __grid_consta
                     }
                 }
                 publish();
+                stamp();
             }
             // ======================================================= layer 0: dW = [X,1]^T g_0, X re-streamed (L2)
             {
@@ -467,6 +483,7 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const __grid_consta
                 }
             }
         }
+        stamp();
         // =========================================================== per-jet losses (models.py:123-132) and batch sums
         if (row_thr) s_rec[half * Rt + row] = rec_acc;
         __syncthreads();
@@ -488,6 +505,8 @@ __global__ void __launch_bounds__(256, 1) fused_train_kernel(const __grid_consta
         }
         __syncthreads();
     }
+    stamp();
+    if (a.dbg && blockIdx.x == 0 && tid == 0) a.dbg[0] = n_dbg;
     tc_fence_before();
     __syncthreads();
     if (warp == 0) tmem_dealloc(tm, 512);

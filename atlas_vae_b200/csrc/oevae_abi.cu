@@ -143,9 +143,19 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
     a.step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
     ++calls;
     const int grid = std::min(a.n_tiles, n_sm);
+    static long long* dbg_buf = nullptr;
+    const bool dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
+    if (dbg && !dbg_buf) cudaMalloc(&dbg_buf, 256 * sizeof(long long));
+    a.dbg = dbg ? dbg_buf : nullptr;
     { PROF(want_grad ? "fused_train" : "fused_eval", s); fused_train_kernel<<<grid, 256, P_.smem_bytes, s>>>(P_, a); }
     CKL();
     if (want_grad) { f.last_fused = true; f.last_grid = grid; }
+    if (dbg) {
+        long long h[256]; cudaStreamSynchronize(s); cudaMemcpy(h, dbg_buf, sizeof h, cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[fused dbg] grid=%d Rt=%d stamps(cycles since start):", grid, P_.Rt);
+        for (int i = 2; i <= (int)h[0]; ++i) fprintf(stderr, " %lld", h[i] - h[1]);
+        fprintf(stderr, "\n");
+    }
     return 0;
 }
 
@@ -738,6 +748,48 @@ int oevae_probe_mn(const float* A, const float* B, int32_t K, int32_t M, int32_t
     umma_probe_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(A, B, K, M, N, raw_out);
     LAUNCHED();
     return free_fail(cudaGetLastError(), "probe launch");
+}
+
+int oevae_probe_latency(int32_t M, int32_t N, int64_t* out_host6, int32_t device) {
+    if (!out_host6 || (M != 64 && M != 128) || N % 16 || N < 16 || N > 256) { g_create_error = "probe_latency: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    long long* d = nullptr;
+    rc = free_fail(cudaMalloc(&d, 6 * sizeof(long long)), "cudaMalloc"); if (rc) return rc;
+    int smem = 2 * 128 * 128 + 1024;
+    umma_latency_kernel<<<1, 128, smem>>>(M, N, d);
+    LAUNCHED();
+    rc = free_fail(cudaMemcpy(out_host6, d, 6 * sizeof(long long), cudaMemcpyDeviceToHost), "probe_latency");
+    cudaFree(d);
+    return rc;
+}
+
+int oevae_probe_issue(int32_t M, int32_t N, int32_t nw, int32_t nm, int32_t mode, int64_t* out_host1, int32_t device) {
+    if (!out_host1 || (M != 64 && M != 128) || N % 16 || N < 16 || N > 128 || nw < 1 || nw > 4 || nm < 1) { g_create_error = "probe_issue: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    long long* d = nullptr;
+    rc = free_fail(cudaMalloc(&d, sizeof(long long)), "cudaMalloc"); if (rc) return rc;
+    umma_issue_kernel<<<1, 128, 2 * 128 * 128 + 1024>>>(M, N, nw, nm, mode, d);
+    LAUNCHED();
+    rc = free_fail(cudaMemcpy(out_host1, d, sizeof(long long), cudaMemcpyDeviceToHost), "probe_issue");
+    cudaFree(d);
+    return rc;
+}
+
+int oevae_probe_bulk(int32_t bytes, int32_t depth, int32_t n_cta, int32_t same_src, int64_t* out_host2, int32_t device) {
+    if (!out_host2 || bytes % 16 || bytes <= 0 || depth < 1 || depth > 8 || (long)bytes * depth > 200 * 1024 || n_cta < 1) { g_create_error = "probe_bulk: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    long long* d = nullptr; unsigned char* src = nullptr;
+    size_t total = (size_t)bytes * depth * n_cta;
+    rc = free_fail(cudaMalloc(&d, 2 * sizeof(long long)), "cudaMalloc"); if (rc) return rc;
+    rc = free_fail(cudaMalloc(&src, total), "cudaMalloc"); if (rc) return rc;
+    cudaMemset(src, 1, total);
+    int smem = bytes * depth + 1024;
+    cudaFuncSetAttribute(bulk_copy_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    bulk_copy_probe_kernel<<<n_cta, 128, smem>>>(src, bytes, depth, same_src ? 0L : (long)bytes * depth, d);
+    LAUNCHED();
+    rc = free_fail(cudaMemcpy(out_host2, d, 2 * sizeof(long long), cudaMemcpyDeviceToHost), "probe_bulk");
+    cudaFree(d); cudaFree(src);
+    return rc;
 }
 
 int64_t oevae_launch_count(void) { return g_launches.load(); }

@@ -172,6 +172,19 @@ OEVAE_API int oevae_gemm(oevae_t h, int32_t kind, const float* A, int64_t sAr, i
  * raw TMEM accumulator [128 lanes, N] so that the M=64 / M=128 lane mapping can be asserted. */
 OEVAE_API int oevae_probe_mn(const float* A, const float* B, int32_t K, int32_t M, int32_t N, float* raw_out, int32_t device, void* stream);
 
+/* Tuning probe: cycles from issuing nm = {1,3,6,12,18,36} dependent tcgen05.mma (M x N x 16, bf16) to the mbarrier
+ * wake-up after tcgen05.commit; out_host6 is a HOST array of 6 int64. */
+OEVAE_API int oevae_probe_latency(int32_t M, int32_t N, int64_t* out_host6, int32_t device);
+
+/* Tuning probe: cycles for nw warps to each issue nm tcgen05.mma (mode 0: descriptors rebuilt, 1: hoisted) and see
+ * their commit; out_host1 is a HOST int64. */
+OEVAE_API int oevae_probe_issue(int32_t M, int32_t N, int32_t nw, int32_t nm, int32_t mode, int64_t* out_host1, int32_t device);
+
+/* Tuning probe: cycles for `depth` cp.async.bulk global->shared copies of `bytes` each, issued back to back by one
+ * thread of each of n_cta CTAs (same_src: every CTA reads the same bytes, as the weight images are read);
+ * out_host2 = {best of 5, first (cold)} of CTA 0. */
+OEVAE_API int oevae_probe_bulk(int32_t bytes, int32_t depth, int32_t n_cta, int32_t same_src, int64_t* out_host2, int32_t device);
+
 /* number of kernels this library has launched since load (bench.py "gpu_launches") */
 OEVAE_API int64_t oevae_launch_count(void);
 
