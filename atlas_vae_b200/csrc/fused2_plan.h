@@ -1,44 +1,57 @@
-// Plan of the feature-major fused training kernel (fused2_train.cuh).
+// Plan of the feature-major fused OE-VAE kernel (fused2_train.cuh), built on the host (fused2_host.cuh).
 //
-// Orientation: every accumulator has FEATURES on the TMEM lanes and JETS on the columns (D = W^T-image x act), so
-// that all 128 lanes work in the epilogues, activation rows are written with 16-byte stores, x is read coalesced
-// and dW^T rows are stored coalesced.  Activation "T-tiles" live in shared memory as [feature rows x 64 jets] bf16
-// SWIZZLE_128B (hi part, then lo part); row `width` of a tile is all ones (bias gradient through the dW product).
-// Keras layer index li: enc k (0..n-1), mean (n), log_var (n+1), dec k (n+2..2n+1), output (2n+2).
+// Orientation: every accumulator has FEATURES on the 128 TMEM lanes and the tile's 64 JETS on the columns
+// (D^T = W^T x act^T), so all 128 lanes work in the epilogues, bias / ReLU / bias-gradient are thread-local,
+// x is read coalesced and dW^T is stored coalesced.
+//
+// Shared-memory objects (all bf16 SWIZZLE_128B, hi part then lo part = the bf16x3 operand split):
+//   activation tile  [r16(width) feature rows x 64 jets]   MN-major B of the forward / dX products (K = features),
+//                                                          K-major A or B of the dW^T products (K = jets)
+//   X chunk          [64 jet rows x 64 features]           K-major B of layer 0, MN-major B of dW_0^T
+//   weight image     one 64-wide block [rows x 128 B] per op, rows = the larger of (in, out), contiguous = the smaller:
+//                    the same bytes are the A operand of the forward product and of the dX product (one K-major,
+//                    the other MN-major).  Layer 0: one op per 64 input features (rows = out); output layer: one op
+//                    per 64 output features (rows = in); heads: two blocks (mean | log_var).
+// Stage s: 0 = first encoder layer, 1..n-1 encoder hidden, n = heads, n+1..2n decoder hidden, 2n+1 = output layer.
+// Tile k (k = 0..2n) holds the output of stage k; tile n is the latent tile (z rows 0..15 forward; g_mu rows 0..15,
+// g_logvar rows 16..31 backward).
 #pragma once
 #include <stdint.h>
 
 namespace oevae {
 
-constexpr int kF2MaxLayers = 19;
+constexpr int kF2MaxStages = 18;
 constexpr int kF2MaxOps = 96;
+constexpr int kF2Jets = 64;          // jets per tile (UMMA N of the forward products)
+constexpr int kF2WSlots = 4;         // weight ring slots
+constexpr int kF2XSlots = 3;         // X chunk ring slots
 
-struct F2Layer {
-    int in, out;
-    int M, Min;                  // lanes (64/128) of the forward accumulator (>= out) and of the dX accumulator (>= in)
-    int kb_in, kb_out;           // ceil(in/64), ceil(out/64)
-    int in_tile, out_tile;       // T-tile ids; in_tile -1 = X (layer 0); out_tile -1 = output layer
+struct F2Stage {
+    int in, out;                     // true dims (heads: out = L per head)
+    int kin, kout;                   // r16(in); r16(out) (heads: 32)
+    int kind;                        // 0 first, 1 hidden rows=in, 2 hidden rows=out, 3 heads, 4 output
+    int rows;                        // image rows per block (multiple of 16)
     int relu;
-    int npad_in;                 // r16(in + 1): UMMA N of the dW^T product
-    long w_off, b_off;
+    int nseg;                        // dW^T lane segments -> flat parameters (heads: 2)
+    int seg_lane0[2], seg_n[2];
+    long seg_w[2], seg_b[2];         // kernel [in, seg_n] and bias [seg_n] offsets in the flat vector
 };
 
 struct F2Plan {
-    int n, nlay, D, L;
-    int nX;                      // 64-feature chunks of X
-    int nC;                      // 128-column chunks of the output layer
-    int n_tiles_smem;            // number of T-tiles
-    int tile_off[kF2MaxLayers];  // byte offset of the hi part
-    int tile_lo[kF2MaxLayers];   // byte distance hi -> lo part (= rows_alloc * 128)
-    int wide_off;                // X ring (2 x [64 jets x 128 B] hi+lo) aliased with the g_y slot ([128 x 128 B] hi+lo)
-    int wring_off;               // 2 weight slots of 32 KB
-    int scratch_off;             // fp32: mu, lv, eps [L][64]; w [64]; kld [64]; rec [4][64]
-    int zero_bytes;              // [0, zero_bytes) is cleared once per CTA (tiles + wide region)
+    int n, S, D, L;                  // hidden layers, stages (2n+2), input dim, latent dim
+    int nX;                          // 64-feature chunks of X (= 64-feature blocks of the output layer)
+    int nC;                          // 128-feature chunks of the output layer
+    int tile_off[kF2MaxStages], tile_rows[kF2MaxStages];
+    int wring_off, wslot_bytes;      // kF2WSlots slots
+    int s_off;                       // X ring (kF2XSlots x 16 KB) aliased with the g_y slot (32 KB)
+    int scratch_off;                 // fp32 scratch (see kernel)
+    int zero_bytes;                  // [0, zero_bytes): cleared once per CTA
     int smem_bytes;
-    int n_op_train, n_op_eval;
-    uint32_t op_off_train[kF2MaxOps], op_bytes_train[kF2MaxOps];
-    uint32_t op_off_eval[kF2MaxOps], op_bytes_eval[kF2MaxOps];
-    F2Layer layer[kF2MaxLayers];
+    int n_op_train, n_op_eval;       // both multiples of kF2WSlots; op k lives in ring slot k % kF2WSlots
+    int op_first[kF2MaxStages];      // per stage: first forward op (stage 0: nX ops; output: nX ops)
+    int op_bwd[kF2MaxStages];        // per stage: backward op (hidden + heads)
+    uint32_t op_off[kF2MaxOps], op_bytes[kF2MaxOps];
+    F2Stage st[kF2MaxStages];
     long P, Ppad;
 };
 

@@ -8,6 +8,8 @@
 #include "engine.h"
 #include "prof.h"
 #include "fused_host.cuh"
+#include "fused2_train.cuh"
+#include "fused2_host.cuh"
 #include <cstdlib>
 
 #include <algorithm>
@@ -84,6 +86,8 @@ int Engine::init(const oevae_config& c) {
 namespace oevae {
 struct FusedState {
     FPlan plan{};
+    F2Plan plan2{};                                         // feature-major kernel (default); plan = jet-major v1 (OEVAE_FUSED=1)
+    bool v2 = false;
     unsigned char* wimg = nullptr; int* pos = nullptr; float* parts = nullptr;
     uint32_t img_bytes = 0;
     bool img_dirty = true, last_fused = false;
@@ -106,6 +110,20 @@ int Engine::fused_init() {
     FusedState* f = new FusedState();
     std::vector<int> pos;
     bool ok = false;
+    if (!(env && atoi(env) == 1)) {
+        uint32_t img_bytes = 0;
+        if (build_fused2_plan(*this, f->plan2, pos, img_bytes)) {
+            f->v2 = true; f->img_bytes = img_bytes;
+            CK(cudaMalloc(&f->wimg, f->img_bytes));
+            CK(cudaMemset(f->wimg, 0, f->img_bytes));
+            CK(cudaMalloc(&f->pos, pos.size() * sizeof(int)));
+            CK(cudaMemcpy(f->pos, pos.data(), pos.size() * sizeof(int), cudaMemcpyHostToDevice));
+            CK(cudaMalloc(&f->parts, (size_t)n_sm * Ppad * sizeof(float)));
+            CK(cudaFuncSetAttribute(fused2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+            fz = f;
+            return 0;
+        }
+    }
     const int cand[4] = {64, 48, 32, 16};
     for (int i = 0; i < 4 && !ok; ++i) {
         if (ert && atoi(ert) != cand[i]) continue;
@@ -135,6 +153,30 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
         CKL();
         f.img_dirty = false;
     }
+    static long long* dbg_buf = nullptr;
+    const bool dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
+    if (dbg && !dbg_buf) cudaMalloc(&dbg_buf, 256 * sizeof(long long));
+    if (f.v2) {
+        F2Args b{};
+        b.x = x; b.w = w; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = f.parts;
+        b.per_jet = per_jet; b.sums = sums;
+        b.B = B; b.n_tiles = (int)((B + kF2Jets - 1) / kF2Jets); b.train = want_grad; b.mse = mse_type();
+        b.beta = beta; b.seed = cfg.seed; b.row_offset = row_offset;
+        b.step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
+        ++calls;
+        b.dbg = dbg ? dbg_buf : nullptr;
+        const int grid2 = std::min(b.n_tiles, n_sm);
+        { PROF(want_grad ? "fused_train" : "fused_eval", s); fused2_kernel<<<grid2, 256, f.plan2.smem_bytes, s>>>(f.plan2, b); }
+        CKL();
+        if (want_grad) { f.last_fused = true; f.last_grid = grid2; }
+        if (dbg) {
+            long long hbuf[256]; cudaStreamSynchronize(s); cudaMemcpy(hbuf, dbg_buf, sizeof hbuf, cudaMemcpyDeviceToHost);
+            fprintf(stderr, "[fused2 dbg] grid=%d stamps(cycles since start):", grid2);
+            for (int i = 2; i <= (int)hbuf[0]; ++i) fprintf(stderr, " %lld", hbuf[i] - hbuf[1]);
+            fprintf(stderr, "\n");
+        }
+        return 0;
+    }
     FusedArgs a{};
     a.x = x; a.w = w; a.eps = eps; a.wimg = f.wimg; a.parts = f.parts;
     a.per_jet = per_jet; a.sums = sums; a.kld_out = nullptr;
@@ -143,9 +185,6 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
     a.step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
     ++calls;
     const int grid = std::min(a.n_tiles, n_sm);
-    static long long* dbg_buf = nullptr;
-    const bool dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
-    if (dbg && !dbg_buf) cudaMalloc(&dbg_buf, 256 * sizeof(long long));
     a.dbg = dbg ? dbg_buf : nullptr;
     { PROF(want_grad ? "fused_train" : "fused_eval", s); fused_train_kernel<<<grid, 256, P_.smem_bytes, s>>>(P_, a); }
     CKL();
