@@ -24,7 +24,7 @@ constexpr int kF2MaxStages = 18;
 constexpr int kF2MaxOps = 96;
 constexpr int kF2Jets = 64;          // jets per tile (UMMA N of the forward products)
 constexpr int kF2WSlots = 4;         // weight ring slots
-constexpr int kF2XSlots = 3;         // X chunk ring slots
+constexpr int kF2XSlots = 2;         // X chunk ring slots
 
 struct F2Stage {
     int in, out;                     // true dims (heads: out = L per head)

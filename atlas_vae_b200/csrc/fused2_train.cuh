@@ -19,7 +19,7 @@ namespace oevae {
 namespace f2 {
 using namespace umma;
 
-constexpr uint32_t T_MU = 0, T_LV = 64, T_CH = 128, T_Y0 = 192, T_DW = 320;
+constexpr uint32_t T_MU = 0, T_LV = 64, T_CH = 128, T_Y0 = 192, T_DW = 320, T_C2 = 448;   // T_C2: second chain accumulator
 
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n\t}" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
@@ -39,27 +39,55 @@ __device__ __forceinline__ uint64_t desc(const Opnd& o, int ks, bool lo) {
     const uint32_t a = o.hi + (lo ? o.lo : 0u) + (uint32_t)ks * o.kstep;
     return o.mn ? smem_desc_sw128_mn(a, o.lbo) : smem_desc_sw128(a);
 }
-// D[128 x N] (+)= A * B over nk k-steps, bf16x3: Ahi*Bhi + Ahi*Blo + Alo*Bhi
-__device__ __forceinline__ void issue(uint32_t d, const Opnd& A, const Opnd& B, int nk, int N, bool acc) {
-    const uint32_t idesc = idesc_bf16_major(128, N, A.mn, B.mn);
+// D[128 x N] (+)= A * B over nk k-steps, bf16x3: Ahi*Bhi + Ahi*Blo + Alo*Bhi.  Descriptors are built once; a k-step
+// only advances their 14-bit start-address field (shared memory is < 256 KB, so the field cannot overflow).
+__device__ __noinline__ void issue_core(uint32_t d, uint64_t ah, uint64_t al, uint64_t bh, uint64_t bl, uint32_t a_step, uint32_t b_step,
+                                        int nk, uint32_t idesc, uint32_t acc) {
     for (int ks = 0; ks < nk; ++ks) {
-        const uint64_t ah = desc(A, ks, false), al = desc(A, ks, true), bh = desc(B, ks, false), bl = desc(B, ks, true);
-        mma_bf16_ss(d, ah, bh, idesc, acc ? 1u : 0u);
+        mma_bf16_ss(d, ah, bh, idesc, acc);
         mma_bf16_ss(d, ah, bl, idesc, 1u);
         mma_bf16_ss(d, al, bh, idesc, 1u);
-        acc = true;
+        acc = 1u;
+        ah += a_step; al += a_step; bh += b_step; bl += b_step;
     }
 }
+// same, k-steps alternating between two accumulators (d0 even, d1 odd) so that consecutive MMAs are independent;
+// acc0 / acc1: whether d0 / d1 already hold partial sums.  The epilogue adds the two.
+__device__ __noinline__ void issue_core2(uint32_t d0, uint32_t d1, uint64_t ah, uint64_t al, uint64_t bh, uint64_t bl, uint32_t a_step,
+                                         uint32_t b_step, int nk, uint32_t idesc, uint32_t acc0, uint32_t acc1) {
+    for (int ks = 0; ks < nk; ++ks) {
+        const uint32_t d = (ks & 1) ? d1 : d0, acc = (ks & 1) ? acc1 : acc0;
+        mma_bf16_ss(d, ah, bh, idesc, acc);
+        mma_bf16_ss(d, ah, bl, idesc, 1u);
+        mma_bf16_ss(d, al, bh, idesc, 1u);
+        if (ks & 1) acc1 = 1u; else acc0 = 1u;
+        ah += a_step; al += a_step; bh += b_step; bl += b_step;
+    }
+}
+__device__ __forceinline__ void issue2(uint32_t d0, uint32_t d1, const Opnd& A, const Opnd& B, int nk, int N, bool acc0, bool acc1) {
+    issue_core2(d0, d1, desc(A, 0, false), desc(A, 0, true), desc(B, 0, false), desc(B, 0, true), A.kstep >> 4, B.kstep >> 4, nk,
+                idesc_bf16_major(128, N, A.mn, B.mn), acc0 ? 1u : 0u, acc1 ? 1u : 0u);
+}
+__device__ __forceinline__ void issue(uint32_t d, const Opnd& A, const Opnd& B, int nk, int N, bool acc) {
+    issue_core(d, desc(A, 0, false), desc(A, 0, true), desc(B, 0, false), desc(B, 0, true), A.kstep >> 4, B.kstep >> 4, nk,
+               idesc_bf16_major(128, N, A.mn, B.mn), acc ? 1u : 0u);
+}
 
+// x0, x1 -> packed bf16 hi parts and packed bf16 lo parts (x ~= hi + lo, |err| <= 2^-17 |x|); non-finite residuals
+// (x = +-inf) are dropped so that an overflowing activation stays +-inf instead of turning into NaN
+__device__ __forceinline__ void split2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+    const __nv_bfloat162 hh = __floats2bfloat162_rn(x0, x1);
+    hi = *reinterpret_cast<const uint32_t*>(&hh);
+    float r0 = x0 - __uint_as_float(hi << 16), r1 = x1 - __uint_as_float(hi & 0xffff0000u);
+    r0 = (fabsf(x0) <= 3.0e38f) ? r0 : 0.f; r1 = (fabsf(x1) <= 3.0e38f) ? r1 : 0.f;
+    const __nv_bfloat162 ll = __floats2bfloat162_rn(r0, r1);
+    lo = *reinterpret_cast<const uint32_t*>(&ll);
+}
 // 16 consecutive jets (col0 % 16 == 0) of feature row `row` of an activation tile, as bf16 hi/lo
 __device__ __forceinline__ void store16(unsigned char* t_hi, unsigned char* t_lo, int row, int col0, const float* v) {
     uint32_t h[8], l[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        __nv_bfloat16 h0, l0, h1, l1;
-        split_bf16(v[2 * j], h0, l0); split_bf16(v[2 * j + 1], h1, l1);
-        h[j] = pack2(h0, h1); l[j] = pack2(l0, l1);
-    }
+    for (int j = 0; j < 8; ++j) split2(v[2 * j], v[2 * j + 1], h[j], l[j]);
     const uint32_t o0 = sw128_off(row, col0), o1 = sw128_off(row, col0 + 8);
     *reinterpret_cast<uint4*>(t_hi + o0) = make_uint4(h[0], h[1], h[2], h[3]);
     *reinterpret_cast<uint4*>(t_hi + o1) = make_uint4(h[4], h[5], h[6], h[7]);
@@ -80,10 +108,10 @@ __device__ __forceinline__ uint32_t positive16(const unsigned char* t_hi, int ro
     }
     return m;
 }
-// v[i] of every lane summed over the 32 lanes; lane i returns the total of index i
-__device__ __forceinline__ float transpose_reduce32(float* v, int lane) {
+// 16 values per lane summed over the 32 lanes; every lane returns the total of index (lane & 15)
+__device__ __forceinline__ float transpose_reduce16(float* v, int lane) {
 #pragma unroll
-    for (int s = 16; s >= 1; s >>= 1) {
+    for (int s = 8; s >= 1; s >>= 1) {
         const bool up = (lane & s) != 0;
 #pragma unroll
         for (int i = 0; i < s; ++i) {
@@ -91,7 +119,7 @@ __device__ __forceinline__ float transpose_reduce32(float* v, int lane) {
             v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
         }
     }
-    return v[0];
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
 }
 }  // namespace f2
 
@@ -106,7 +134,10 @@ struct F2Args {
     long long* dbg;
 };
 
-__global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ F2Plan P, F2Args a) {
+
+constexpr int kF2Threads = 512;                             // 16 warps: lane quarter q = warp & 3, column group h = warp >> 2
+
+__global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_constant__ F2Plan P, F2Args a) {
     using namespace umma;
     using namespace f2;
     extern __shared__ unsigned char smem_dyn[];
@@ -115,7 +146,7 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
     unsigned char* sm = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, q = warp & 3, h = warp >> 2;
     const int frow = 32 * q + lane;                          // TMEM lane = feature row owned by this thread
-    const int jc0 = 32 * h;                                  // first of the 32 jet columns owned by this thread
+    const int jc0 = 16 * h;                                  // first of the 16 jet columns owned by this thread
     const int n = P.n, D = P.D, L = P.L, so = 2 * n + 1;
     const int nops = a.train ? P.n_op_train : P.n_op_eval;
     const int n_fwd_ops = P.op_first[so] + P.nX;
@@ -123,13 +154,14 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
     float* s_w = reinterpret_cast<float*>(sm + P.scratch_off);        // [64] jet weights (0 for rows past the batch)
     float* s_rec = s_w + 64;                                           // [4][64] per lane-quarter reconstruction sums
     float* s_kld = s_rec + 256;                                        // [64]
-    float* s_db = s_kld + 64;                                          // [4][2][128] bias-gradient halves
-    float* s_eps = s_db + 1024;                                        // [L][64]
+    float* s_db = s_kld + 64;                                          // [4 buffers][4 column groups][128] bias-gradient parts
+    float* s_eps = s_db + 2048;                                        // [L][64]
     auto tile_hi = [&](int k) { return sm + P.tile_off[k]; };
     auto tile_lo = [&](int k) { return sm + P.tile_off[k] + P.tile_rows[k] * 128; };
     auto xslot = [&](int s) { return sm + P.s_off + s * 16384; };      // hi 8 KB, lo 8 KB
     unsigned char* gy_hi = sm + P.s_off; unsigned char* gy_lo = gy_hi + 16384;
-    auto wslot = [&](long g) { return sm + P.wring_off + (int)(g % kF2WSlots) * P.wslot_bytes; };
+    auto wslot = [&](int g) { return sm + P.wring_off + (g & (kF2WSlots - 1)) * P.wslot_bytes; };
+    auto db_at = [&](int buf, int hh, int row) -> float& { return s_db[(buf * 4 + hh) * 128 + row]; };
 
     // ---- one-time setup
     if (tid == 0) {
@@ -138,7 +170,7 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
         for (int i = 0; i < kF2WSlots; ++i) mbar_init(&wbar[i], 1);
         mbar_fence_init();
     }
-    for (int i = tid * 16; i < P.zero_bytes; i += 256 * 16) *reinterpret_cast<uint4*>(sm + i) = make_uint4(0, 0, 0, 0);
+    for (int i = tid * 16; i < P.zero_bytes; i += kF2Threads * 16) *reinterpret_cast<uint4*>(sm + i) = make_uint4(0, 0, 0, 0);
     if (warp == 0) tmem_alloc(&tmem_base_s, 512);
     fence_async_smem();
     tc_fence_before();
@@ -147,26 +179,30 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
     const uint32_t tm = tmem_base_s;
     const uint32_t t_lane = tm + ((uint32_t)(32 * q) << 16);
 
-    // ---- weight ring (thread 0 only): ops are consumed strictly in order; op g lives in slot g % 4
+    // ---- weight ring: ops are consumed strictly in order; op g lives in slot g % 4.  Thread 0 (the MMA issuer) waits for
+    // arrivals (wget); the producer (lane 0 of the last warp, idle in most epilogues) mirrors the same program order,
+    // declares ops consumed (wdone) and keeps the ring full.  Each keeps its own counters; nothing is shared.
+    const bool producer = tid == kF2Threads - 32;
     const int my_tiles = ((int)blockIdx.x < a.n_tiles) ? (a.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
-    const long w_total = (long)my_tiles * nops;
-    long w_issued = 0, w_done = 0, gbase = 0;
-    int w_next = 0;
+    const int w_total = my_tiles * nops;
+    int w_issued = 0, w_done = 0, gbase = 0, w_next = 0;
+    auto wbar_wait = [&](int g) { mbar_wait(&wbar[g & (kF2WSlots - 1)], (uint32_t)((g >> 2) & 1)); };
     auto refill = [&]() {
         while (w_issued < w_total && w_issued < w_done + kF2WSlots) {
-            const int k = (int)(w_issued % nops), s = (int)(w_issued % kF2WSlots);
+            const int k = w_issued % nops, s = w_issued & (kF2WSlots - 1);
             const uint32_t bytes = (!a.train && k >= n_fwd_ops) ? 16u : P.op_bytes[k];
             mbar_expect_tx(&wbar[s], bytes);
             bulk_g2s(wslot(w_issued), a.wimg + P.op_off[k], bytes, &wbar[s]);
             ++w_issued;
         }
     };
-    auto wget = [&](int k) -> uint32_t {                      // wait until op k of this tile has landed; returns its slot
-        for (; w_next <= k; ++w_next) { const long g = gbase + w_next; mbar_wait(&wbar[g % kF2WSlots], (uint32_t)((g / kF2WSlots) & 1)); }
+    auto wget = [&](int k) -> uint32_t {                      // thread 0: wait until op k of this tile has landed; returns its slot
+        for (; w_next <= k; ++w_next) wbar_wait(gbase + w_next);
         return smem_u32(wslot(gbase + k));
     };
-    auto wdone = [&](int k) { w_done = gbase + k + 1; refill(); };   // every MMA that reads ops <= k has completed
-    if (tid == 0) refill();
+    auto wdone = [&](int k) { w_done = gbase + k + 1; refill(); };   // producer: every MMA that reads ops <= k has completed
+    auto wdone_dummy = [&](int k) { wbar_wait(gbase + k); wdone(k); };   // producer: op k has no consumer, only its arrival counts
+    if (producer) refill();
 
     uint32_t ph_m = 0, ph_y = 0, ph_x = 0;
     auto wait_mma = [&]() { mbar_wait(&mma_bar, ph_m); ph_m ^= 1u; tc_fence_after(); };
@@ -189,71 +225,103 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
             const long nrow0 = row0 + (long)pf * gridDim.x * kF2Jets;
             const long nbytes = min((long)kF2Jets, a.B - nrow0) * D * 4;
             const char* nx = reinterpret_cast<const char*>(a.x + nrow0 * D);
-            for (long o = (long)tid * 128; o < nbytes; o += 256 * 128) prefetch_l2(nx + o);
+            for (long o = (long)tid * 128; o < nbytes; o += kF2Threads * 128) prefetch_l2(nx + o);
+        }
+        // reparameterisation noise of the tile -> s_eps[l][jet]: external eps, or one Philox counter (row, quad, step)
+        // = latents 4*quad .. 4*quad+3 of one jet (the spec of oracle/philox.py)
+        if (a.eps) {
+            for (int i = tid; i < 64 * L; i += kF2Threads) {
+                const int j = i / L, l = i - j * L;
+                s_eps[l * 64 + j] = j < nvalid ? __ldg(a.eps + (row0 + j) * L + l) : 0.f;
+            }
+        } else if (tid < 64 * ((L + 3) >> 2)) {
+            const int j = tid & 63, quad = tid >> 6;
+            float nrm[4];
+            philox_normal4(a.seed, a.row_offset + (unsigned long long)(row0 + j), (unsigned)quad, a.step, nrm);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) if (4 * quad + t < L) s_eps[(4 * quad + t) * 64 + j] = nrm[t];
         }
 
-        // [64 jets x features 64c..64c+63] of X -> ring slot xs (bf16 hi/lo, K-major rows = jets)
-        auto stage_x = [&](int c, int xs) {
-            unsigned char* hi = xslot(xs); unsigned char* lo = hi + 8192;
+        // X chunk c = [64 jets x features 64c..64c+63]: ldx pulls this thread's two float4 into registers (issued two
+        // chunks ahead), stx writes them to ring slot xs as bf16 hi/lo (K-major rows = jets)
+        auto ldx = [&](int c, float4 (&r)[2]) {
 #pragma unroll
-            for (int it = 0; it < 4; ++it) {
-                const int idx = tid + 256 * it, r = idx >> 4, c4 = (idx & 15) << 2, col = 64 * c + c4;
-                float v[4] = {0.f, 0.f, 0.f, 0.f};
-                if (r < nvalid) {
-                    const float* p = a.x + (row0 + r) * D + col;
-                    if (col + 3 < D && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
-                        const float4 t = __ldg(reinterpret_cast<const float4*>(p));
-                        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) v[j] = (col + j < D) ? __ldg(p + j) : 0.f;
+            for (int it = 0; it < 2; ++it) {
+                const int idx = tid + kF2Threads * it, rr = idx >> 4, c4 = (idx & 15) << 2, col = 64 * c + c4;
+                float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (c < P.nX && rr < nvalid) {
+                    const float* p = a.x + (row0 + rr) * D + col;
+                    if (col + 3 < D && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) t = __ldg(reinterpret_cast<const float4*>(p));
+                    else {
+                        if (col < D) t.x = __ldg(p);
+                        if (col + 1 < D) t.y = __ldg(p + 1);
+                        if (col + 2 < D) t.z = __ldg(p + 2);
+                        if (col + 3 < D) t.w = __ldg(p + 3);
                     }
                 }
-                __nv_bfloat16 hh[4], ll[4];
+                r[it] = t;
+            }
+        };
+        auto stx = [&](int xs, const float4 (&r)[2]) {
+            unsigned char* hi = xslot(xs); unsigned char* lo = hi + 8192;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) split_bf16(v[j], hh[j], ll[j]);
-                const uint32_t off = sw128_off(r, c4);
-                *reinterpret_cast<uint2*>(hi + off) = make_uint2(pack2(hh[0], hh[1]), pack2(hh[2], hh[3]));
-                *reinterpret_cast<uint2*>(lo + off) = make_uint2(pack2(ll[0], ll[1]), pack2(ll[2], ll[3]));
+            for (int it = 0; it < 2; ++it) {
+                const int idx = tid + kF2Threads * it, rr = idx >> 4, c4 = (idx & 15) << 2;
+                uint32_t ha, la, hb, lb;
+                split2(r[it].x, r[it].y, ha, la); split2(r[it].z, r[it].w, hb, lb);
+                const uint32_t off = sw128_off(rr, c4);
+                *reinterpret_cast<uint2*>(hi + off) = make_uint2(ha, hb);
+                *reinterpret_cast<uint2*>(lo + off) = make_uint2(la, lb);
             }
         };
         // chain accumulator -> bias + ReLU -> tile s (pad rows zero)
-        auto epi_act = [&](int s) {
+        auto epi_act = [&](int s, float bias, bool two) {
             const F2Stage& st = P.st[s];
             if (32 * q >= P.tile_rows[s]) return;
-            const float bias = frow < st.out ? __ldg(a.theta + st.seg_b[0] + frow) : 0.f;
+            float v[16];
+            tmem_ld16(t_lane + T_CH + jc0, v);
+            if (two) {
+                float u[16];
+                tmem_ld16(t_lane + T_C2 + jc0, u);
 #pragma unroll
-            for (int g = 0; g < 2; ++g) {
-                float v[16];
-                tmem_ld16(t_lane + T_CH + jc0 + 16 * g, v);
-                if (frow < P.tile_rows[s]) {
+                for (int j = 0; j < 16; ++j) v[j] += u[j];
+            }
+            if (frow < P.tile_rows[s]) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const float t = v[j] + bias;
-                        v[j] = frow < st.out ? (st.relu ? fmaxf(t, 0.f) : t) : 0.f;
-                    }
-                    store16(tile_hi(s), tile_lo(s), frow, jc0 + 16 * g, v);
+                for (int j = 0; j < 16; ++j) {
+                    const float t = v[j] + bias;
+                    v[j] = frow < st.out ? (st.relu ? fmaxf(t, 0.f) : t) : 0.f;
                 }
+                store16(tile_hi(s), tile_lo(s), frow, jc0, v);
             }
         };
-        // chain accumulator (dX of stage s) -> ReLU mask of H_{s-1} -> G_{s-1} over tile s-1, bias-gradient halves
+        auto bias_of = [&](int s) { return frow < P.st[s].out ? __ldg(a.theta + P.st[s].seg_b[0] + frow) : 0.f; };
+        // chain accumulator (dX of stage s) -> ReLU mask of H_{s-1} -> G_{s-1} over tile s-1, bias-gradient parts
         auto epi_grad = [&](int s) {
             const F2Stage& st = P.st[s];
             const int rows = P.tile_rows[s - 1];
             if (32 * q >= rows) return;
-            float dbs = 0.f;
+            float v[16];
+            tmem_ld16(t_lane + T_CH + jc0, v);
+            if (frow < rows) {
+                float dbs = 0.f;
+                const uint32_t m = positive16(tile_hi(s - 1), frow, jc0);
 #pragma unroll
-            for (int g = 0; g < 2; ++g) {
-                float v[16];
-                tmem_ld16(t_lane + T_CH + jc0 + 16 * g, v);
-                if (frow < rows) {
-                    const uint32_t m = positive16(tile_hi(s - 1), frow, jc0 + 16 * g);
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) { v[j] = (((m >> j) & 1u) && frow < st.in) ? v[j] : 0.f; dbs += v[j]; }
-                    store16(tile_hi(s - 1), tile_lo(s - 1), frow, jc0 + 16 * g, v);
-                }
+                for (int j = 0; j < 16; ++j) { v[j] = (((m >> j) & 1u) && frow < st.in) ? v[j] : 0.f; dbs += v[j]; }
+                store16(tile_hi(s - 1), tile_lo(s - 1), frow, jc0, v);
+                db_at((s - 1) & 1, h, frow) = dbs;
             }
-            if (frow < rows) s_db[(((s - 1) & 1) * 2 + h) * 128 + frow] = dbs;
+        };
+        // 16 columns i0.. of a dW^T accumulator row -> rows i0.. of the Keras [in, ld] kernel gradient, column o
+        auto put_dw = [&](float* dw, long ld, int i0, int in, const float* v) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                if (i0 + j < in) { float* d = dw + (long)(i0 + j) * ld; *d = tile_iter ? *d + v[j] : v[j]; }
+            }
+        };
+        auto put_db = [&](float* d, int buf, int row) {
+            const float t = (db_at(buf, 0, row) + db_at(buf, 1, row)) + (db_at(buf, 2, row) + db_at(buf, 3, row));
+            *d = tile_iter ? *d + t : t;
         };
         // dW^T accumulator of stage s (lane = output feature, column = input feature) -> partial-gradient slice
         auto epi_dw = [&](int s, int buf) {
@@ -265,45 +333,42 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
             for (int k = 0; k < 2; ++k) if (k < st.nseg && frow >= st.seg_lane0[k] && frow < st.seg_lane0[k] + st.seg_n[k]) sg = k;
             const int o = sg >= 0 ? frow - st.seg_lane0[sg] : 0, ld = sg >= 0 ? st.seg_n[sg] : 0;
             float* dw = part + (sg >= 0 ? st.seg_w[sg] : 0) + o;
-            const int ng = st.kin >> 4, g0 = h ? (ng + 1) >> 1 : 0, g1 = h ? ng : (ng + 1) >> 1;
-            for (int g = g0; g < g1; ++g) {
+            for (int g = h; g < (st.kin >> 4); g += 4) {
                 float v[16];
                 tmem_ld16(t_lane + T_DW + 16 * g, v);
-                if (sg >= 0) {
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const int i = 16 * g + j;
-                        if (i < st.in) { float* d = dw + (long)i * ld; *d = tile_iter ? *d + v[j] : v[j]; }
-                    }
-                }
+                if (sg >= 0) put_dw(dw, ld, 16 * g, st.in, v);
             }
-            if (sg >= 0 && h == 0) {
-                float* d = part + st.seg_b[sg] + o;
-                const float t = s_db[(buf * 2) * 128 + frow] + s_db[(buf * 2 + 1) * 128 + frow];
-                *d = tile_iter ? *d + t : t;
-            }
+            if (sg >= 0 && h == 0) put_db(part + st.seg_b[sg] + o, buf, frow);
         };
 
         // =========================================================== forward, stage 0: X streamed in 64-feature chunks
         {
             const F2Stage& st = P.st[0];
-            for (int c = 0; c < P.nX; ++c) {
+            float4 ra[2], rb[2];
+            ldx(0, ra); ldx(1, rb);
+            auto chunk = [&](int c, float4 (&r)[2]) {
                 const int xs = c % kF2XSlots;
-                if (c >= kF2XSlots) { wait_x(xs); if (tid == 0) wdone(P.op_first[0] + c - kF2XSlots); }
-                stage_x(c, xs);
+                if (c >= kF2XSlots) { wait_x(xs); if (producer) wdone(P.op_first[0] + c - kF2XSlots); }
+                stx(xs, r);
+                ldx(c + 2, r);
                 publish();
                 if (tid == 0) {
                     const uint32_t wb = wget(P.op_first[0] + c);
                     tc_fence_after();
                     const int nk = min(4, (D - 64 * c + 15) >> 4);
-                    issue(tm + T_CH, opnd_k(wb, st.rows * 128), opnd_k(smem_u32(xslot(xs)), 8192), nk, kF2Jets, c > 0);
+                    issue2(tm + T_CH, tm + T_C2, opnd_k(wb, st.rows * 128), opnd_k(smem_u32(xslot(xs)), 8192), nk, kF2Jets, c > 0, c > 0);
                     mma_commit(&xbar[xs]);
                 }
+            };
+            for (int c = 0; c < P.nX; c += 2) {
+                chunk(c, ra);
+                if (c + 1 < P.nX) chunk(c + 1, rb);
             }
+            const float bias0 = bias_of(0);
             for (int c = max(0, P.nX - kF2XSlots); c < P.nX; ++c) wait_x(c % kF2XSlots);
-            if (tid == 0) wdone(P.op_first[0] + P.nX - 1);
+            if (producer) wdone(P.op_first[0] + P.nX - 1);
             stamp();
-            epi_act(0);
+            epi_act(0, bias0, D > 16);
             publish();
             stamp();
         }
@@ -316,7 +381,8 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
                 const uint32_t part_b = st.rows * 128;
                 const Opnd B = opnd_mn(smem_u32(tile_hi(s - 1)), P.tile_rows[s - 1] * 128, 8192);
                 const int nk = st.kin >> 4;
-                if (st.kind == 1) issue(tm + T_CH, opnd_mn(wb, part_b, part_b), B, nk, kF2Jets, false);
+                if (false) {}
+                else if (st.kind == 1) issue(tm + T_CH, opnd_mn(wb, part_b, part_b), B, nk, kF2Jets, false);
                 else if (st.kind == 2) issue(tm + T_CH, opnd_k(wb, part_b), B, nk, kF2Jets, false);
                 else {                                                   // heads: mean block, log_var block
                     issue(tm + T_MU, opnd_mn(wb, 2 * part_b, part_b), B, nk, kF2Jets, false);
@@ -324,70 +390,40 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
                 }
                 mma_commit(&mma_bar);
             }
+            // biases are fetched while the MMAs run
+            float b_mu = 0.f, b_lv = 0.f;
+            if (s != n) b_mu = bias_of(s);
+            else if (lane < L) { b_mu = __ldg(a.theta + st.seg_b[0] + lane); b_lv = __ldg(a.theta + st.seg_b[1] + lane); }
             wait_mma();
-            if (tid == 0) wdone(P.op_first[s]);
+            if (producer) wdone(P.op_first[s]);
             if (s != n) {
-                epi_act(s);
+                epi_act(s, b_mu, false);
             } else if (q == 0) {
                 // ---- heads: Sampling (models.py:9-15) + KLD (models.py:81-85); z -> rows 0..15 of the latent tile
-                const F2Stage& hs = P.st[n];
-                const float b_mu = lane < L ? __ldg(a.theta + hs.seg_b[0] + lane) : 0.f;
-                const float b_lv = lane < L ? __ldg(a.theta + hs.seg_b[1] + lane) : 0.f;
-                float kl[32];
+                float mu[16], lv[16], kl[16];
+                tmem_ld16(t_lane + T_MU + jc0, mu);
+                tmem_ld16(t_lane + T_LV + jc0, lv);
 #pragma unroll
-                for (int g = 0; g < 2; ++g) {
-                    float mu[16], lv[16], ep[16], z[16];
-                    tmem_ld16(t_lane + T_MU + jc0 + 16 * g, mu);
-                    tmem_ld16(t_lane + T_LV + jc0 + 16 * g, lv);
-                    if (a.eps) {
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const int col = jc0 + 16 * g + j;
-                            ep[j] = (lane < L && col < nvalid) ? __ldg(a.eps + (row0 + col) * L + lane) : 0.f;
-                        }
-                    } else {
-                        // Philox counter (row, quad, step) yields latents 4*quad..4*quad+3 of one jet: lane (quad, t) draws
-                        // jet cb+t and the four lanes of a quad exchange components
-#pragma unroll
-                        for (int cb = 0; cb < 16; cb += 4) {
-                            float nrm[4];
-                            philox_normal4(a.seed, a.row_offset + (unsigned long long)(row0 + jc0 + 16 * g + cb + (lane & 3)),
-                                           (unsigned)(lane >> 2), a.step, nrm);
-#pragma unroll
-                            for (int r = 0; r < 4; ++r) {
-                                const int sel = (lane & 3) ^ r;
-                                const float pub = sel == 0 ? nrm[0] : sel == 1 ? nrm[1] : sel == 2 ? nrm[2] : nrm[3];
-                                const float got = __shfl_sync(0xffffffffu, pub, (lane & ~3) | sel);
-                                // got = component (lane & 3) of jet cb + sel
-#pragma unroll
-                                for (int t = 0; t < 4; ++t) if (t == sel) ep[cb + t] = got;
-                            }
-                        }
+                for (int j = 0; j < 16; ++j) {
+                    float zz = 0.f, kk = 0.f;
+                    if (lane < L) {
+                        const float m = mu[j] + b_mu, v = lv[j] + b_lv;
+                        zz = m + clipv(expf(v * 0.5f)) * s_eps[lane * 64 + jc0 + j];
+                        kk = 1.f + v - clipv(expf(v)) - m * m;
                     }
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const int col = jc0 + 16 * g + j;
-                        float zz = 0.f, kk = 0.f;
-                        if (lane < L) {
-                            const float m = mu[j] + b_mu, v = lv[j] + b_lv;
-                            zz = m + clipv(expf(v * 0.5f)) * ep[j];
-                            kk = 1.f + v - clipv(expf(v)) - m * m;
-                            s_eps[lane * 64 + col] = ep[j];
-                        }
-                        z[j] = zz; kl[16 * g + j] = kk;
-                    }
-                    if (lane < 16) store16(tile_hi(n), tile_lo(n), lane, jc0 + 16 * g, z);
+                    mu[j] = zz; kl[j] = kk;
                 }
-                const float ks = transpose_reduce32(kl, lane);
-                s_kld[jc0 + lane] = -(ks / (float)L) / 2.f;
+                if (lane < 16) store16(tile_hi(n), tile_lo(n), lane, jc0, mu);
+                const float ks = transpose_reduce16(kl, lane);
+                if (lane < 16) s_kld[jc0 + lane] = -(ks / (float)L) / 2.f;
             }
             publish();
             stamp();
         }
         // =========================================================== output layer in 128-feature chunks
-        float rec_acc[32];
+        float rec_acc[16];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) rec_acc[j] = 0.f;
+        for (int j = 0; j < 16; ++j) rec_acc[j] = 0.f;
         {
             const F2Stage& st = P.st[so];
             const uint32_t part_b = st.rows * 128;
@@ -401,47 +437,43 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
                       opnd_mn(smem_u32(tile_hi(2 * n)), P.tile_rows[2 * n] * 128, 8192), st.kin >> 4, kF2Jets, false);
                 mma_commit(&y_bar);
             };
-            if (tid == 0) { wget(ob - 1); wdone(ob - 1); issue_y(0); }   // ob-1: stage 2n's op or the alignment dummy
+            if (producer && ob - 1 != P.op_first[2 * n]) wdone_dummy(ob - 1);                   // alignment dummy before the output ops
+            if (tid == 0) issue_y(0);
             for (int c = 0; c < P.nC; ++c) {
                 const int last_op = ob + min(2 * c + 1, P.nX - 1);
+                const int f = 128 * c + frow;
+                const bool valid = f < D;
+                // this thread's 16 x values of the chunk (L2-resident since stage 0), issued before the accumulator wait
+                float xv[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) xv[j] = (valid && jc0 + j < nvalid) ? __ldg(a.x + (row0 + jc0 + j) * D + f) : 0.f;
+                const float bias = valid ? __ldg(a.theta + st.seg_b[0] + f) : 0.f;
                 wait_y();
                 if (tid == 0 && c + 1 < P.nC) issue_y(c + 1);
                 stamp();
                 // reconstruction loss (models.py:66,72-78) and its gradient through clip_values
                 {
-                    const int f = 128 * c + frow;
-                    const bool valid = f < D;
-                    const float bias = valid ? __ldg(a.theta + st.seg_b[0] + f) : 0.f;
                     float dbs = 0.f;
+                    float y[16];
+                    tmem_ld16(t_lane + T_Y0 + 64 * (c & 1) + jc0, y);
 #pragma unroll
-                    for (int g = 0; g < 2; ++g) {
-                        float y[16], xv[16];
-                        tmem_ld16(t_lane + T_Y0 + 64 * (c & 1) + jc0 + 16 * g, y);
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const int col = jc0 + 16 * g + j;
-                            xv[j] = (valid && col < nvalid) ? __ldg(a.x + (row0 + col) * D + f) : 0.f;
+                    for (int j = 0; j < 16; ++j) {
+                        float gy = 0.f;
+                        if (valid) {
+                            const float yr = y[j] + bias, d = clipv(yr) - xv[j], wj = s_w[jc0 + j];
+                            rec_acc[j] += a.mse ? d * d : fabsf(d);
+                            const float gg = a.mse ? wj * 2.f * d * inv_d : wj * (float)((d > 0.f) - (d < 0.f)) * inv_d;
+                            gy = clip_pass(yr) ? gg : 0.f;
                         }
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            float gy = 0.f;
-                            if (valid) {
-                                const float yr = y[j] + bias, d = clipv(yr) - xv[j], wj = s_w[jc0 + 16 * g + j];
-                                rec_acc[16 * g + j] += a.mse ? d * d : fabsf(d);
-                                const float gg = a.mse ? wj * 2.f * d * inv_d : wj * (float)((d > 0.f) - (d < 0.f)) * inv_d;
-                                gy = clip_pass(yr) ? gg : 0.f;
-                            }
-                            dbs += gy; y[j] = gy;
-                        }
-                        if (a.train) store16(gy_hi, gy_lo, frow, jc0 + 16 * g, y);
+                        dbs += gy; y[j] = gy;
                     }
-                    if (a.train) s_db[((2 + (c & 1)) * 2 + h) * 128 + frow] = dbs;
+                    if (a.train) { store16(gy_hi, gy_lo, frow, jc0, y); db_at(2 + (c & 1), h, frow) = dbs; }
                 }
                 stamp();
                 if (!a.train) {
                     tc_fence_before();
                     __syncthreads();                                    // accumulator reads done before chunk c+2 overwrites it
-                    if (tid == 0) wdone(last_op);
+                    if (producer) wdone(last_op);
                     continue;
                 }
                 publish();
@@ -459,37 +491,21 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
                     mma_commit(&mma_bar);
                 }
                 wait_mma();
-                if (tid == 0) wdone(last_op);
+                if (producer) wdone(last_op);
                 stamp();
                 // dW_out^T chunk -> part (lanes = output features: coalesced rows of the Keras [in, D] kernel)
-                {
-                    const int f = 128 * c + frow;
-                    const bool valid = f < D;
-                    float* dw = part + st.seg_w[0] + f;
-                    const int ng = st.kin >> 4, g0 = h ? (ng + 1) >> 1 : 0, g1 = h ? ng : (ng + 1) >> 1;
-                    for (int g = g0; g < g1; ++g) {
-                        float v[16];
-                        tmem_ld16(t_lane + T_DW + 16 * g, v);
-                        if (valid) {
-#pragma unroll
-                            for (int j = 0; j < 16; ++j) {
-                                const int i = 16 * g + j;
-                                if (i < st.in) { float* d = dw + (long)i * D; *d = tile_iter ? *d + v[j] : v[j]; }
-                            }
-                        }
-                    }
-                    if (valid && h == 0) {
-                        float* d = part + st.seg_b[0] + f;
-                        const float t = s_db[((2 + (c & 1)) * 2) * 128 + frow] + s_db[((2 + (c & 1)) * 2 + 1) * 128 + frow];
-                        *d = tile_iter ? *d + t : t;
-                    }
+                for (int g = h; g < (st.kin >> 4); g += 4) {
+                    float v[16];
+                    tmem_ld16(t_lane + T_DW + 16 * g, v);
+                    if (valid) put_dw(part + st.seg_w[0] + f, D, 16 * g, st.in, v);
                 }
+                if (valid && h == 0) put_db(part + st.seg_b[0] + f, 2 + (c & 1), frow);
                 tc_fence_before();
                 stamp();
             }
-            const float rs = transpose_reduce32(rec_acc, lane);
-            s_rec[q * 64 + jc0 + lane] = rs;
-            if (a.train) { __syncthreads(); epi_grad(so); publish(); }
+            const float rs = transpose_reduce16(rec_acc, lane);
+            if (lane < 16) s_rec[q * 64 + jc0 + lane] = rs;
+            if (a.train) { epi_grad(so); publish(); }
             stamp();
         }
         // =========================================================== backward chain: stages 2n .. 1
@@ -513,43 +529,38 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
                     }
                     mma_commit(&mma_bar);
                 }
+                float b_mu = 0.f, b_lv = 0.f;
+                if (s == n + 1 && lane < L) { b_mu = __ldg(a.theta + P.st[n].seg_b[0] + lane); b_lv = __ldg(a.theta + P.st[n].seg_b[1] + lane); }
                 wait_mma();
-                if (tid == 0) wdone(P.op_bwd[s]);
+                if (producer) wdone(P.op_bwd[s]);
                 epi_dw(s, s & 1);
                 if (s != n + 1) {
                     epi_grad(s);
                 } else if (q == 0) {
                     // ---- latent backward: g_z -> g_mu (rows 0..15), g_logvar (rows 16..31) of the latent tile
-                    const F2Stage& hs = P.st[n];
-                    const float b_mu = lane < L ? __ldg(a.theta + hs.seg_b[0] + lane) : 0.f;
-                    const float b_lv = lane < L ? __ldg(a.theta + hs.seg_b[1] + lane) : 0.f;
                     const float inv_l = 1.f / (float)L;
                     float dbm = 0.f, dbl = 0.f;
+                    float gz[16], mu[16], lv[16];
+                    tmem_ld16(t_lane + T_CH + jc0, gz);
+                    tmem_ld16(t_lane + T_MU + jc0, mu);
+                    tmem_ld16(t_lane + T_LV + jc0, lv);
 #pragma unroll
-                    for (int g = 0; g < 2; ++g) {
-                        float gz[16], mu[16], lv[16];
-                        tmem_ld16(t_lane + T_CH + jc0 + 16 * g, gz);
-                        tmem_ld16(t_lane + T_MU + jc0 + 16 * g, mu);
-                        tmem_ld16(t_lane + T_LV + jc0 + 16 * g, lv);
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const int col = jc0 + 16 * g + j;
-                            float gm = 0.f, gl = 0.f;
-                            if (lane < L) {
-                                const float m = mu[j] + b_mu, v = lv[j] + b_lv, gk = a.beta * s_w[col];
-                                const float e_raw = expf(v), s_raw = expf(v * 0.5f);
-                                gm = gz[j] + gk * m * inv_l;
-                                gl = gk * (-(1.f - (clip_pass(e_raw) ? e_raw : 0.f)) * 0.5f * inv_l)
-                                   + gz[j] * s_eps[lane * 64 + col] * (clip_pass(s_raw) ? s_raw * 0.5f : 0.f);
-                            }
-                            mu[j] = gm; lv[j] = gl; dbm += gm; dbl += gl;
+                    for (int j = 0; j < 16; ++j) {
+                        float gm = 0.f, gl = 0.f;
+                        if (lane < L) {
+                            const float m = mu[j] + b_mu, v = lv[j] + b_lv, gk = a.beta * s_w[jc0 + j];
+                            const float e_raw = expf(v), s_raw = expf(v * 0.5f);
+                            gm = gz[j] + gk * m * inv_l;
+                            gl = gk * (-(1.f - (clip_pass(e_raw) ? e_raw : 0.f)) * 0.5f * inv_l)
+                               + gz[j] * s_eps[lane * 64 + jc0 + j] * (clip_pass(s_raw) ? s_raw * 0.5f : 0.f);
                         }
-                        if (lane < 16) {
-                            store16(tile_hi(n), tile_lo(n), lane, jc0 + 16 * g, mu);
-                            store16(tile_hi(n), tile_lo(n), 16 + lane, jc0 + 16 * g, lv);
-                        }
+                        mu[j] = gm; lv[j] = gl; dbm += gm; dbl += gl;
                     }
-                    if (lane < 16) { s_db[((n & 1) * 2 + h) * 128 + lane] = dbm; s_db[((n & 1) * 2 + h) * 128 + 16 + lane] = dbl; }
+                    if (lane < 16) {
+                        store16(tile_hi(n), tile_lo(n), lane, jc0, mu);
+                        store16(tile_hi(n), tile_lo(n), 16 + lane, jc0, lv);
+                        db_at(n & 1, h, lane) = dbm; db_at(n & 1, h, 16 + lane) = dbl;
+                    }
                 }
                 publish();
                 stamp();
@@ -559,10 +570,13 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
                 const F2Stage& st = P.st[0];
                 for (int c0 = 0; c0 < P.nX; c0 += 7) {
                     const int c1 = min(P.nX, c0 + 7);
-                    for (int c = c0; c < c1; ++c) {
+                    float4 ra[2], rb[2];
+                    ldx(c0, ra); ldx(c0 + 1 < c1 ? c0 + 1 : P.nX, rb);
+                    auto chunk = [&](int c, float4 (&r)[2]) {
                         const int xs = (c - c0) % kF2XSlots;
                         if (c - c0 >= kF2XSlots) wait_x(xs);
-                        stage_x(c, xs);
+                        stx(xs, r);
+                        ldx(c + 2 < c1 ? c + 2 : P.nX, r);
                         publish();
                         if (tid == 0) {
                             tc_fence_after();
@@ -570,29 +584,21 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
                                   opnd_mn(smem_u32(xslot(xs)), 8192, 8192), 4, 64, false);
                             mma_commit(&xbar[xs]);
                         }
+                    };
+                    for (int c = c0; c < c1; c += 2) {
+                        chunk(c, ra);
+                        if (c + 1 < c1) chunk(c + 1, rb);
                     }
                     for (int c = max(c0, c1 - kF2XSlots); c < c1; ++c) wait_x((c - c0) % kF2XSlots);
                     stamp();
                     if (32 * q < st.out) {
                         const bool valid = frow < st.out;
-                        float* dw = part + st.seg_w[0] + frow;
-                        const int ng = (c1 - c0) * 4, g0 = h ? (ng + 1) >> 1 : 0, g1 = h ? ng : (ng + 1) >> 1;
-                        for (int g = g0; g < g1; ++g) {
+                        for (int g = h; g < (c1 - c0) * 4; g += 4) {
                             float v[16];
                             tmem_ld16(t_lane + 16 * g, v);
-                            if (valid) {
-#pragma unroll
-                                for (int j = 0; j < 16; ++j) {
-                                    const int i = 64 * c0 + 16 * g + j;
-                                    if (i < D) { float* d = dw + (long)i * st.out; *d = tile_iter ? *d + v[j] : v[j]; }
-                                }
-                            }
+                            if (valid) put_dw(part + st.seg_w[0] + frow, st.out, 64 * c0 + 16 * g, D, v);
                         }
-                        if (valid && h == 0 && c0 == 0) {
-                            float* d = part + st.seg_b[0] + frow;
-                            const float t = s_db[frow] + s_db[128 + frow];
-                            *d = tile_iter ? *d + t : t;
-                        }
+                        if (valid && h == 0 && c0 == 0) put_db(part + st.seg_b[0] + frow, 0, frow);
                     }
                     publish();
                 }
@@ -600,7 +606,11 @@ __global__ void __launch_bounds__(256, 1) fused2_kernel(const __grid_constant__ 
         }
         stamp();
         // =========================================================== per-jet losses (models.py:123-132) and batch sums
-        if (tid == 0) { wget(nops - 1); wdone(nops - 1); gbase += nops; }
+        if (tid == 0) { wget(nops - 1); gbase += nops; }
+        if (producer) {                                                  // trailing dummies / shrunk ops have no consumer
+            for (int k = (a.train ? P.op_bwd[1] : n_fwd_ops - 1) + 1; k < nops; ++k) wdone_dummy(k);
+            gbase += nops;
+        }
         __syncthreads();
         if (tid < 64) {
             const int j = tid;

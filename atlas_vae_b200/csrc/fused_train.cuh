@@ -524,17 +524,31 @@ struct AdamImgArgs {
     unsigned char* wimg; const int* pos;                    // pos: [4][n] byte offsets (fwd hi, fwd lo, dx hi, dx lo), -1 = none
 };
 
-__global__ void adam_img_kernel(AdamImgArgs a) {
-    long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.n) return;
+// block = (32 parameters) x (8 slices of the partial-gradient list): slice y sums parts y, y+8, ... in order, the eight
+// slice sums are combined in a fixed tree, so the result does not depend on scheduling.
+__global__ void __launch_bounds__(256) adam_img_kernel(AdamImgArgs a) {
+    __shared__ float red[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const long i = (long)blockIdx.x * 32 + tx;
+    const bool in = i < a.n;
+    float g = 0.f;
+    if (a.parts) {
+        if (in) {
+            float g0 = 0.f, g1 = 0.f;
+            int sidx = ty;
+            for (; sidx + 8 < a.n_parts; sidx += 16) { g0 += a.parts[(long)sidx * a.part_stride + i]; g1 += a.parts[(long)(sidx + 8) * a.part_stride + i]; }
+            if (sidx < a.n_parts) g0 += a.parts[(long)sidx * a.part_stride + i];
+            g = g0 + g1;
+        }
+        red[ty][tx] = g;
+        __syncthreads();
+        if (ty == 0) g = ((red[0][tx] + red[1][tx]) + (red[2][tx] + red[3][tx])) + ((red[4][tx] + red[5][tx]) + (red[6][tx] + red[7][tx]));
+    }
+    if (ty != 0 || !in) return;
     float th = a.theta[i];
     if (a.parts || a.grad_in) {
-        float g;
-        if (a.parts) {
-            g = 0.f;
-            for (int s = 0; s < a.n_parts; ++s) g += a.parts[(long)s * a.part_stride + i];
-            if (a.grad_out) a.grad_out[i] = g;
-        } else g = a.grad_in[i];
+        if (a.parts) { if (a.grad_out) a.grad_out[i] = g; }
+        else g = a.grad_in[i];
         if (a.apply) {
             g = clipv(g);
             float m = a.m[i], v = a.v[i];

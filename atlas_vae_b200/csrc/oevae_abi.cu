@@ -149,7 +149,7 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
     if (f.img_dirty) {                                      // weights were set from the host: rebuild the bf16 images
         AdamImgArgs ai{};
         ai.theta = theta; ai.n = P; ai.wimg = f.wimg; ai.pos = f.pos;
-        { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, 256), 256, 0, s>>>(ai); }
+        { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, 32), 256, 0, s>>>(ai); }
         CKL();
         f.img_dirty = false;
     }
@@ -166,7 +166,7 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
         ++calls;
         b.dbg = dbg ? dbg_buf : nullptr;
         const int grid2 = std::min(b.n_tiles, n_sm);
-        { PROF(want_grad ? "fused_train" : "fused_eval", s); fused2_kernel<<<grid2, 256, f.plan2.smem_bytes, s>>>(f.plan2, b); }
+        { PROF(want_grad ? "fused_train" : "fused_eval", s); fused2_kernel<<<grid2, kF2Threads, f.plan2.smem_bytes, s>>>(f.plan2, b); }
         CKL();
         if (want_grad) { f.last_fused = true; f.last_grid = grid2; }
         if (dbg) {
@@ -466,7 +466,7 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
         ai.theta = theta; ai.m = m; ai.v = v; ai.n = P;
         ai.alpha = a.alpha; ai.b1 = a.b1; ai.b2 = a.b2; ai.eps = a.eps; ai.apply = apply;
         ai.wimg = fz->wimg; ai.pos = fz->pos;
-        { PROF("adam", s); adam_img_kernel<<<cdiv(P, 256), 256, 0, s>>>(ai); }
+        { PROF("adam", s); adam_img_kernel<<<cdiv(P, 32), 256, 0, s>>>(ai); }
         CKL();
         if (apply) fz->img_dirty = false;
         return 0;
