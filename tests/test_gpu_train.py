@@ -166,3 +166,20 @@ def test_errors_are_reported():
         dev.loss_and_grad(np.zeros((4, 6), np.float32), np.ones(4, np.float32))
     with pytest.raises(OevaeError):                       # x_ood without w_ood
         dev.eval_losses(np.zeros((4, 6), np.float32), np.ones(4, np.float32), np.zeros((4, 6), np.float32), None, np.zeros((4, 4), np.float32))
+
+
+def test_vae_driver_end_to_end(tmp_path):
+    """python -m atlas_vae_b200.vae on BASELINE config 1 shapes (tiny sample): train, score, cuts, histograms."""
+    import pickle
+    from atlas_vae_b200 import vae as drv
+    out = str(tmp_path / 'o')
+    rc = drv.main(['--n_train', '4000', '--n_valid', '3000', '--n_sig', '1000', '--n_const', '20', '--n_dims', '4',
+                   '--FC_layers', '80', '40', '10', '--batch_size', '1000', '--n_epochs', '2', '--beta', '1', '--apply_cuts', 'ON',
+                   '--output_dir', out])
+    assert rc == 0
+    hist = pickle.load(open(out + '/history.pkl', 'rb'))
+    assert len(hist['Train loss']) == 2 and np.isfinite(hist['Train loss']).all() and hist['Train loss'][1] < hist['Train loss'][0]
+    res = pickle.load(open(out + '/plots/cut_histograms.pkl', 'rb'))
+    assert 'best_gain' in res and res['bkg_eff_1e+01']['n_pass'] > 0
+    e, counts, _ = res['bkg_eff_1e+01']['m_uncut']
+    assert counts.sum() == 4000                                   # every finite jet lands in a mass bin

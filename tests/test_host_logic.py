@@ -61,3 +61,17 @@ def test_synthetic_jets_are_deterministic():
     assert bool((v[:, :, 0] >= 0).all())
     m2 = v[:, :, 0] ** 2 - (v[:, :, 1:] ** 2).sum(-1)
     assert float(m2.abs().max()) < 1e-1 * float((v[:, :, 0] ** 2).max())          # massless constituents
+
+
+def test_cli_accepts_reference_flags_and_readme_aliases():
+    """vae.py:16-66 flag names and the README's older spellings land on the same fields."""
+    from atlas_vae_b200.vae import parse_args
+    a = parse_args(['--n_train', '1e5', '--n_const', '20', '--n_dims', '4', '--FC_layers', '80', '40', '10', '--batch_size', '5e3',
+                    '--beta', '1', '--apply_cuts', 'ON', '--output_dir', 'o'])
+    assert (a.n_train, a.batch_size, a.FC_layers, a.apply_cuts) == (100000, 5000, [80, 40, 10], 'ON')
+    assert a.model_out == 'o/model.h5' and a.hist_file == 'o/history.pkl'
+    b = parse_args(['--n_constituents', '20', '--FCN_neurons', '80', '40', '--latent_dim', '10', '--apply_cut', 'ON',
+                    '--n_test', '2e5', '--n_W', '3e5', '--n_top', '4e5', '--patience', '5', '--n_gpus', '8'])
+    assert b.n_const == 20 and b.FC_layers == [80, 40, 10] and b.apply_cuts == 'ON'
+    assert (b.n_valid, b.n_OoD, b.n_sig, b.patience, b.n_gpus) == (200000, 300000, 400000, 5, 8)
+    assert parse_args([]).FC_layers == [80, 40, 20, 10] and parse_args(['--latent_dim', '6']).FC_layers == [80, 40, 20, 6]
