@@ -59,6 +59,8 @@ SIGNATURES = {
     'oevae_probe_latency': (C.c_int, [_i32, _i32, C.POINTER(_i64), _i32]),
     'oevae_probe_issue': (C.c_int, [_i32, _i32, _i32, _i32, _i32, C.POINTER(_i64), _i32]),
     'oevae_probe_bulk': (C.c_int, [_i32, _i32, _i32, _i32, C.POINTER(_i64), _i32]),
+    'oevae_host_register': (C.c_int, [_vp, _i64]),
+    'oevae_host_unregister': (C.c_int, [_vp]),
     'oevae_launch_count': (_i64, []),
     'oevae_profile_enable': (C.c_int, [_i32]),
     'oevae_profile_report': (C.c_int, [C.c_char_p, _i32]),

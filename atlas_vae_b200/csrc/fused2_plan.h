@@ -53,6 +53,7 @@ struct F2Plan {
     uint32_t op_off[kF2MaxOps], op_bytes[kF2MaxOps];
     F2Stage st[kF2MaxStages];
     long P, Ppad;
+    int n_dwbuf, dw_cols;            // fused3: dW^T accumulators in TMEM columns [320, 320 + n_dwbuf * dw_cols)
 };
 
 }  // namespace oevae

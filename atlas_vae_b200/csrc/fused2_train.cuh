@@ -121,6 +121,12 @@ __device__ __forceinline__ float transpose_reduce16(float* v, int lane) {
     }
     return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
 }
+// nan_to_num(p * log2(p / q)) of utils.py:347-350 on the SFU: approximate reciprocal + lg2.approx (abs error of the log
+// <= 2^-22 near 1, 2 ulp elsewhere); p/q < 0 -> NaN -> 0, q = 0 -> +-inf -> +-FLT_MAX or NaN -> 0 exactly as NumPy's
+__device__ __forceinline__ float kld_term_fast(float p, float q) {
+    const float t = p * __log2f(__fdividef(p, q));
+    return (t != t) ? 0.f : fminf(fmaxf(t, -3.402823466e+38f), 3.402823466e+38f);
+}
 }  // namespace f2
 
 struct F2Args {
@@ -132,23 +138,30 @@ struct F2Args {
     float beta;
     unsigned long long seed, row_offset; unsigned int step;
     long long* dbg;
+    // SCORE instantiation only (anomaly scoring, vae.py:163-167 + utils.py:346-386): nullable [B] outputs
+    float* s_mse; float* s_mae; float* s_kld; float* s_jsd; float* s_lat; unsigned char* s_fin;
+    float* s_xhat;                                          // nullable [B, D]: clip_values(X_hat) of the pass (vae.py:165)
 };
 
 
 constexpr int kF2Threads = 512;                             // 16 warps: lane quarter q = warp & 3, column group h = warp >> 2
 
+// SCORE = false: training step (a.train) / get_losses (eval).  SCORE = true: forward only, and the output epilogue
+// accumulates loss_function's MSE / MAE / KLD / JSD between X and clip_values(X_hat) instead of the training loss.
+template <bool SCORE>
 __global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_constant__ F2Plan P, F2Args a) {
+    const bool is_train = !SCORE && a.train;
     using namespace umma;
     using namespace f2;
     extern __shared__ unsigned char smem_dyn[];
-    __shared__ uint64_t mma_bar, y_bar, xbar[kF2XSlots], wbar[kF2WSlots];
+    __shared__ uint64_t mma_bar, y_bar[2], xbar[kF2XSlots], wbar[kF2WSlots];
     __shared__ uint32_t tmem_base_s;
     unsigned char* sm = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, q = warp & 3, h = warp >> 2;
     const int frow = 32 * q + lane;                          // TMEM lane = feature row owned by this thread
     const int jc0 = 16 * h;                                  // first of the 16 jet columns owned by this thread
     const int n = P.n, D = P.D, L = P.L, so = 2 * n + 1;
-    const int nops = a.train ? P.n_op_train : P.n_op_eval;
+    const int nops = is_train ? P.n_op_train : P.n_op_eval;
     const int n_fwd_ops = P.op_first[so] + P.nX;
 
     float* s_w = reinterpret_cast<float*>(sm + P.scratch_off);        // [64] jet weights (0 for rows past the batch)
@@ -165,7 +178,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_cons
 
     // ---- one-time setup
     if (tid == 0) {
-        mbar_init(&mma_bar, 1); mbar_init(&y_bar, 1);
+        mbar_init(&mma_bar, 1); mbar_init(&y_bar[0], 1); mbar_init(&y_bar[1], 1);
         for (int i = 0; i < kF2XSlots; ++i) mbar_init(&xbar[i], 1);
         for (int i = 0; i < kF2WSlots; ++i) mbar_init(&wbar[i], 1);
         mbar_fence_init();
@@ -190,7 +203,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_cons
     auto refill = [&]() {
         while (w_issued < w_total && w_issued < w_done + kF2WSlots) {
             const int k = w_issued % nops, s = w_issued & (kF2WSlots - 1);
-            const uint32_t bytes = (!a.train && k >= n_fwd_ops) ? 16u : P.op_bytes[k];
+            const uint32_t bytes = (!is_train && k >= n_fwd_ops) ? 16u : P.op_bytes[k];
             mbar_expect_tx(&wbar[s], bytes);
             bulk_g2s(wslot(w_issued), a.wimg + P.op_off[k], bytes, &wbar[s]);
             ++w_issued;
@@ -206,7 +219,9 @@ __global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_cons
 
     uint32_t ph_m = 0, ph_y = 0, ph_x = 0;
     auto wait_mma = [&]() { mbar_wait(&mma_bar, ph_m); ph_m ^= 1u; tc_fence_after(); };
-    auto wait_y = [&]() { mbar_wait(&y_bar, ph_y); ph_y ^= 1u; tc_fence_after(); };
+    // one barrier per accumulator slot: y(c+1) is issued by thread 0 right after ITS wait on y(c), so a single barrier could
+    // complete twice before a slow warp has polled it once (parity aliasing)
+    auto wait_y = [&](int c) { mbar_wait(&y_bar[c & 1], (ph_y >> (c & 1)) & 1u); ph_y ^= 1u << (c & 1); tc_fence_after(); };
     auto wait_x = [&](int s) { mbar_wait(&xbar[s], (ph_x >> s) & 1u); ph_x ^= 1u << s; tc_fence_after(); };
     auto publish = [&]() { fence_async_smem(); tc_fence_before(); __syncthreads(); };   // smem writes + TMEM reads done
 
@@ -220,7 +235,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_cons
         const int nvalid = (int)min((long)kF2Jets, a.B - row0);
         float* part = a.parts + (long)blockIdx.x * P.Ppad;
         w_next = 0;
-        if (tid < 64) s_w[tid] = tid < nvalid ? a.w[row0 + tid] : 0.f;
+        if (tid < 64) s_w[tid] = (tid < nvalid && !SCORE) ? a.w[row0 + tid] : 0.f;
         for (int pf = tile_iter ? 1 : 0; pf < 2; ++pf) {   // pull the next tile's rows of X (and the first tile's own) towards L2
             const long nrow0 = row0 + (long)pf * gridDim.x * kF2Jets;
             const long nbytes = min((long)kF2Jets, a.B - nrow0) * D * 4;
@@ -422,8 +437,13 @@ __global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_cons
         }
         // =========================================================== output layer in 128-feature chunks
         float rec_acc[16];
+        float sc_mae[SCORE ? 16 : 1], sc_kl[SCORE ? 16 : 1], sc_js[SCORE ? 16 : 1];   // rec_acc doubles as the MSE sum
 #pragma unroll
         for (int j = 0; j < 16; ++j) rec_acc[j] = 0.f;
+        if constexpr (SCORE) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { sc_mae[j] = 0.f; sc_kl[j] = 0.f; sc_js[j] = 0.f; }
+        }
         {
             const F2Stage& st = P.st[so];
             const uint32_t part_b = st.rows * 128;
@@ -435,7 +455,7 @@ __global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_cons
                 tc_fence_after();
                 issue(tm + T_Y0 + 64 * (c & 1), opnd_mn(wb, part_b, P.wslot_bytes),
                       opnd_mn(smem_u32(tile_hi(2 * n)), P.tile_rows[2 * n] * 128, 8192), st.kin >> 4, kF2Jets, false);
-                mma_commit(&y_bar);
+                mma_commit(&y_bar[c & 1]);
             };
             if (producer && ob - 1 != P.op_first[2 * n]) wdone_dummy(ob - 1);                   // alignment dummy before the output ops
             if (tid == 0) issue_y(0);
@@ -448,9 +468,24 @@ __global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_cons
 #pragma unroll
                 for (int j = 0; j < 16; ++j) xv[j] = (valid && jc0 + j < nvalid) ? __ldg(a.x + (row0 + jc0 + j) * D + f) : 0.f;
                 const float bias = valid ? __ldg(a.theta + st.seg_b[0] + f) : 0.f;
-                wait_y();
+                wait_y(c);
                 if (tid == 0 && c + 1 < P.nC) issue_y(c + 1);
                 stamp();
+                if constexpr (SCORE) {
+                    // loss_function (utils.py:346-375) terms of this thread's feature for its 16 jets; Q = clip_values(X_hat)
+                    float y[16];
+                    tmem_ld16(t_lane + T_Y0 + 64 * (c & 1) + jc0, y);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        if (valid && jc0 + j < nvalid) {
+                            const float p = xv[j], qv = clipv(y[j] + bias), d = p - qv;
+                            rec_acc[j] += d * d; sc_mae[j] += fabsf(d);
+                            if (a.s_kld) sc_kl[j] += kld_term_fast(p, qv);
+                            if (a.s_jsd) { const float mm = (p + qv) / 2.f; sc_js[j] += (kld_term_fast(p, mm) + kld_term_fast(qv, mm)) / 2.f; }
+                                if (a.s_xhat) a.s_xhat[(row0 + jc0 + j) * D + f] = qv;
+                        }
+                    }
+                } else
                 // reconstruction loss (models.py:66,72-78) and its gradient through clip_values
                 {
                     float dbs = 0.f;
@@ -467,10 +502,10 @@ __global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_cons
                         }
                         dbs += gy; y[j] = gy;
                     }
-                    if (a.train) { store16(gy_hi, gy_lo, frow, jc0, y); db_at(2 + (c & 1), h, frow) = dbs; }
+                    if (is_train) { store16(gy_hi, gy_lo, frow, jc0, y); db_at(2 + (c & 1), h, frow) = dbs; }
                 }
                 stamp();
-                if (!a.train) {
+                if (!is_train) {
                     tc_fence_before();
                     __syncthreads();                                    // accumulator reads done before chunk c+2 overwrites it
                     if (producer) wdone(last_op);
@@ -505,11 +540,15 @@ __global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_cons
             }
             const float rs = transpose_reduce16(rec_acc, lane);
             if (lane < 16) s_rec[q * 64 + jc0 + lane] = rs;
-            if (a.train) { epi_grad(so); publish(); }
+            if constexpr (SCORE) {                                       // s_db is free outside training: [3][4 quarters][64 jets]
+                const float r1 = transpose_reduce16(sc_mae, lane), r2 = transpose_reduce16(sc_kl, lane), r3 = transpose_reduce16(sc_js, lane);
+                if (lane < 16) { s_db[q * 64 + jc0 + lane] = r1; s_db[256 + q * 64 + jc0 + lane] = r2; s_db[512 + q * 64 + jc0 + lane] = r3; }
+            }
+            if (is_train) { epi_grad(so); publish(); }
             stamp();
         }
         // =========================================================== backward chain: stages 2n .. 1
-        if (a.train) {
+        if (is_train) {
             for (int s = 2 * n; s >= 1; --s) {
                 const F2Stage& st = P.st[s];
                 if (tid == 0) {
@@ -607,12 +646,25 @@ __global__ void __launch_bounds__(kF2Threads, 1) fused2_kernel(const __grid_cons
         stamp();
         // =========================================================== per-jet losses (models.py:123-132) and batch sums
         if (tid == 0) { wget(nops - 1); gbase += nops; }
-        if (producer) {                                                  // trailing dummies / shrunk ops have no consumer
-            for (int k = (a.train ? P.op_bwd[1] : n_fwd_ops - 1) + 1; k < nops; ++k) wdone_dummy(k);
+        __syncthreads();
+        // trailing dummies / shrunk ops have no consumer; the producer frees their slots only after thread 0 has seen every
+        // arrival of this tile (a slot refilled earlier could complete twice before thread 0 polls it: parity aliasing)
+        if (producer) {
+            for (int k = (is_train ? P.op_bwd[1] : n_fwd_ops - 1) + 1; k < nops; ++k) wdone_dummy(k);
             gbase += nops;
         }
-        __syncthreads();
-        if (tid < 64) {
+        if (SCORE) {
+            if (tid < nvalid) {
+                const int j = tid;
+                auto q4 = [&](const float* b) { return (b[j] + b[64 + j]) + (b[128 + j] + b[192 + j]); };
+                if (a.s_mse) a.s_mse[row0 + j] = q4(s_rec) / (float)D;
+                if (a.s_mae) a.s_mae[row0 + j] = q4(s_db) / (float)D;
+                if (a.s_kld) a.s_kld[row0 + j] = q4(s_db + 256);
+                if (a.s_jsd) a.s_jsd[row0 + j] = q4(s_db + 512);
+                if (a.s_lat) a.s_lat[row0 + j] = isfinite(s_kld[j]) ? s_kld[j] : 0.f;       // latent_loss, utils.py:378-386
+                if (a.s_fin) a.s_fin[row0 + j] = 1;                                         // clip_values leaves no non-finite X_hat
+            }
+        } else if (tid < 64) {
             const int j = tid;
             float lr_ = 0.f, lk = 0.f, tot = 0.f;
             if (j < nvalid) {

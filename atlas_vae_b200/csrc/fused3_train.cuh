@@ -1,0 +1,704 @@
+// Warp-specialised version of the feature-major fused OE-VAE step (same plan, shared-memory layout, weight image and
+// arithmetic as fused2_train.cuh; see that file and fused2_plan.h for the layouts).
+//   forward + losses  models.py:30-36,49-52,62-69,72-85,123-132      gradient of the batch SUM  models.py:183
+//   scoring (SCORE)   vae.py:163-167, utils.py:346-386
+// Roles (576 threads):
+//   warps 0..15  workers: stage X chunks (fp32 -> bf16 hi/lo), run every epilogue (bias/ReLU/split, Sampling + KLD, loss and
+//                its gradient, ReLU masks), drain the dW^T accumulators to the partial-gradient slice
+//   warp 16      MMA issuer (one lane): waits for operands on mbarriers, issues tcgen05.mma, signals with tcgen05.commit
+//   warp 17      weight producer (one lane): cp.async.bulk of the pre-swizzled weight ops through a 4-slot ring
+// No __syncthreads inside a tile: every hand-off is an mbarrier, so the issuer runs ahead of the epilogues, X staging
+// overlaps the layer-0 MMAs, and the dW^T drains overlap the next stage's MMAs (two dW^T accumulators).
+//
+// TMEM columns: [0,64) mu, [64,128) log_var, [128,192) chain accumulator, [192,256) / [256,320) output-layer chunk
+// accumulators (slot 0 doubles as the second layer-0 accumulator), [320,512) dW^T accumulators (one or two).
+#pragma once
+#include "fused2_train.cuh"
+
+namespace oevae {
+
+constexpr int kF3Workers = 16;                               // worker warps
+constexpr int kF3Threads = (kF3Workers + 2) * 32;
+constexpr uint32_t kF3_TDW = 320;
+
+namespace f3 {
+using namespace umma;
+// Single-thread tcgen05 instructions issued from WARP-UNIFORM code: every lane of the issuer warp runs the same control
+// flow with the same values and elect.sync picks the lane that executes the instruction.  The operands then stay in
+// uniform registers; issuing from a divergent `if (lane == 0)` region makes ptxas wrap every MMA in an
+// ELECT / 7x R2UR.BROADCAST / BRA.U.ANY loop (~110 cycles per MMA measured, against ~48 of operand fetch).
+__device__ __forceinline__ void mma_e(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, pe;\n\t"
+        "elect.sync _|pe, 0xffffffff;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void commit_e(uint64_t* bar) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred pe;\n\t"
+        "elect.sync _|pe, 0xffffffff;\n\t"
+        "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t"
+        "}" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void arrive_e(uint64_t* bar) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred pe;\n\t"
+        ".reg .b64 st;\n\t"
+        "elect.sync _|pe, 0xffffffff;\n\t"
+        "@pe mbarrier.arrive.shared::cta.b64 st, [%0];\n\t"
+        "}" ::"r"(smem_u32(bar)) : "memory");
+}
+// D[128 x N] (+)= A * B over nk k-steps, bf16x3 (Ahi*Bhi + Ahi*Blo + Alo*Bhi); see f2::issue_core
+__device__ __forceinline__ void issue_e(uint32_t d, const f2::Opnd& A, const f2::Opnd& B, int nk, int N, bool acc) {
+    uint64_t ah = f2::desc(A, 0, false), al = f2::desc(A, 0, true), bh = f2::desc(B, 0, false), bl = f2::desc(B, 0, true);
+    const uint32_t a_step = A.kstep >> 4, b_step = B.kstep >> 4, idesc = idesc_bf16_major(128, N, A.mn, B.mn);
+    uint32_t ac = acc ? 1u : 0u;
+#pragma unroll 1
+    for (int ks = 0; ks < nk; ++ks) {
+        mma_e(d, ah, bh, idesc, ac);
+        mma_e(d, ah, bl, idesc, 1u);
+        mma_e(d, al, bh, idesc, 1u);
+        ac = 1u;
+        ah += a_step; al += a_step; bh += b_step; bl += b_step;
+    }
+}
+// same, k-steps alternating between two accumulators (d0 even, d1 odd); the epilogue adds the two
+__device__ __forceinline__ void issue2_e(uint32_t d0, uint32_t d1, const f2::Opnd& A, const f2::Opnd& B, int nk, int N, bool acc0, bool acc1) {
+    uint64_t ah = f2::desc(A, 0, false), al = f2::desc(A, 0, true), bh = f2::desc(B, 0, false), bl = f2::desc(B, 0, true);
+    const uint32_t a_step = A.kstep >> 4, b_step = B.kstep >> 4, idesc = idesc_bf16_major(128, N, A.mn, B.mn);
+    uint32_t ac0 = acc0 ? 1u : 0u, ac1 = acc1 ? 1u : 0u;
+#pragma unroll 1
+    for (int ks = 0; ks < nk; ++ks) {
+        const uint32_t d = (ks & 1) ? d1 : d0, ac = (ks & 1) ? ac1 : ac0;
+        mma_e(d, ah, bh, idesc, ac);
+        mma_e(d, ah, bl, idesc, 1u);
+        mma_e(d, al, bh, idesc, 1u);
+        if (ks & 1) ac1 = 1u; else ac0 = 1u;
+        ah += a_step; al += a_step; bh += b_step; bl += b_step;
+    }
+}
+__device__ __forceinline__ void worker_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kF3Workers * 32) : "memory"); }
+// every lane has fenced its own writes / TMEM reads; one arrival per warp
+__device__ __forceinline__ void warp_arrive(uint64_t* bar, int lane) {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar);
+}
+}  // namespace f3
+
+template <bool SCORE>
+__global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_constant__ F2Plan P, F2Args a) {
+    using namespace umma;
+    using namespace f2;
+    using namespace f3;
+    const bool is_train = !SCORE && a.train;
+    extern __shared__ unsigned char smem_dyn[];
+    __shared__ uint64_t wfull[kF2WSlots], wempty[kF2WSlots], xfull[kF2XSlots], xempty[kF2XSlots];
+    __shared__ uint64_t yfull[2], yempty[2], gyfull, gyempty, dwfull[2], dwempty[2];
+    __shared__ uint64_t acc[kF2MaxStages], tready[kF2MaxStages], accB[kF2MaxStages], gready[kF2MaxStages];
+    __shared__ uint32_t tmem_base_s;
+    unsigned char* sm = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler: role branches do not diverge
+    const int q = warp & 3, h = (warp >> 2) & 3;
+    const int frow = 32 * q + lane;                          // TMEM lane = feature row owned by this worker thread
+    const int jc0 = 16 * h;                                  // first of the 16 jet columns owned by this worker thread
+    const int n = P.n, D = P.D, L = P.L, so = 2 * n + 1;
+    const int nops = is_train ? P.n_op_train : P.n_op_eval;
+    const int n_fwd_ops = P.op_first[so] + P.nX;
+    const int ndw = P.n_dwbuf, dwc = P.dw_cols;             // dW^T accumulators and their column pitch
+
+    float* s_w = reinterpret_cast<float*>(sm + P.scratch_off);        // [64] jet weights (0 for rows past the batch)
+    float* s_rec = s_w + 64;                                           // [4][64] per lane-quarter reconstruction sums
+    float* s_kld = s_rec + 256;                                        // [64]
+    float* s_db = s_kld + 64;                                          // [6 buffers][4 column groups][128] bias-gradient parts:
+                                                                       // chain stage k -> buffer k % 3, output chunk c -> 3 + c % 3 (a buffer
+                                                                       // is rewritten two worker_sync()s after its last reader)
+    float* s_eps = s_db + 3072;                                        // [L][64]
+    auto tile_hi = [&](int k) { return sm + P.tile_off[k]; };
+    auto tile_lo = [&](int k) { return sm + P.tile_off[k] + P.tile_rows[k] * 128; };
+    auto xslot = [&](int s) { return sm + P.s_off + s * 16384; };      // hi 8 KB, lo 8 KB
+    unsigned char* gy_hi = sm + P.s_off; unsigned char* gy_lo = gy_hi + 16384;
+    auto db_at = [&](int buf, int hh, int row) -> float& { return s_db[(buf * 4 + hh) * 128 + row]; };
+
+    // ---- one-time setup
+    if (tid == 0) {
+        for (int i = 0; i < kF2WSlots; ++i) { mbar_init(&wfull[i], 1); mbar_init(&wempty[i], 1); }
+        for (int i = 0; i < kF2XSlots; ++i) { mbar_init(&xfull[i], kF3Workers); mbar_init(&xempty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&yfull[i], 1); mbar_init(&yempty[i], kF3Workers); mbar_init(&dwfull[i], 1); mbar_init(&dwempty[i], kF3Workers); }
+        mbar_init(&gyfull, kF3Workers); mbar_init(&gyempty, 1);
+        for (int i = 0; i < kF2MaxStages; ++i) { mbar_init(&acc[i], 1); mbar_init(&tready[i], kF3Workers); mbar_init(&accB[i], 1); mbar_init(&gready[i], kF3Workers); }
+        mbar_fence_init();
+    }
+    for (int i = tid * 16; i < P.zero_bytes; i += kF3Threads * 16) *reinterpret_cast<uint4*>(sm + i) = make_uint4(0, 0, 0, 0);
+    if (warp == 0) tmem_alloc(&tmem_base_s, 512);
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tm = tmem_base_s;
+    const uint32_t t_lane = tm + ((uint32_t)(32 * q) << 16);
+    const int my_tiles = ((int)blockIdx.x < a.n_tiles) ? (a.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+
+    int n_dbg = 0;
+    auto stamp = [&]() { if (a.dbg && blockIdx.x == 0 && tid == 0 && n_dbg < 255) a.dbg[1 + n_dbg++] = clock64(); };
+    stamp();
+    int n_dbg2 = 0;                                          // MMA issuer's own stamps: a.dbg[256] = count, [257..511]
+    auto stamp2 = [&]() { if (a.dbg && blockIdx.x == 0 && n_dbg2 < 255) a.dbg[257 + n_dbg2++] = clock64(); };
+
+    if (warp == kF3Workers + 1) {
+        // ======================================================================================= weight producer
+        if (lane == 0) {
+            const long total = (long)my_tiles * nops;
+            for (long g = 0; g < total; ++g) {
+                const int slot = (int)(g & (kF2WSlots - 1)), k = (int)(g % nops);
+                if (g >= kF2WSlots) mbar_wait(&wempty[slot], (uint32_t)(((g >> 2) - 1) & 1));
+                const uint32_t bytes = (!is_train && k >= n_fwd_ops) ? 16u : P.op_bytes[k];
+                mbar_expect_tx(&wfull[slot], bytes);
+                bulk_g2s(sm + P.wring_off + slot * P.wslot_bytes, a.wimg + P.op_off[k], bytes, &wfull[slot]);
+            }
+        }
+        __syncwarp();
+    } else if (warp == kF3Workers) {
+        // ======================================================================================= MMA issuer
+        // every lane runs this code with identical values (see f3::mma_e)
+        {
+            const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base_s, 0);
+            const uint32_t smu = __shfl_sync(0xffffffffu, smem_u32(sm), 0);      // shared-window address of the aligned base
+            auto tile_a = [&](int k) { return smu + (uint32_t)P.tile_off[k]; };
+            auto xslot_a = [&](uint32_t b) { return smu + (uint32_t)P.s_off + b * 16384u; };
+            const uint32_t gy_a = smu + (uint32_t)P.s_off;
+            long gbase = 0;                                  // ops consumed by earlier tiles
+            uint32_t xk = 0, yk = 0, gk = 0, dk = 0;         // cumulative uses of the X ring, y slots, g_y slot, dW^T accumulators
+            int tile_iter = 0;
+            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_iter) {
+                const uint32_t tp = (uint32_t)(tile_iter & 1);
+                int wseen = 0;
+                auto wslot_addr = [&](int k) { return smu + (uint32_t)P.wring_off + (uint32_t)((gbase + k) & (kF2WSlots - 1)) * (uint32_t)P.wslot_bytes; };
+                auto wget = [&](int k) -> uint32_t {        // all ops <= k of this tile have landed; returns the slot of op k
+                    for (; wseen <= k; ++wseen) mbar_wait(&wfull[(gbase + wseen) & (kF2WSlots - 1)], (uint32_t)(((gbase + wseen) >> 2) & 1));
+                    return wslot_addr(k);
+                };
+                auto wrel = [&](int k) { commit_e(&wempty[(gbase + k) & (kF2WSlots - 1)]); };   // slot free once the MMAs issued so far complete
+                auto wskip = [&](int k) { wget(k); arrive_e(&wempty[(gbase + k) & (kF2WSlots - 1)]); };   // op without a consumer
+                auto dw_acquire = [&]() -> uint32_t {        // next dW^T accumulator, drained by the workers
+                    const uint32_t b = dk % ndw, r = dk / ndw;
+                    if (r >= 1) { mbar_wait(&dwempty[b], (r - 1) & 1); tc_fence_after(); }
+                    return tm + kF3_TDW + b * dwc;
+                };
+                auto dw_commit = [&]() { commit_e(&dwfull[dk % ndw]); ++dk; };
+
+                // ---- forward, stage 0
+                {
+                    const F2Stage& st = P.st[0];
+                    for (int c = 0; c < P.nX; ++c, ++xk) {
+                        const uint32_t wb = wget(P.op_first[0] + c);
+                        mbar_wait(&xfull[xk & 1], (xk >> 1) & 1);
+                        tc_fence_after();
+                        stamp2();
+                        const int nk = min(4, (D - 64 * c + 15) >> 4);
+                        issue2_e(tm + T_CH, tm + T_Y0, opnd_k(wb, st.rows * 128), opnd_k(xslot_a(xk & 1), 8192), nk, kF2Jets, c > 0, c > 0);
+                        commit_e(&xempty[xk & 1]);
+                        wrel(P.op_first[0] + c);
+                        stamp2();
+                    }
+                    commit_e(&acc[0]);
+                }
+                // ---- forward chain
+                for (int s = 1; s <= 2 * n; ++s) {
+                    const F2Stage& st = P.st[s];
+                    const uint32_t wb = wget(P.op_first[s]);
+                    mbar_wait(&tready[s - 1], tp);
+                    tc_fence_after();
+                    stamp2();
+                    const uint32_t part_b = st.rows * 128;
+                    const Opnd B = opnd_mn(tile_a((s - 1)), P.tile_rows[s - 1] * 128, 8192);
+                    const int nk = st.kin >> 4;
+                    if (st.kind == 1) issue_e(tm + T_CH, opnd_mn(wb, part_b, part_b), B, nk, kF2Jets, false);
+                    else if (st.kind == 2) issue_e(tm + T_CH, opnd_k(wb, part_b), B, nk, kF2Jets, false);
+                    else {                                                   // heads: mean block, log_var block
+                        issue_e(tm + T_MU, opnd_mn(wb, 2 * part_b, part_b), B, nk, kF2Jets, false);
+                        issue_e(tm + T_LV, opnd_mn(wb + part_b, 2 * part_b, part_b), B, nk, kF2Jets, false);
+                    }
+                    wrel(P.op_first[s]);
+                    commit_e(&acc[s]);
+                    stamp2();
+                }
+                // ---- output layer (+ its backward products in training)
+                {
+                    const F2Stage& st = P.st[so];
+                    const uint32_t part_b = st.rows * 128;
+                    const int ob = P.op_first[so];
+                    if (ob - 1 != P.op_first[2 * n]) wskip(ob - 1);                           // alignment dummy
+                    mbar_wait(&tready[2 * n], tp);
+                    tc_fence_after();
+                    auto issue_y = [&](int c) {
+                        const uint32_t b = yk & 1, r = yk >> 1;
+                        if (r >= 1) { mbar_wait(&yempty[b], (r - 1) & 1); tc_fence_after(); }
+                        wget(ob + min(2 * c + 1, P.nX - 1));
+                        issue_e(tm + T_Y0 + 64 * b, opnd_mn(wslot_addr(ob + 2 * c), part_b, P.wslot_bytes),
+                              opnd_mn(tile_a((2 * n)), P.tile_rows[2 * n] * 128, 8192), st.kin >> 4, kF2Jets, false);
+                        commit_e(&yfull[b]);
+                        ++yk;
+                    };
+                    issue_y(0);
+                    for (int c = 0; c < P.nC; ++c) {
+                        if (c + 1 < P.nC) issue_y(c + 1);
+                        if (is_train) {
+                            mbar_wait(&gyfull, gk & 1);
+                            tc_fence_after();
+                            // g_dn += W_out[:, chunk] x g_y[chunk]   (A: K-major rows = in features; B: MN-major, K = chunk features)
+                            for (int b = 0; b < 2 && 2 * c + b < P.nX; ++b) {
+                                const int nk = min(4, (D - 64 * (2 * c + b) + 15) >> 4);
+                                issue_e(tm + T_CH, opnd_k(wslot_addr(ob + 2 * c + b), part_b), opnd_mn(gy_a + b * 8192, 16384, 8192), nk, kF2Jets, c > 0 || b > 0);
+                            }
+                            // dW_out^T[chunk] = g_y (A: K-major, K = jets) x d_n (B: K-major, N = in features)
+                            const uint32_t tdw = dw_acquire();
+                            issue_e(tdw, opnd_k(gy_a, 16384), opnd_k(tile_a((2 * n)), P.tile_rows[2 * n] * 128), 4, st.kin, false);
+                            commit_e(&gyempty); ++gk;
+                            dw_commit();
+                        }
+                        for (int b = 0; b < 2 && 2 * c + b < P.nX; ++b) wrel(ob + 2 * c + b);
+                    }
+                    if (is_train) commit_e(&accB[so]);
+                }
+                if (is_train) {
+                    // ---- backward chain: dW_s^T first (it reads H_{s-1}, which the workers overwrite with G_{s-1} next)
+                    for (int s = 2 * n; s >= 1; --s) {
+                        const F2Stage& st = P.st[s];
+                        const uint32_t wb = wget(P.op_bwd[s]);
+                        mbar_wait(&gready[s], tp);
+                        tc_fence_after();
+                        const uint32_t part_b = st.rows * 128;
+                        const uint32_t g_hi = tile_a((s)), g_lo = P.tile_rows[s] * 128;
+                        const Opnd G = opnd_mn(g_hi, g_lo, 8192);
+                        // G_{s-1}^T = W_s x G_s^T
+                        if (st.kind == 1) issue_e(tm + T_CH, opnd_k(wb, part_b), G, st.kout >> 4, kF2Jets, false);
+                        else if (st.kind == 2) issue_e(tm + T_CH, opnd_mn(wb, part_b, part_b), G, st.kout >> 4, kF2Jets, false);
+                        else {
+                            issue_e(tm + T_CH, opnd_k(wb, 2 * part_b), G, 1, kF2Jets, false);                                      // W_mu g_mu
+                            issue_e(tm + T_CH, opnd_k(wb + part_b, 2 * part_b), opnd_mn(g_hi + 2048, g_lo, 8192), 1, kF2Jets, true);   // + W_lv g_lv
+                        }
+                        // dW_s^T = G_s (A: K-major, K = jets) x H_{s-1} (B: K-major, N = in features)
+                        const uint32_t tdw = dw_acquire();
+                        issue_e(tdw, opnd_k(g_hi, g_lo), opnd_k(tile_a((s - 1)), P.tile_rows[s - 1] * 128), 4, st.kin, false);
+                        wrel(P.op_bwd[s]);
+                        commit_e(&accB[s]);
+                        dw_commit();
+                    }
+                    // ---- stage 0: dW_0^T = G_0 x X, one 64-feature chunk of re-staged X per dW^T accumulator
+                    mbar_wait(&gready[0], tp);
+                    tc_fence_after();
+                    for (int c = 0; c < P.nX; ++c, ++xk) {
+                        mbar_wait(&xfull[xk & 1], (xk >> 1) & 1);
+                        tc_fence_after();
+                        const uint32_t tdw = dw_acquire();
+                        issue_e(tdw, opnd_k(tile_a((0)), P.tile_rows[0] * 128), opnd_mn(xslot_a(xk & 1), 8192, 8192), 4, 64, false);
+                        commit_e(&xempty[xk & 1]);
+                        dw_commit();
+                    }
+                }
+                for (int k = (is_train ? P.op_bwd[1] : n_fwd_ops - 1) + 1; k < nops; ++k) wskip(k);   // trailing dummies / shrunk ops
+                gbase += nops;
+            }
+        }
+        __syncwarp();
+    } else {
+        // ======================================================================================= workers
+        uint32_t xk = 0, yk = 0, gk = 0, dk = 0;
+        int tile_iter = 0;
+        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_iter) {
+            const uint32_t tp = (uint32_t)(tile_iter & 1);
+            const long row0 = (long)tile * kF2Jets;
+            const int nvalid = (int)min((long)kF2Jets, a.B - row0);
+            float* part = a.parts + (long)blockIdx.x * P.Ppad;
+            if (tid < 64) s_w[tid] = (tid < nvalid && !SCORE) ? a.w[row0 + tid] : 0.f;
+            // reparameterisation noise of the tile -> s_eps[l][jet]: external eps, or one Philox counter (row, quad, step)
+            if (a.eps) {
+                for (int i = tid; i < 64 * L; i += kF3Workers * 32) {
+                    const int j = i / L, l = i - j * L;
+                    s_eps[l * 64 + j] = j < nvalid ? __ldg(a.eps + (row0 + j) * L + l) : 0.f;
+                }
+            } else if (tid < 64 * ((L + 3) >> 2)) {
+                const int j = tid & 63, quad = tid >> 6;
+                float nrm[4];
+                philox_normal4(a.seed, a.row_offset + (unsigned long long)(row0 + j), (unsigned)quad, a.step, nrm);
+#pragma unroll
+                for (int t = 0; t < 4; ++t) if (4 * quad + t < L) s_eps[(4 * quad + t) * 64 + j] = nrm[t];
+            }
+
+            // X chunk c = [64 jets x features 64c..64c+63]: ldx pulls this thread's two float4 into registers, stx writes them
+            // to a ring slot as bf16 hi/lo (K-major rows = jets)
+            auto ldx = [&](int c, float4 (&r)[2]) {
+#pragma unroll
+                for (int it = 0; it < 2; ++it) {
+                    const int idx = tid + kF3Workers * 32 * it, rr = idx >> 4, c4 = (idx & 15) << 2, col = 64 * c + c4;
+                    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (c < P.nX && rr < nvalid) {
+                        const float* p = a.x + (row0 + rr) * D + col;
+                        if (col + 3 < D && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) t = __ldg(reinterpret_cast<const float4*>(p));
+                        else {
+                            if (col < D) t.x = __ldg(p);
+                            if (col + 1 < D) t.y = __ldg(p + 1);
+                            if (col + 2 < D) t.z = __ldg(p + 2);
+                            if (col + 3 < D) t.w = __ldg(p + 3);
+                        }
+                    }
+                    r[it] = t;
+                }
+            };
+            auto stx = [&](int xs, const float4 (&r)[2]) {
+                unsigned char* hi = xslot(xs); unsigned char* lo = hi + 8192;
+#pragma unroll
+                for (int it = 0; it < 2; ++it) {
+                    const int idx = tid + kF3Workers * 32 * it, rr = idx >> 4, c4 = (idx & 15) << 2;
+                    uint32_t ha, la, hb, lb;
+                    split2(r[it].x, r[it].y, ha, la); split2(r[it].z, r[it].w, hb, lb);
+                    const uint32_t off = sw128_off(rr, c4);
+                    *reinterpret_cast<uint2*>(hi + off) = make_uint2(ha, hb);
+                    *reinterpret_cast<uint2*>(lo + off) = make_uint2(la, lb);
+                }
+            };
+            // stage chunk c into the next ring slot (waits until the MMAs that read the slot's previous content are done)
+            auto stage_x = [&](float4 (&r)[2]) {
+                const uint32_t b = xk & 1, rr = xk >> 1;
+                if (rr >= 1) mbar_wait(&xempty[b], (rr - 1) & 1);
+                stx(b, r);
+                fence_async_smem();
+                warp_arrive(&xfull[b], lane);
+                ++xk;
+            };
+            // smem tile writes + TMEM reads of this thread are done -> one arrival per warp
+            auto publish = [&](uint64_t* bar) { fence_async_smem(); tc_fence_before(); warp_arrive(bar, lane); };
+            auto wait_acc = [&](uint64_t* bar, uint32_t parity) { mbar_wait(bar, parity); tc_fence_after(); };
+
+            // chain accumulator -> bias + ReLU -> tile s (pad rows zero)
+            auto epi_act = [&](int s, float bias, bool two) {
+                const F2Stage& st = P.st[s];
+                if (32 * q >= P.tile_rows[s]) return;
+                float v[16];
+                tmem_ld16(t_lane + T_CH + jc0, v);
+                if (two) {
+                    float u[16];
+                    tmem_ld16(t_lane + T_Y0 + jc0, u);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] += u[j];
+                }
+                if (frow < P.tile_rows[s]) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const float t = v[j] + bias;
+                        v[j] = frow < st.out ? (st.relu ? fmaxf(t, 0.f) : t) : 0.f;
+                    }
+                    store16(tile_hi(s), tile_lo(s), frow, jc0, v);
+                }
+            };
+            auto bias_of = [&](int s) { return frow < P.st[s].out ? __ldg(a.theta + P.st[s].seg_b[0] + frow) : 0.f; };
+            // chain accumulator (dX of stage s) -> ReLU mask of H_{s-1} -> G_{s-1} over tile s-1, bias-gradient parts
+            auto epi_grad = [&](int s) {
+                const F2Stage& st = P.st[s];
+                const int rows = P.tile_rows[s - 1];
+                if (32 * q >= rows) return;
+                float v[16];
+                tmem_ld16(t_lane + T_CH + jc0, v);
+                if (frow < rows) {
+                    float dbs = 0.f;
+                    const uint32_t m = positive16(tile_hi(s - 1), frow, jc0);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) { v[j] = (((m >> j) & 1u) && frow < st.in) ? v[j] : 0.f; dbs += v[j]; }
+                    store16(tile_hi(s - 1), tile_lo(s - 1), frow, jc0, v);
+                    db_at((s - 1) % 3, h, frow) = dbs;
+                }
+            };
+            // 16 columns i0.. of a dW^T accumulator row -> rows i0.. of the Keras [in, ld] kernel gradient, column o
+            auto put_dw = [&](float* dw, long ld, int i0, int in, const float* v) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    if (i0 + j < in) { float* d = dw + (long)(i0 + j) * ld; *d = tile_iter ? *d + v[j] : v[j]; }
+                }
+            };
+            auto put_db = [&](float* d, int buf, int row) {
+                const float t = (db_at(buf, 0, row) + db_at(buf, 1, row)) + (db_at(buf, 2, row) + db_at(buf, 3, row));
+                *d = tile_iter ? *d + t : t;
+            };
+            // next dW^T accumulator to drain: wait for its MMAs; the caller reads it, then calls dw_release
+            auto dw_wait = [&]() -> uint32_t {
+                const uint32_t b = dk % ndw, r = dk / ndw;
+                mbar_wait(&dwfull[b], r & 1);
+                tc_fence_after();
+                return t_lane + kF3_TDW + b * dwc;
+            };
+            auto dw_release = [&]() { tc_fence_before(); warp_arrive(&dwempty[dk % ndw], lane); ++dk; };
+            // dW^T accumulator of chain stage s (lane = output feature, column = input feature) -> partial-gradient slice
+            auto drain_chain = [&](int s, int buf) {
+                const F2Stage& st = P.st[s];
+                worker_sync();                                           // bias-gradient parts of the four column groups are in s_db
+                const uint32_t tdw = dw_wait();
+                const int top = st.seg_lane0[st.nseg - 1] + st.seg_n[st.nseg - 1];
+                if (32 * q < top) {
+                    int sg = -1;
+#pragma unroll
+                    for (int k = 0; k < 2; ++k) if (k < st.nseg && frow >= st.seg_lane0[k] && frow < st.seg_lane0[k] + st.seg_n[k]) sg = k;
+                    const int o = sg >= 0 ? frow - st.seg_lane0[sg] : 0, ld = sg >= 0 ? st.seg_n[sg] : 0;
+                    float* dw = part + (sg >= 0 ? st.seg_w[sg] : 0) + o;
+                    for (int g = h; g < (st.kin >> 4); g += 4) {
+                        float v[16];
+                        tmem_ld16(tdw + 16 * g, v);
+                        if (sg >= 0) put_dw(dw, ld, 16 * g, st.in, v);
+                    }
+                    if (sg >= 0 && h == 0) put_db(part + st.seg_b[sg] + o, buf, frow);
+                }
+                dw_release();
+            };
+
+            worker_sync();                                               // s_w / s_eps visible; previous tile's scratch reads done
+            // =========================================================== forward, stage 0: X streamed in 64-feature chunks
+            {
+                float4 ra[2], rb[2];
+                ldx(0, ra); ldx(1, rb);
+                for (int c = 0; c < P.nX; c += 2) {
+                    stage_x(ra); ldx(c + 2, ra);
+                    if (c + 1 < P.nX) { stage_x(rb); ldx(c + 3, rb); }
+                }
+                const float bias0 = bias_of(0);
+                wait_acc(&acc[0], tp);
+                stamp();
+                epi_act(0, bias0, D > 16);
+                publish(&tready[0]);
+                stamp();
+            }
+            // =========================================================== forward chain: stages 1 .. 2n
+            for (int s = 1; s <= 2 * n; ++s) {
+                const F2Stage& st = P.st[s];
+                float b_mu = 0.f, b_lv = 0.f;
+                if (s != n) b_mu = bias_of(s);
+                else if (lane < L) { b_mu = __ldg(a.theta + st.seg_b[0] + lane); b_lv = __ldg(a.theta + st.seg_b[1] + lane); }
+                wait_acc(&acc[s], tp);
+                stamp();
+                if (s != n) {
+                    epi_act(s, b_mu, false);
+                    stamp();
+                } else if (q == 0) {
+                    // ---- heads: Sampling (models.py:9-15) + KLD (models.py:81-85); z -> rows 0..15 of the latent tile
+                    float mu[16], lv[16], kl[16];
+                    tmem_ld16(t_lane + T_MU + jc0, mu);
+                    tmem_ld16(t_lane + T_LV + jc0, lv);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        float zz = 0.f, kk = 0.f;
+                        if (lane < L) {
+                            const float m = mu[j] + b_mu, v = lv[j] + b_lv;
+                            zz = m + clipv(expf(v * 0.5f)) * s_eps[lane * 64 + jc0 + j];
+                            kk = 1.f + v - clipv(expf(v)) - m * m;
+                        }
+                        mu[j] = zz; kl[j] = kk;
+                    }
+                    if (lane < 16) store16(tile_hi(n), tile_lo(n), lane, jc0, mu);
+                    const float ks = transpose_reduce16(kl, lane);
+                    if (lane < 16) s_kld[jc0 + lane] = -(ks / (float)L) / 2.f;
+                }
+                publish(&tready[s]);
+                stamp();
+            }
+            // =========================================================== output layer in 128-feature chunks
+            float rec_acc[16];
+            float sc_mae[SCORE ? 16 : 1], sc_kl[SCORE ? 16 : 1], sc_js[SCORE ? 16 : 1];   // rec_acc doubles as the MSE sum
+#pragma unroll
+            for (int j = 0; j < 16; ++j) rec_acc[j] = 0.f;
+            if constexpr (SCORE) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) { sc_mae[j] = 0.f; sc_kl[j] = 0.f; sc_js[j] = 0.f; }
+            }
+            {
+                const F2Stage& st = P.st[so];
+                const float inv_d = 1.f / (float)D;
+                // dW_out^T chunk c -> part (lanes = output features: coalesced rows of the Keras [in, D] kernel)
+                auto drain_out = [&](int c) {
+                    worker_sync();
+                    const uint32_t tdw = dw_wait();
+                    const int f = 128 * c + frow;
+                    const bool valid = f < D;
+                    for (int g = h; g < (st.kin >> 4); g += 4) {
+                        float v[16];
+                        tmem_ld16(tdw + 16 * g, v);
+                        if (valid) put_dw(part + st.seg_w[0] + f, D, 16 * g, st.in, v);
+                    }
+                    if (valid && h == 0) put_db(part + st.seg_b[0] + f, 3 + c % 3, frow);
+                    dw_release();
+                };
+                for (int c = 0; c < P.nC; ++c) {
+                    const int f = 128 * c + frow;
+                    const bool valid = f < D;
+                    // this thread's 16 x values of the chunk (L2-resident since stage 0), issued before the accumulator wait
+                    float xv[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) xv[j] = (valid && jc0 + j < nvalid) ? __ldg(a.x + (row0 + jc0 + j) * D + f) : 0.f;
+                    const float bias = valid ? __ldg(a.theta + st.seg_b[0] + f) : 0.f;
+                    const uint32_t yb = yk & 1;
+                    wait_acc(&yfull[yb], (yk >> 1) & 1);
+                    float y[16];
+                    tmem_ld16(t_lane + T_Y0 + 64 * yb + jc0, y);
+                    tc_fence_before();
+                    warp_arrive(&yempty[yb], lane);
+                    ++yk;
+                    stamp();
+                    if constexpr (SCORE) {
+                        // loss_function (utils.py:346-375) terms of this thread's feature for its 16 jets; Q = clip_values(X_hat)
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            if (valid && jc0 + j < nvalid) {
+                                const float p = xv[j], qv = clipv(y[j] + bias), d = p - qv;
+                                rec_acc[j] += d * d; sc_mae[j] += fabsf(d);
+                                if (a.s_kld) sc_kl[j] += kld_term_fast(p, qv);
+                                if (a.s_jsd) { const float mm = (p + qv) / 2.f; sc_js[j] += (kld_term_fast(p, mm) + kld_term_fast(qv, mm)) / 2.f; }
+                                if (a.s_xhat) a.s_xhat[(row0 + jc0 + j) * D + f] = qv;
+                            }
+                        }
+                    } else {
+                        // reconstruction loss (models.py:66,72-78) and its gradient through clip_values
+                        float dbs = 0.f;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            float gy = 0.f;
+                            if (valid) {
+                                const float yr = y[j] + bias, d = clipv(yr) - xv[j], wj = s_w[jc0 + j];
+                                rec_acc[j] += a.mse ? d * d : fabsf(d);
+                                const float gg = a.mse ? wj * 2.f * d * inv_d : wj * (float)((d > 0.f) - (d < 0.f)) * inv_d;
+                                gy = clip_pass(yr) ? gg : 0.f;
+                            }
+                            dbs += gy; y[j] = gy;
+                        }
+                        if (is_train) {
+                            if (gk >= 1) mbar_wait(&gyempty, (gk - 1) & 1);          // MMAs of the previous chunk have read g_y
+                            store16(gy_hi, gy_lo, frow, jc0, y);
+                            db_at(3 + c % 3, h, frow) = dbs;
+                            fence_async_smem();
+                            warp_arrive(&gyfull, lane);
+                            ++gk;
+                            if (c >= 1) drain_out(c - 1);
+                        }
+                    }
+                    stamp();
+                }
+                const float rs = transpose_reduce16(rec_acc, lane);
+                if (lane < 16) s_rec[q * 64 + jc0 + lane] = rs;
+                if constexpr (SCORE) {                                       // s_db is free outside training: [3][4 quarters][64 jets]
+                    const float r1 = transpose_reduce16(sc_mae, lane), r2 = transpose_reduce16(sc_kl, lane), r3 = transpose_reduce16(sc_js, lane);
+                    if (lane < 16) { s_db[q * 64 + jc0 + lane] = r1; s_db[256 + q * 64 + jc0 + lane] = r2; s_db[512 + q * 64 + jc0 + lane] = r3; }
+                }
+                if (is_train) {
+                    drain_out(P.nC - 1);
+                    wait_acc(&accB[so], tp);
+                    epi_grad(so);
+                    publish(&gready[2 * n]);
+                }
+                stamp();
+            }
+            // =========================================================== backward chain: stages 2n .. 1
+            if (is_train) {
+                for (int s = 2 * n; s >= 1; --s) {
+                    float b_mu = 0.f, b_lv = 0.f;
+                    if (s == n + 1 && lane < L) { b_mu = __ldg(a.theta + P.st[n].seg_b[0] + lane); b_lv = __ldg(a.theta + P.st[n].seg_b[1] + lane); }
+                    wait_acc(&accB[s], tp);
+                    if (s != n + 1) {
+                        epi_grad(s);
+                    } else if (q == 0) {
+                        // ---- latent backward: g_z -> g_mu (rows 0..15), g_logvar (rows 16..31) of the latent tile
+                        const float inv_l = 1.f / (float)L;
+                        float dbm = 0.f, dbl = 0.f;
+                        float gz[16], mu[16], lv[16];
+                        tmem_ld16(t_lane + T_CH + jc0, gz);
+                        tmem_ld16(t_lane + T_MU + jc0, mu);
+                        tmem_ld16(t_lane + T_LV + jc0, lv);
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            float gm = 0.f, gl = 0.f;
+                            if (lane < L) {
+                                const float m = mu[j] + b_mu, v = lv[j] + b_lv, gkw = a.beta * s_w[jc0 + j];
+                                const float e_raw = expf(v), s_raw = expf(v * 0.5f);
+                                gm = gz[j] + gkw * m * inv_l;
+                                gl = gkw * (-(1.f - (clip_pass(e_raw) ? e_raw : 0.f)) * 0.5f * inv_l)
+                                   + gz[j] * s_eps[lane * 64 + jc0 + j] * (clip_pass(s_raw) ? s_raw * 0.5f : 0.f);
+                            }
+                            mu[j] = gm; lv[j] = gl; dbm += gm; dbl += gl;
+                        }
+                        if (lane < 16) {
+                            store16(tile_hi(n), tile_lo(n), lane, jc0, mu);
+                            store16(tile_hi(n), tile_lo(n), 16 + lane, jc0, lv);
+                            db_at(n % 3, h, lane) = dbm; db_at(n % 3, h, 16 + lane) = dbl;
+                        }
+                    }
+                    publish(&gready[s - 1]);
+                    drain_chain(s, s % 3);
+                    stamp();
+                }
+                // ======================================================= stage 0: dW_0^T = G_0 x X, X re-staged from L2
+                {
+                    const F2Stage& st = P.st[0];
+                    auto drain0 = [&](int c) {
+                        if (c == 0) worker_sync();
+                        const uint32_t tdw = dw_wait();
+                        if (32 * q < st.out) {
+                            const bool valid = frow < st.out;
+                            float v[16];
+                            tmem_ld16(tdw + 16 * h, v);
+                            if (valid) put_dw(part + st.seg_w[0] + frow, st.out, 64 * c + 16 * h, D, v);
+                            if (valid && h == 0 && c == 0) put_db(part + st.seg_b[0] + frow, 0, frow);
+                        }
+                        dw_release();
+                    };
+                    float4 ra[2], rb[2];
+                    ldx(0, ra); ldx(1, rb);
+                    for (int c = 0; c < P.nX; c += 2) {
+                        stage_x(ra); ldx(c + 2, ra);
+                        if (c >= 1) drain0(c - 1);
+                        if (c + 1 < P.nX) { stage_x(rb); ldx(c + 3, rb); drain0(c); }
+                    }
+                    drain0(P.nX - 1);
+                }
+            }
+            stamp();
+            // =========================================================== per-jet losses (models.py:123-132) and batch sums
+            worker_sync();
+            if (SCORE) {
+                if (tid < nvalid) {
+                    const int j = tid;
+                    auto q4 = [&](const float* b) { return (b[j] + b[64 + j]) + (b[128 + j] + b[192 + j]); };
+                    if (a.s_mse) a.s_mse[row0 + j] = q4(s_rec) / (float)D;
+                    if (a.s_mae) a.s_mae[row0 + j] = q4(s_db) / (float)D;
+                    if (a.s_kld) a.s_kld[row0 + j] = q4(s_db + 256);
+                    if (a.s_jsd) a.s_jsd[row0 + j] = q4(s_db + 512);
+                    if (a.s_lat) a.s_lat[row0 + j] = isfinite(s_kld[j]) ? s_kld[j] : 0.f;       // latent_loss, utils.py:378-386
+                    if (a.s_fin) a.s_fin[row0 + j] = 1;                                         // clip_values leaves no non-finite X_hat
+                }
+            } else if (tid < 64) {
+                const int j = tid;
+                float lr_ = 0.f, lk = 0.f, tot = 0.f;
+                if (j < nvalid) {
+                    const float rec = (s_rec[j] + s_rec[64 + j] + s_rec[128 + j] + s_rec[192 + j]) / (float)D, wj = s_w[j];
+                    lr_ = rec * wj; lk = s_kld[j] * wj * a.beta; tot = lr_ + lk + 0.f;
+                    if (a.per_jet) {
+                        a.per_jet[row0 + j] = lr_; a.per_jet[a.B + row0 + j] = lk;
+                        a.per_jet[2 * a.B + row0 + j] = 0.f; a.per_jet[3 * a.B + row0 + j] = tot;
+                    }
+                }
+                if (a.sums) {
+                    const double v0 = warp_sum((double)lr_), v1 = warp_sum((double)lk), v3 = warp_sum((double)tot);
+                    if (lane == 0) { atomicAdd(a.sums, v0); atomicAdd(a.sums + 1, v1); atomicAdd(a.sums + 3, v3); }
+                }
+            }
+        }
+    }
+    stamp();
+    if (a.dbg && blockIdx.x == 0 && tid == 0) a.dbg[0] = n_dbg;
+    if (a.dbg && blockIdx.x == 0 && warp == kF3Workers && lane == 0) a.dbg[256] = n_dbg2;
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tm, 512);
+}
+
+}  // namespace oevae

@@ -9,6 +9,7 @@
 #include "prof.h"
 #include "fused_host.cuh"
 #include "fused2_train.cuh"
+#include "fused3_train.cuh"
 #include "fused2_host.cuh"
 #include <cstdlib>
 
@@ -87,7 +88,7 @@ namespace oevae {
 struct FusedState {
     FPlan plan{};
     F2Plan plan2{};                                         // feature-major kernel (default); plan = jet-major v1 (OEVAE_FUSED=1)
-    bool v2 = false;
+    bool v2 = false, v3 = true;                             // v3: warp-specialised fused3_kernel on the same plan (OEVAE_FUSED_V=2 selects fused2)
     unsigned char* wimg = nullptr; int* pos = nullptr; float* parts = nullptr;
     uint32_t img_bytes = 0;
     bool img_dirty = true, last_fused = false;
@@ -119,7 +120,11 @@ int Engine::fused_init() {
             CK(cudaMalloc(&f->pos, pos.size() * sizeof(int)));
             CK(cudaMemcpy(f->pos, pos.data(), pos.size() * sizeof(int), cudaMemcpyHostToDevice));
             CK(cudaMalloc(&f->parts, (size_t)n_sm * Ppad * sizeof(float)));
-            CK(cudaFuncSetAttribute(fused2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+            CK(cudaFuncSetAttribute(fused2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+            CK(cudaFuncSetAttribute(fused2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+            CK(cudaFuncSetAttribute(fused3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+            CK(cudaFuncSetAttribute(fused3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+            { const char* ev = getenv("OEVAE_FUSED_V"); f->v3 = !(ev && atoi(ev) == 2); }   // 3: warp-specialised kernel (default), 2: fused2
             fz = f;
             return 0;
         }
@@ -155,7 +160,7 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
     }
     static long long* dbg_buf = nullptr;
     const bool dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
-    if (dbg && !dbg_buf) cudaMalloc(&dbg_buf, 256 * sizeof(long long));
+    if (dbg && !dbg_buf) { cudaMalloc(&dbg_buf, 512 * sizeof(long long)); cudaMemset(dbg_buf, 0, 512 * sizeof(long long)); }
     if (f.v2) {
         F2Args b{};
         b.x = x; b.w = w; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = f.parts;
@@ -166,14 +171,23 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
         ++calls;
         b.dbg = dbg ? dbg_buf : nullptr;
         const int grid2 = std::min(b.n_tiles, n_sm);
-        { PROF(want_grad ? "fused_train" : "fused_eval", s); fused2_kernel<<<grid2, kF2Threads, f.plan2.smem_bytes, s>>>(f.plan2, b); }
+        {
+            PROF(want_grad ? "fused_train" : "fused_eval", s);
+            if (f.v3) fused3_kernel<false><<<grid2, kF3Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
+            else fused2_kernel<false><<<grid2, kF2Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
+        }
         CKL();
         if (want_grad) { f.last_fused = true; f.last_grid = grid2; }
         if (dbg) {
-            long long hbuf[256]; cudaStreamSynchronize(s); cudaMemcpy(hbuf, dbg_buf, sizeof hbuf, cudaMemcpyDeviceToHost);
-            fprintf(stderr, "[fused2 dbg] grid=%d stamps(cycles since start):", grid2);
+            long long hbuf[512]; cudaStreamSynchronize(s); cudaMemcpy(hbuf, dbg_buf, sizeof hbuf, cudaMemcpyDeviceToHost);
+            fprintf(stderr, "[fused%d dbg] grid=%d stamps(cycles since start):", f.v3 ? 3 : 2, grid2);
             for (int i = 2; i <= (int)hbuf[0]; ++i) fprintf(stderr, " %lld", hbuf[i] - hbuf[1]);
             fprintf(stderr, "\n");
+            if (f.v3 && hbuf[256] > 0) {
+                fprintf(stderr, "[fused3 dbg] issuer stamps:");
+                for (int i = 0; i < (int)hbuf[256]; ++i) fprintf(stderr, " %lld", hbuf[257 + i] - hbuf[1]);
+                fprintf(stderr, "\n");
+            }
         }
         return 0;
     }
@@ -480,8 +494,35 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
                   float* o_lat, unsigned char* o_fin, float* o_xhat, cudaStream_t s) {
     if (N < 0 || n_iter < 1) return fail(OEVAE_EINVAL, "bad N / n_iter");
     if (cfg.noise_mode == OEVAE_NOISE_EXTERNAL && !eps) return fail(OEVAE_EINVAL, "noise_mode EXTERNAL needs eps");
-    long chunk = std::min<long>(N, std::max<long>(cap_rows, 65536));
     if (N == 0) return 0;
+    // single sampling pass: the whole pass is one launch of the fused forward kernel in its
+    // SCORE instantiation (X read once, nothing but the [N] score vectors written)
+    if (fz && fz->v2 && n_iter == 1 && !getenv("OEVAE_SCORE_LAYERED")) {
+        FusedState& f = *fz;
+        if (f.img_dirty) {
+            AdamImgArgs ai{};
+            ai.theta = theta; ai.n = P; ai.wimg = f.wimg; ai.pos = f.pos;
+            { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, 32), 256, 0, s>>>(ai); }
+            CKL();
+            f.img_dirty = false;
+        }
+        F2Args b{};
+        b.x = x; b.w = nullptr; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = nullptr;
+        b.B = N; b.n_tiles = (int)((N + kF2Jets - 1) / kF2Jets); b.train = 0; b.mse = 0; b.beta = 0.f;
+        b.seed = cfg.seed; b.row_offset = row_offset;
+        b.step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
+        ++calls;
+        b.s_mse = o_mse; b.s_mae = o_mae; b.s_kld = o_kld; b.s_jsd = o_jsd; b.s_lat = o_lat; b.s_fin = o_fin; b.s_xhat = o_xhat;
+        const int grid2 = std::min(b.n_tiles, n_sm);
+        {
+            PROF("fused_score", s);
+            if (f.v3) fused3_kernel<true><<<grid2, kF3Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
+            else fused2_kernel<true><<<grid2, kF2Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
+        }
+        CKL();
+        return 0;
+    }
+    long chunk = std::min<long>(N, std::max<long>(cap_rows, 65536));
     TRY(reserve(chunk));
     for (long r0 = 0; r0 < N; r0 += chunk) {
         long nr = std::min(chunk, N - r0);
@@ -832,6 +873,22 @@ int oevae_probe_bulk(int32_t bytes, int32_t depth, int32_t n_cta, int32_t same_s
 }
 
 int64_t oevae_launch_count(void) { return g_launches.load(); }
+
+// page-lock / release a host range in place; "already registered" is success (overlapping loads share pages) and no
+// CUDA error is left pending for the caller's next runtime call
+int oevae_host_register(void* p, int64_t bytes) {
+    if (!p || bytes <= 0) return OEVAE_EINVAL;
+    cudaError_t e = cudaHostRegister(p, (size_t)bytes, cudaHostRegisterDefault);
+    if (e == cudaSuccess) return 0;
+    cudaGetLastError();
+    return e == cudaErrorHostMemoryAlreadyRegistered ? 1 : OEVAE_ECUDA;
+}
+int oevae_host_unregister(void* p) {
+    if (!p) return OEVAE_EINVAL;
+    cudaError_t e = cudaHostUnregister(p);
+    if (e != cudaSuccess) { cudaGetLastError(); return OEVAE_ECUDA; }
+    return 0;
+}
 
 int oevae_profile_enable(int32_t on) {
     if (on && !g_prof.on) g_prof.clear();

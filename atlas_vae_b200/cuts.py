@@ -115,6 +115,8 @@ def mass_histograms_device(var_t, w_t, jzw_t, edges, score_t=None, cut=0.0, keep
     dev = var_t.device
     edges_t = torch.as_tensor(np.ascontiguousarray(edges, np.float64)).to(dev)
     nb = edges_t.numel() - 1
+    if nb < 1:                                  # a selection with min == max gives a single edge (utils.py:541-548): no bins
+        return np.zeros((2, 0), np.int64), np.zeros((2, 0), np.float64)
     counts = torch.zeros((2, nb), dtype=torch.int64, device=dev)
     wsums = torch.zeros((2, nb), dtype=torch.float64, device=dev)
     check(_ffi.lib().oevae_hist(ptr(var_t), ptr(w_t), ptr(jzw_t), ptr(score_t), ptr(keep_t), var_t.numel(), float(cut),

@@ -19,6 +19,7 @@ import numpy as np
 import torch
 
 from .engine import DeviceVAE
+from . import _ffi
 from . import dist as _dist
 
 
@@ -203,9 +204,8 @@ class _BatchStager:
         self.rank, self.world = shard
         self.copy_stream = torch.cuda.Stream(device=device)
         self._registered = []
-        rt = torch.cuda.cudart()
         for a in self.arrays:
-            if a.nbytes and int(rt.cudaHostRegister(a.ctypes.data, a.nbytes, 0)) == 0:
+            if a.nbytes and _ffi.lib().oevae_host_register(a.ctypes.data, a.nbytes) == 0:
                 self._registered.append(a)
         self.h2d_bytes = 0
 
@@ -243,9 +243,8 @@ class _BatchStager:
 
     def close(self):
         torch.cuda.synchronize(self.device)
-        rt = torch.cuda.cudart()
         for a in self._registered:
-            rt.cudaHostUnregister(a.ctypes.data)
+            _ffi.lib().oevae_host_unregister(a.ctypes.data)
         self._registered = []
 
 

@@ -212,6 +212,38 @@ def run_ours(args):
                 'share_of_step': top['share'],
                 'step': {'achieved': ALG_BYTES_PER_JET * BATCH / (ms * 1e-3 / K) / 1e9, 'frac': ALG_BYTES_PER_JET * BATCH / (ms * 1e-3 / K) / 1e9 / peak}}
 
+    # ---- anomaly-scoring leg (BASELINE metric "anomaly-score jets/s", cfg-4 shapes on this rank's resident jets):
+    # vae.py:163-167 predict + loss_function(Latent, MAE, KLD, JSD) + filtering flag, then the apply_cut jet-mass
+    # histogram (plots.py:259,697-715) of the jets above an MAE cut.  Every pass reads the whole 1.6 GB array.
+    from atlas_vae_b200 import cuts as Cc
+    from atlas_vae_b200._ffi import ptr, check
+    g = torch.Generator(device=dev); g.manual_seed(99 + rank)
+    mass = torch.rand(n_jets, device=dev, generator=g) * 300.0
+    jzw = torch.where(torch.rand(n_jets, device=dev, generator=g) < 0.2, -1.0, 0.0)
+    edges = torch.arange(0.0, 302.5, 2.5, dtype=torch.float64, device=dev)
+    counts = torch.zeros((2, edges.numel() - 1), dtype=torch.int64, device=dev); wsums = torch.zeros_like(counts, dtype=torch.float64)
+    SC_ALG = D * 4 + 4 + 4 + 1 + 4 * 4                             # X row, m, w, label, 4 scores = 1625 B
+    def score_pass():
+        out = vae.score(X, 1, None, metrics=('Latent', 'MAE', 'KLD', 'JSD'))
+        check(_ffi.lib().oevae_hist(ptr(mass), ptr(wts), ptr(jzw), ptr(out['MAE']), ptr(out['finite']), n_jets, 0.3,
+                                    ptr(edges), edges.numel(), ptr(counts), ptr(wsums), local, torch.cuda.current_stream().cuda_stream))
+    score_pass(); sync()
+    n_sp = 3
+    _ffi.profile(True)
+    e0.record()
+    for _ in range(n_sp): score_pass()
+    e1.record(); sync()
+    sc_ms = max_over_ranks(e0.elapsed_time(e1)) / n_sp
+    srows = _ffi.profile_report(); _ffi.profile(False)
+    stot = sum(r[2] for r in srows) or 1.0
+    sc_val = world * n_jets / (sc_ms * 1e-3)
+    scoring = {'metric': 'anomaly-score jets/s (predict + Latent/MAE/KLD/JSD + cut + jet-mass histogram)', 'value': sc_val, 'unit': UNIT,
+               'n_jets_per_gpu': n_jets, 'ms_per_pass': sc_ms,
+               'roofline': {'bound': 'hbm', 'achieved': n_jets * SC_ALG / (sc_ms * 1e-3) / 1e9, 'peak': peak, 'unit': 'GB/s',
+                            'frac': n_jets * SC_ALG / (sc_ms * 1e-3) / 1e9 / peak, 'alg_bytes_per_jet': SC_ALG},
+               'kernels': [{'name': r[0], 'launches_per_pass': r[1] / n_sp, 'us_per_launch': 1e3 * r[2] / r[1], 'share': r[2] / stot} for r in srows[:4]]}
+    del mass, jzw
+
     # ---- end to end through the host API: pinned host arrays, H2D per step, D2H of the loss sums per step
     n_e2e = min(n_batches, K)
     Xh = X[:n_e2e * BATCH].cpu().numpy(); wh = np.ones(n_e2e * BATCH, np.float32)
@@ -242,7 +274,7 @@ def run_ours(args):
                                             'precision': args.precision, 'mean_train_loss': loss_mean},
             'clocks': clk, 'gpu_launches': int(launches),
             'e2e': {'value': e2e_val, 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': 32, 'ms_per_step': e2e_ms / n_e2e},
-            'roofline': roof, 'kernels': kernels[:8]}
+            'roofline': roof, 'kernels': kernels[:8], 'scoring': scoring}
     if world == 1 and not args.no_cpu:
         jps, cores, dt, done = cpu_reference_steps(args.cpu_steps, 5, budget_s=20.0)
         line['cpu_baseline'] = {'value': jps, 'unit': UNIT, 'cores': cores, 'kind': 'port',

@@ -185,6 +185,12 @@ OEVAE_API int oevae_probe_issue(int32_t M, int32_t N, int32_t nw, int32_t nm, in
  * out_host2 = {best of 5, first (cold)} of CTA 0. */
 OEVAE_API int oevae_probe_bulk(int32_t bytes, int32_t depth, int32_t n_cta, int32_t same_src, int64_t* out_host2, int32_t device);
 
+/* _BatchStager (host loads -> device batches, replacing the implicit per-step H2D of models.py:180): page-lock a
+ * host array in place.  Returns 0 when newly registered (release it with oevae_host_unregister), 1 when the range
+ * was already page-locked (nothing to release), OEVAE_ECUDA otherwise; never leaves a CUDA error pending. */
+OEVAE_API int oevae_host_register(void* host_ptr, int64_t bytes);
+OEVAE_API int oevae_host_unregister(void* host_ptr);
+
 /* number of kernels this library has launched since load (bench.py "gpu_launches") */
 OEVAE_API int64_t oevae_launch_count(void);
 

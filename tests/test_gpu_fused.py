@@ -85,3 +85,54 @@ def test_fused_philox_noise():
     out, _ = V.losses_and_grad(flat, FC, D, X, w, None, None, eps, OE_type='KLD', beta=1.0, want_grad=False)
     _close(pj.cpu().numpy(), np.stack(out), 1e-3, 1e-5, 'losses with Philox eps')
     assert torch.equal(dev.eval_losses(X, w, None, None, None, 1.0, 0., 0.), pj)
+
+
+@pytest.mark.parametrize('N', [1, 63, 1500, 148 * 64 * 2 + 37])
+def test_fused_score_vs_oracle(N):
+    """Anomaly scoring (vae.py:163-167, utils.py:346-386) through the SCORE instantiation of the fused forward kernel:
+    ragged N, several tiles per CTA.  X_hat / MSE / MAE / Latent vs the float64 oracle at rel 1e-3.  KLD / JSD hold
+    log2(p/q) of near-cancelling ratios, so (as in test_gpu_scoring.test_score_vs_oracle) they are compared with the
+    oracle's metric evaluated on the DEVICE's own X_hat: rel 1e-3 + 1e-4 of the vector's scale (SFU lg2 / reciprocal)."""
+    from atlas_vae_b200.engine import DeviceVAE
+    from oracle import scoring as S
+    rng = np.random.default_rng(5)
+    FC, D = [80, 40, 20, 10], 400
+    flat = V.init_params(FC, D, 4)
+    X = rng.normal(0, 0.4, (N, D)).astype(np.float32); X[:, 300:] = 0
+    eps = rng.normal(size=(1, N, 10)).astype(np.float32)
+    dev = DeviceVAE(FC, D, 'KLD', 'bf16x3', 'external', 0); dev.set_params(flat)
+    out = {k: v.cpu().numpy() for k, v in dev.score(X, 1, eps, metrics=('MSE', 'MAE', 'KLD', 'JSD', 'Latent'), want_xhat=True).items()}
+    slim = {k: v.cpu().numpy() for k, v in dev.score(X, 1, eps, metrics=('MAE', 'Latent')).items()}     # no X_hat, two metrics
+    np.testing.assert_array_equal(slim['MAE'], out['MAE']); np.testing.assert_array_equal(slim['Latent'], out['Latent'])
+    n_ref = min(N, 2000)                                           # float64 oracle on a prefix (it is slow), device X_hat on all rows
+    xhat = S.predict(flat, FC, D, X[:n_ref], [eps[0, :n_ref]], np.float64)
+    _close(out['xhat'][:n_ref], xhat, 1e-3, 1e-4, 'xhat')           # abs floor: 2^-16-relative operand split over 8 layers of O(1) sums
+    ref = S.score_metrics(X[:n_ref].astype(np.float64), xhat, ('MSE', 'MAE'))
+    for m in ('MSE', 'MAE'):
+        _close(out[m][:n_ref], ref[m], 1e-3, 1e-6, m)
+    _close(out['Latent'][:n_ref], S.latent_score(flat, FC, D, X[:n_ref], np.float64), 1e-3, 1e-6, 'Latent')
+    assert out['finite'].all()
+    ref2 = S.score_metrics(X, out['xhat'], ('MSE', 'MAE', 'KLD', 'JSD'))
+    for m in ('MSE', 'MAE'):
+        _close(out[m], ref2[m], 1e-4, 1e-6, m + ' (device X_hat)')
+    for m in ('KLD', 'JSD'):
+        scale = max(np.abs(ref2[m]).max(), 1e-6)
+        _close(out[m], ref2[m], 1e-3, 1e-4 * scale, m)
+
+
+def test_fused2_kernel_still_matches(monkeypatch):
+    """The non-specialised fused2 kernel (OEVAE_FUSED_V=2) stays available as a cross-check of fused3."""
+    monkeypatch.setenv('OEVAE_FUSED_V', '2')
+    FC, D, B = [80, 40, 20, 10], 400, 777
+    X, w, eps = _data(FC, D, B)
+    flat = V.init_params(FC, D, 2)
+    dev = _dev(FC, D); dev.set_params(flat)
+    pj = torch.empty((4, B), device='cuda'); g = torch.empty(dev.n_params, device='cuda')
+    dev.loss_and_grad(X, w, None, None, eps, 1.0, 0., 0., pj, None, g)
+    monkeypatch.setenv('OEVAE_FUSED_V', '3')
+    dev3 = _dev(FC, D); dev3.set_params(flat)
+    pj3 = torch.empty((4, B), device='cuda'); g3 = torch.empty(dev3.n_params, device='cuda')
+    dev3.loss_and_grad(X, w, None, None, eps, 1.0, 0., 0., pj3, None, g3)
+    # same arithmetic, same per-tile summation order -> identical bits
+    np.testing.assert_array_equal(pj.cpu().numpy(), pj3.cpu().numpy())
+    np.testing.assert_allclose(g.cpu().numpy(), g3.cpu().numpy(), rtol=1e-5, atol=1e-7)
