@@ -125,6 +125,13 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
     unsigned char* gy_hi = sm + P.s_off; unsigned char* gy_lo = gy_hi + 16384;
     auto db_at = [&](int buf, int hh, int row) -> float& { return s_db[(buf * 4 + hh) * 128 + row]; };
 
+    // the first tile's rows of X start moving towards L2 while the CTA sets itself up
+    if (warp < kF3Workers && (int)blockIdx.x < a.n_tiles) {
+        const long r0 = (long)blockIdx.x * kF2Jets;
+        const long nbytes = min((long)kF2Jets, a.B - r0) * P.D * 4;
+        const char* px = reinterpret_cast<const char*>(a.x + r0 * P.D);
+        for (long o = (long)tid * 128; o < nbytes; o += kF3Workers * 32 * 128) prefetch_l2(px + o);
+    }
     // ---- one-time setup
     if (tid == 0) {
         for (int i = 0; i < kF2WSlots; ++i) { mbar_init(&wfull[i], 1); mbar_init(&wempty[i], 1); }
@@ -317,6 +324,12 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
             const int nvalid = (int)min((long)kF2Jets, a.B - row0);
             float* part = a.parts + (long)blockIdx.x * P.Ppad;
             if (tid < 64) s_w[tid] = (tid < nvalid && !SCORE) ? a.w[row0 + tid] : 0.f;
+            {   // pull the next tile's rows of X towards L2
+                const long nrow0 = row0 + (long)gridDim.x * kF2Jets;
+                const long nbytes = min((long)kF2Jets, a.B - nrow0) * D * 4;
+                const char* nx = reinterpret_cast<const char*>(a.x + nrow0 * D);
+                for (long o = (long)tid * 128; o < nbytes; o += kF3Workers * 32 * 128) prefetch_l2(nx + o);
+            }
             // reparameterisation noise of the tile -> s_eps[l][jet]: external eps, or one Philox counter (row, quad, step)
             if (a.eps) {
                 for (int i = tid; i < 64 * L; i += kF3Workers * 32) {
@@ -381,7 +394,9 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                 const F2Stage& st = P.st[s];
                 if (32 * q >= P.tile_rows[s]) return;
                 float v[16];
+                stamp();
                 tmem_ld16(t_lane + T_CH + jc0, v);
+                stamp();
                 if (two) {
                     float u[16];
                     tmem_ld16(t_lane + T_Y0 + jc0, u);
@@ -390,9 +405,13 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                 }
                 if (frow < P.tile_rows[s]) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const float t = v[j] + bias;
-                        v[j] = frow < st.out ? (st.relu ? fmaxf(t, 0.f) : t) : 0.f;
+                    // rows out..tile_rows-1 hold exact zeros (zero image rows, bias_of() = 0 there)
+                    if (st.relu) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j] + bias, 0.f);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) v[j] = v[j] + bias;
                     }
                     store16(tile_hi(s), tile_lo(s), frow, jc0, v);
                 }
@@ -415,10 +434,16 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                 }
             };
             // 16 columns i0.. of a dW^T accumulator row -> rows i0.. of the Keras [in, ld] kernel gradient, column o
+            // (a warp writes 32 consecutive o per row: one 128-byte segment per store)
             auto put_dw = [&](float* dw, long ld, int i0, int in, const float* v) {
+                float* d = dw + (long)i0 * ld;
+                const int cnt = in - i0;                                 // warp-uniform
+                if (tile_iter == 0) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    if (i0 + j < in) { float* d = dw + (long)(i0 + j) * ld; *d = tile_iter ? *d + v[j] : v[j]; }
+                    for (int j = 0; j < 16; ++j) { if (j < cnt) *d = v[j]; d += ld; }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) { if (j < cnt) *d += v[j]; d += ld; }
                 }
             };
             auto put_db = [&](float* d, int buf, int row) {
@@ -492,8 +517,9 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                         float zz = 0.f, kk = 0.f;
                         if (lane < L) {
                             const float m = mu[j] + b_mu, v = lv[j] + b_lv;
-                            zz = m + clipv(expf(v * 0.5f)) * s_eps[lane * 64 + jc0 + j];
-                            kk = 1.f + v - clipv(expf(v)) - m * m;
+                            const float sg = __expf(v * 0.5f);                      // sigma; exp(v) = sigma^2 (SFU ex2, rel err ~1e-6)
+                            zz = m + clipv(sg) * s_eps[lane * 64 + jc0 + j];
+                            kk = 1.f + v - clipv(sg * sg) - m * m;
                         }
                         mu[j] = zz; kl[j] = kk;
                     }
@@ -518,14 +544,19 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                 const float inv_d = 1.f / (float)D;
                 // dW_out^T chunk c -> part (lanes = output features: coalesced rows of the Keras [in, D] kernel)
                 auto drain_out = [&](int c) {
+                    stamp();
                     worker_sync();
+                    stamp();
                     const uint32_t tdw = dw_wait();
+                    stamp();
                     const int f = 128 * c + frow;
                     const bool valid = f < D;
                     for (int g = h; g < (st.kin >> 4); g += 4) {
                         float v[16];
                         tmem_ld16(tdw + 16 * g, v);
+                        stamp();
                         if (valid) put_dw(part + st.seg_w[0] + f, D, 16 * g, st.in, v);
+                        stamp();
                     }
                     if (valid && h == 0) put_db(part + st.seg_b[0] + f, 3 + c % 3, frow);
                     dw_release();
@@ -572,8 +603,10 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                             }
                             dbs += gy; y[j] = gy;
                         }
+                        stamp();
                         if (is_train) {
                             if (gk >= 1) mbar_wait(&gyempty, (gk - 1) & 1);          // MMAs of the previous chunk have read g_y
+                            stamp();
                             store16(gy_hi, gy_lo, frow, jc0, y);
                             db_at(3 + c % 3, h, frow) = dbs;
                             fence_async_smem();
@@ -619,7 +652,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                             float gm = 0.f, gl = 0.f;
                             if (lane < L) {
                                 const float m = mu[j] + b_mu, v = lv[j] + b_lv, gkw = a.beta * s_w[jc0 + j];
-                                const float e_raw = expf(v), s_raw = expf(v * 0.5f);
+                                const float s_raw = __expf(v * 0.5f), e_raw = s_raw * s_raw;
                                 gm = gz[j] + gkw * m * inv_l;
                                 gl = gkw * (-(1.f - (clip_pass(e_raw) ? e_raw : 0.f)) * 0.5f * inv_l)
                                    + gz[j] * s_eps[lane * 64 + jc0 + j] * (clip_pass(s_raw) ? s_raw * 0.5f : 0.f);

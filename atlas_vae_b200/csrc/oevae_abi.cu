@@ -119,7 +119,7 @@ int Engine::fused_init() {
             CK(cudaMemset(f->wimg, 0, f->img_bytes));
             CK(cudaMalloc(&f->pos, pos.size() * sizeof(int)));
             CK(cudaMemcpy(f->pos, pos.data(), pos.size() * sizeof(int), cudaMemcpyHostToDevice));
-            CK(cudaMalloc(&f->parts, (size_t)n_sm * Ppad * sizeof(float)));
+            CK(cudaMalloc(&f->parts, ((size_t)n_sm * Ppad + 64) * sizeof(float)));
             CK(cudaFuncSetAttribute(fused2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
             CK(cudaFuncSetAttribute(fused2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
             CK(cudaFuncSetAttribute(fused3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
@@ -163,7 +163,7 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
     if (dbg && !dbg_buf) { cudaMalloc(&dbg_buf, 512 * sizeof(long long)); cudaMemset(dbg_buf, 0, 512 * sizeof(long long)); }
     if (f.v2) {
         F2Args b{};
-        b.x = x; b.w = w; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = f.parts;
+        b.x = x; b.w = w; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = f.parts + (getenv("OEVAE_PART_SHIFT") ? atoi(getenv("OEVAE_PART_SHIFT")) : 0);
         b.per_jet = per_jet; b.sums = sums;
         b.B = B; b.n_tiles = (int)((B + kF2Jets - 1) / kF2Jets); b.train = want_grad; b.mse = mse_type();
         b.beta = beta; b.seed = cfg.seed; b.row_offset = row_offset;
@@ -475,7 +475,7 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
     if (fz) {                                               // same update + refresh of the bf16 weight images
         AdamImgArgs ai{};
         if (grad_in) ai.grad_in = grad_in;
-        else if (fz->last_fused) { ai.parts = fz->parts; ai.n_parts = fz->last_grid; ai.part_stride = Ppad; ai.grad_out = grad_out; }
+        else if (fz->last_fused) { ai.parts = fz->parts + (getenv("OEVAE_PART_SHIFT") ? atoi(getenv("OEVAE_PART_SHIFT")) : 0); ai.n_parts = fz->last_grid; ai.part_stride = Ppad; ai.grad_out = grad_out; }
         else { ai.parts = parts; ai.n_parts = n_slots_used; ai.part_stride = Ppad; ai.grad_out = grad_out; }
         ai.theta = theta; ai.m = m; ai.v = v; ai.n = P;
         ai.alpha = a.alpha; ai.b1 = a.b1; ai.b2 = a.b2; ai.eps = a.eps; ai.apply = apply;

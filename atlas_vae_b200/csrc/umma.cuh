@@ -29,11 +29,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         "{\n\t"
         ".reg .pred p;\n\t"
         "WAIT_LOOP:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
         "@p bra DONE;\n\t"
         "bra WAIT_LOOP;\n\t"
         "DONE:\n\t"
-        "}" ::"r"(addr), "r"(parity) : "memory");
+        "}" ::"r"(addr), "r"(parity), "r"(0x989680u) : "memory");     // suspend-time hint: the hardware parks the thread until the phase flips
 }
 
 // generic-proxy smem writes -> visible to the async proxy (tcgen05.mma / TMA reads)

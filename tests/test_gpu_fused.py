@@ -133,6 +133,6 @@ def test_fused2_kernel_still_matches(monkeypatch):
     dev3 = _dev(FC, D); dev3.set_params(flat)
     pj3 = torch.empty((4, B), device='cuda'); g3 = torch.empty(dev3.n_params, device='cuda')
     dev3.loss_and_grad(X, w, None, None, eps, 1.0, 0., 0., pj3, None, g3)
-    # same arithmetic, same per-tile summation order -> identical bits
-    np.testing.assert_array_equal(pj.cpu().numpy(), pj3.cpu().numpy())
-    np.testing.assert_allclose(g.cpu().numpy(), g3.cpu().numpy(), rtol=1e-5, atol=1e-7)
+    # same contractions and summation order; fused3 evaluates exp() of the Sampling layer on the SFU (rel ~1e-6)
+    np.testing.assert_allclose(pj.cpu().numpy(), pj3.cpu().numpy(), rtol=2e-5, atol=1e-7)
+    _close_grad(g3.cpu().numpy(), g.cpu().numpy(), 1e-4, 1e-5)
