@@ -2,11 +2,13 @@
 // arithmetic as fused2_train.cuh; see that file and fused2_plan.h for the layouts).
 //   forward + losses  models.py:30-36,49-52,62-69,72-85,123-132      gradient of the batch SUM  models.py:183
 //   scoring (SCORE)   vae.py:163-167, utils.py:346-386
-// Roles (576 threads):
+// Roles (704 threads):
 //   warps 0..15  workers: stage X chunks (fp32 -> bf16 hi/lo), run every epilogue (bias/ReLU/split, Sampling + KLD, loss and
-//                its gradient, ReLU masks), drain the dW^T accumulators to the partial-gradient slice
+//                its gradient, ReLU masks)
 //   warp 16      MMA issuer (one lane): waits for operands on mbarriers, issues tcgen05.mma, signals with tcgen05.commit
 //   warp 17      weight producer (one lane): cp.async.bulk of the pre-swizzled weight ops through a 4-slot ring
+//   warps 18..21 drain warps (one per TMEM lane quarter): dW^T accumulators + bias-gradient parts -> partial-gradient slice.
+//                The slice is 293 KB per tile at cfg-2 and one SM stores ~17 B/clk, so the drains run beside the chain
 // No __syncthreads inside a tile: every hand-off is an mbarrier, so the issuer runs ahead of the epilogues, X staging
 // overlaps the layer-0 MMAs, and the dW^T drains overlap the next stage's MMAs (two dW^T accumulators).
 //
@@ -18,7 +20,9 @@
 namespace oevae {
 
 constexpr int kF3Workers = 16;                               // worker warps
-constexpr int kF3Threads = (kF3Workers + 2) * 32;
+constexpr int kF3Drains = 4;                                 // drain warps, one per TMEM lane quarter
+constexpr int kF3Threads = (kF3Workers + 2 + kF3Drains) * 32;
+constexpr int kF3MaxChunks = 24;                             // 128-feature chunks of the output layer (plan: 2 nX + 4 n + 8 <= 96 ops)
 constexpr uint32_t kF3_TDW = 320;
 
 namespace f3 {
@@ -91,14 +95,14 @@ __device__ __forceinline__ void warp_arrive(uint64_t* bar, int lane) {
 }  // namespace f3
 
 template <bool SCORE>
-__global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_constant__ F2Plan P, F2Args a) {
+__global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threads, 1) fused3_kernel(const __grid_constant__ F2Plan P, F2Args a) {
     using namespace umma;
     using namespace f2;
     using namespace f3;
     const bool is_train = !SCORE && a.train;
     extern __shared__ unsigned char smem_dyn[];
     __shared__ uint64_t wfull[kF2WSlots], wempty[kF2WSlots], xfull[kF2XSlots], xempty[kF2XSlots];
-    __shared__ uint64_t yfull[2], yempty[2], gyfull, gyempty, dwfull[2], dwempty[2];
+    __shared__ uint64_t yfull[2], yempty[2], gyfull[kF3MaxChunks], gyempty, dwfull[2], dwempty[2];
     __shared__ uint64_t acc[kF2MaxStages], tready[kF2MaxStages], accB[kF2MaxStages], gready[kF2MaxStages];
     __shared__ uint32_t tmem_base_s;
     unsigned char* sm = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
@@ -136,17 +140,23 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
     if (tid == 0) {
         for (int i = 0; i < kF2WSlots; ++i) { mbar_init(&wfull[i], 1); mbar_init(&wempty[i], 1); }
         for (int i = 0; i < kF2XSlots; ++i) { mbar_init(&xfull[i], kF3Workers); mbar_init(&xempty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&yfull[i], 1); mbar_init(&yempty[i], kF3Workers); mbar_init(&dwfull[i], 1); mbar_init(&dwempty[i], kF3Workers); }
-        mbar_init(&gyfull, kF3Workers); mbar_init(&gyempty, 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(&yfull[i], 1); mbar_init(&yempty[i], kF3Workers); mbar_init(&dwfull[i], 1); mbar_init(&dwempty[i], kF3Drains); }
+        for (int i = 0; i < kF3MaxChunks; ++i) mbar_init(&gyfull[i], kF3Workers);
+        mbar_init(&gyempty, 1);
         for (int i = 0; i < kF2MaxStages; ++i) { mbar_init(&acc[i], 1); mbar_init(&tready[i], kF3Workers); mbar_init(&accB[i], 1); mbar_init(&gready[i], kF3Workers); }
         mbar_fence_init();
     }
-    for (int i = tid * 16; i < P.zero_bytes; i += kF3Threads * 16) *reinterpret_cast<uint4*>(sm + i) = make_uint4(0, 0, 0, 0);
+    for (int i = tid * 16; i < P.zero_bytes; i += (int)blockDim.x * 16) *reinterpret_cast<uint4*>(sm + i) = make_uint4(0, 0, 0, 0);
     if (warp == 0) tmem_alloc(&tmem_base_s, 512);
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    // Programmatic dependent launch: everything above (X prefetch, barriers, TMEM, zeroed tiles) overlaps the tail of the
+    // previous kernel in the stream (the Adam / weight-image kernel); its results (weight image, biases) and the partial-
+    // gradient slices it reads are only touched below.  Both instructions are no-ops for an ordinary launch.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const uint32_t tm = tmem_base_s;
     const uint32_t t_lane = tm + ((uint32_t)(32 * q) << 16);
     const int my_tiles = ((int)blockIdx.x < a.n_tiles) ? (a.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
@@ -256,7 +266,7 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                     for (int c = 0; c < P.nC; ++c) {
                         if (c + 1 < P.nC) issue_y(c + 1);
                         if (is_train) {
-                            mbar_wait(&gyfull, gk & 1);
+                            mbar_wait(&gyfull[c], tp);
                             tc_fence_after();
                             // g_dn += W_out[:, chunk] x g_y[chunk]   (A: K-major rows = in features; B: MN-major, K = chunk features)
                             for (int b = 0; b < 2 && 2 * c + b < P.nX; ++b) {
@@ -314,15 +324,105 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
             }
         }
         __syncwarp();
+    } else if (warp >= kF3Workers + 2) {
+        // ======================================================================================= drain warps
+        // dW^T accumulators (lane = output feature, column = input feature) -> rows of the Keras [in, out] kernel gradients
+        // in this CTA's partial-gradient slice; a warp writes 32 consecutive outputs per row (one 128-byte segment per
+        // store).  Order = the issuer's: output chunks, chain stages 2n..1, layer-0 chunks.
+        if (is_train) {
+            uint32_t dk = 0;
+            int tile_iter = 0;
+            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_iter) {
+                const uint32_t tp = (uint32_t)(tile_iter & 1);
+                float* part = a.parts + (long)blockIdx.x * P.Ppad;
+                auto put_dw = [&](float* dw, long ld, int i0, int in, const float* v) {
+                    float* d = dw + (long)i0 * ld;
+                    const int cnt = in - i0;                             // warp-uniform
+                    if (tile_iter == 0) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) { if (j < cnt) *d = v[j]; d += ld; }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) { if (j < cnt) *d += v[j]; d += ld; }
+                    }
+                };
+                auto put_db = [&](float* d, int buf, int row) {
+                    const float t = (db_at(buf, 0, row) + db_at(buf, 1, row)) + (db_at(buf, 2, row) + db_at(buf, 3, row));
+                    *d = tile_iter ? *d + t : t;
+                };
+                auto dw_wait = [&]() -> uint32_t {
+                    const uint32_t b = dk % ndw, r = dk / ndw;
+                    mbar_wait(&dwfull[b], r & 1);
+                    tc_fence_after();
+                    return t_lane + kF3_TDW + b * dwc;
+                };
+                auto dw_release = [&]() { tc_fence_before(); warp_arrive(&dwempty[dk % ndw], lane); ++dk; };
+                // ---- output layer: chunk c = features 128c.. (bias-gradient parts of loss(c) are behind gyfull[c])
+                {
+                    const F2Stage& st = P.st[so];
+                    for (int c = 0; c < P.nC; ++c) {
+                        mbar_wait(&gyfull[c], tp);
+                        const uint32_t tdw = dw_wait();
+                        const int f = 128 * c + frow;
+                        const bool valid = f < D;
+                        for (int g = 0; g < (st.kin >> 4); ++g) {
+                            float v[16];
+                            tmem_ld16(tdw + 16 * g, v);
+                            if (valid) put_dw(part + st.seg_w[0] + f, D, 16 * g, st.in, v);
+                        }
+                        if (valid) put_db(part + st.seg_b[0] + f, 3 + c % 3, frow);
+                        dw_release();
+                    }
+                }
+                // ---- chain stages (bias-gradient parts of G_s are behind gready[s])
+                for (int s = 2 * n; s >= 1; --s) {
+                    const F2Stage& st = P.st[s];
+                    mbar_wait(&gready[s], tp);
+                    const uint32_t tdw = dw_wait();
+                    const int top = st.seg_lane0[st.nseg - 1] + st.seg_n[st.nseg - 1];
+                    if (32 * q < top) {
+                        int sg = -1;
+#pragma unroll
+                        for (int k = 0; k < 2; ++k) if (k < st.nseg && frow >= st.seg_lane0[k] && frow < st.seg_lane0[k] + st.seg_n[k]) sg = k;
+                        const int o = sg >= 0 ? frow - st.seg_lane0[sg] : 0, ld = sg >= 0 ? st.seg_n[sg] : 0;
+                        float* dw = part + (sg >= 0 ? st.seg_w[sg] : 0) + o;
+                        for (int g = 0; g < (st.kin >> 4); ++g) {
+                            float v[16];
+                            tmem_ld16(tdw + 16 * g, v);
+                            if (sg >= 0) put_dw(dw, ld, 16 * g, st.in, v);
+                        }
+                        if (sg >= 0) put_db(part + st.seg_b[sg] + o, s % 3, frow);
+                    }
+                    dw_release();
+                }
+                // ---- layer 0: one 64-feature chunk of dW_0^T per accumulator
+                {
+                    const F2Stage& st = P.st[0];
+                    mbar_wait(&gready[0], tp);
+                    for (int c = 0; c < P.nX; ++c) {
+                        const uint32_t tdw = dw_wait();
+                        if (32 * q < st.out) {
+                            const bool valid = frow < st.out;
+                            for (int g = 0; g < 4; ++g) {
+                                float v[16];
+                                tmem_ld16(tdw + 16 * g, v);
+                                if (valid) put_dw(part + st.seg_w[0] + frow, st.out, 64 * c + 16 * g, D, v);
+                            }
+                            if (valid && c == 0) put_db(part + st.seg_b[0] + frow, 0, frow);
+                        }
+                        dw_release();
+                    }
+                }
+            }
+        }
     } else {
         // ======================================================================================= workers
-        uint32_t xk = 0, yk = 0, gk = 0, dk = 0;
+        uint32_t xk = 0, yk = 0, gk = 0;
         int tile_iter = 0;
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_iter) {
             const uint32_t tp = (uint32_t)(tile_iter & 1);
             const long row0 = (long)tile * kF2Jets;
             const int nvalid = (int)min((long)kF2Jets, a.B - row0);
-            float* part = a.parts + (long)blockIdx.x * P.Ppad;
             if (tid < 64) s_w[tid] = (tid < nvalid && !SCORE) ? a.w[row0 + tid] : 0.f;
             {   // pull the next tile's rows of X towards L2
                 const long nrow0 = row0 + (long)gridDim.x * kF2Jets;
@@ -433,53 +533,6 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                     db_at((s - 1) % 3, h, frow) = dbs;
                 }
             };
-            // 16 columns i0.. of a dW^T accumulator row -> rows i0.. of the Keras [in, ld] kernel gradient, column o
-            // (a warp writes 32 consecutive o per row: one 128-byte segment per store)
-            auto put_dw = [&](float* dw, long ld, int i0, int in, const float* v) {
-                float* d = dw + (long)i0 * ld;
-                const int cnt = in - i0;                                 // warp-uniform
-                if (tile_iter == 0) {
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) { if (j < cnt) *d = v[j]; d += ld; }
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 16; ++j) { if (j < cnt) *d += v[j]; d += ld; }
-                }
-            };
-            auto put_db = [&](float* d, int buf, int row) {
-                const float t = (db_at(buf, 0, row) + db_at(buf, 1, row)) + (db_at(buf, 2, row) + db_at(buf, 3, row));
-                *d = tile_iter ? *d + t : t;
-            };
-            // next dW^T accumulator to drain: wait for its MMAs; the caller reads it, then calls dw_release
-            auto dw_wait = [&]() -> uint32_t {
-                const uint32_t b = dk % ndw, r = dk / ndw;
-                mbar_wait(&dwfull[b], r & 1);
-                tc_fence_after();
-                return t_lane + kF3_TDW + b * dwc;
-            };
-            auto dw_release = [&]() { tc_fence_before(); warp_arrive(&dwempty[dk % ndw], lane); ++dk; };
-            // dW^T accumulator of chain stage s (lane = output feature, column = input feature) -> partial-gradient slice
-            auto drain_chain = [&](int s, int buf) {
-                const F2Stage& st = P.st[s];
-                worker_sync();                                           // bias-gradient parts of the four column groups are in s_db
-                const uint32_t tdw = dw_wait();
-                const int top = st.seg_lane0[st.nseg - 1] + st.seg_n[st.nseg - 1];
-                if (32 * q < top) {
-                    int sg = -1;
-#pragma unroll
-                    for (int k = 0; k < 2; ++k) if (k < st.nseg && frow >= st.seg_lane0[k] && frow < st.seg_lane0[k] + st.seg_n[k]) sg = k;
-                    const int o = sg >= 0 ? frow - st.seg_lane0[sg] : 0, ld = sg >= 0 ? st.seg_n[sg] : 0;
-                    float* dw = part + (sg >= 0 ? st.seg_w[sg] : 0) + o;
-                    for (int g = h; g < (st.kin >> 4); g += 4) {
-                        float v[16];
-                        tmem_ld16(tdw + 16 * g, v);
-                        if (sg >= 0) put_dw(dw, ld, 16 * g, st.in, v);
-                    }
-                    if (sg >= 0 && h == 0) put_db(part + st.seg_b[sg] + o, buf, frow);
-                }
-                dw_release();
-            };
-
             worker_sync();                                               // s_w / s_eps visible; previous tile's scratch reads done
             // =========================================================== forward, stage 0: X streamed in 64-feature chunks
             {
@@ -542,25 +595,6 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
             {
                 const F2Stage& st = P.st[so];
                 const float inv_d = 1.f / (float)D;
-                // dW_out^T chunk c -> part (lanes = output features: coalesced rows of the Keras [in, D] kernel)
-                auto drain_out = [&](int c) {
-                    stamp();
-                    worker_sync();
-                    stamp();
-                    const uint32_t tdw = dw_wait();
-                    stamp();
-                    const int f = 128 * c + frow;
-                    const bool valid = f < D;
-                    for (int g = h; g < (st.kin >> 4); g += 4) {
-                        float v[16];
-                        tmem_ld16(tdw + 16 * g, v);
-                        stamp();
-                        if (valid) put_dw(part + st.seg_w[0] + f, D, 16 * g, st.in, v);
-                        stamp();
-                    }
-                    if (valid && h == 0) put_db(part + st.seg_b[0] + f, 3 + c % 3, frow);
-                    dw_release();
-                };
                 for (int c = 0; c < P.nC; ++c) {
                     const int f = 128 * c + frow;
                     const bool valid = f < D;
@@ -610,9 +644,8 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                             store16(gy_hi, gy_lo, frow, jc0, y);
                             db_at(3 + c % 3, h, frow) = dbs;
                             fence_async_smem();
-                            warp_arrive(&gyfull, lane);
+                            warp_arrive(&gyfull[c], lane);
                             ++gk;
-                            if (c >= 1) drain_out(c - 1);
                         }
                     }
                     stamp();
@@ -624,7 +657,6 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                     if (lane < 16) { s_db[q * 64 + jc0 + lane] = r1; s_db[256 + q * 64 + jc0 + lane] = r2; s_db[512 + q * 64 + jc0 + lane] = r3; }
                 }
                 if (is_train) {
-                    drain_out(P.nC - 1);
                     wait_acc(&accB[so], tp);
                     epi_grad(so);
                     publish(&gready[2 * n]);
@@ -666,32 +698,16 @@ __global__ void __launch_bounds__(kF3Threads, 1) fused3_kernel(const __grid_cons
                         }
                     }
                     publish(&gready[s - 1]);
-                    drain_chain(s, s % 3);
                     stamp();
                 }
                 // ======================================================= stage 0: dW_0^T = G_0 x X, X re-staged from L2
                 {
-                    const F2Stage& st = P.st[0];
-                    auto drain0 = [&](int c) {
-                        if (c == 0) worker_sync();
-                        const uint32_t tdw = dw_wait();
-                        if (32 * q < st.out) {
-                            const bool valid = frow < st.out;
-                            float v[16];
-                            tmem_ld16(tdw + 16 * h, v);
-                            if (valid) put_dw(part + st.seg_w[0] + frow, st.out, 64 * c + 16 * h, D, v);
-                            if (valid && h == 0 && c == 0) put_db(part + st.seg_b[0] + frow, 0, frow);
-                        }
-                        dw_release();
-                    };
                     float4 ra[2], rb[2];
                     ldx(0, ra); ldx(1, rb);
                     for (int c = 0; c < P.nX; c += 2) {
                         stage_x(ra); ldx(c + 2, ra);
-                        if (c >= 1) drain0(c - 1);
-                        if (c + 1 < P.nX) { stage_x(rb); ldx(c + 3, rb); drain0(c); }
+                        if (c + 1 < P.nX) { stage_x(rb); ldx(c + 3, rb); }
                     }
-                    drain0(P.nX - 1);
                 }
             }
             stamp();

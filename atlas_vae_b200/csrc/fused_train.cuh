@@ -528,6 +528,10 @@ struct AdamImgArgs {
 // slice sums are combined in a fixed tree, so the result does not depend on scheduling.
 __global__ void __launch_bounds__(256) adam_img_kernel(AdamImgArgs a) {
     __shared__ float red[8][33];
+    // programmatic dependent launch (no-ops otherwise): let the next training kernel begin its set-up, then wait for
+    // the kernel that produced the partial gradients
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const long i = (long)blockIdx.x * 32 + tx;
     const bool in = i < a.n;

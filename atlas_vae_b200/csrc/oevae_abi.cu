@@ -12,6 +12,7 @@
 #include "fused3_train.cuh"
 #include "fused2_host.cuh"
 #include <cstdlib>
+#include <utility>
 
 #include <algorithm>
 #include <atomic>
@@ -102,6 +103,20 @@ Engine::~Engine() {
     if (fz) { if (fz->wimg) cudaFree(fz->wimg); if (fz->pos) cudaFree(fz->pos); if (fz->parts) cudaFree(fz->parts); delete fz; }
 }
 
+// launch with the programmatic-stream-serialization attribute (PDL): the kernel may start while its predecessor in the
+// stream drains; it orders itself with griddepcontrol.wait.  OEVAE_PDL=0 falls back to ordinary launches.
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+    static const bool pdl = !(getenv("OEVAE_PDL") && atoi(getenv("OEVAE_PDL")) == 0);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 // fused kernel set-up: only for bf16x3 and nets that fit one CTA (see build_fused_plan); otherwise layered path
 int Engine::fused_init() {
     if (cfg.precision != OEVAE_PREC_BF16X3) return 0;
@@ -173,7 +188,7 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
         const int grid2 = std::min(b.n_tiles, n_sm);
         {
             PROF(want_grad ? "fused_train" : "fused_eval", s);
-            if (f.v3) fused3_kernel<false><<<grid2, kF3Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
+            if (f.v3) CK(launch_pdl(fused3_kernel<false>, dim3(grid2), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b));
             else fused2_kernel<false><<<grid2, kF2Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
         }
         CKL();
@@ -480,7 +495,7 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
         ai.theta = theta; ai.m = m; ai.v = v; ai.n = P;
         ai.alpha = a.alpha; ai.b1 = a.b1; ai.b2 = a.b2; ai.eps = a.eps; ai.apply = apply;
         ai.wimg = fz->wimg; ai.pos = fz->pos;
-        { PROF("adam", s); adam_img_kernel<<<cdiv(P, 32), 256, 0, s>>>(ai); }
+        { PROF("adam", s); CK(launch_pdl(adam_img_kernel, dim3((unsigned)cdiv(P, 32)), dim3(256), 0, s, ai)); }
         CKL();
         if (apply) fz->img_dirty = false;
         return 0;
@@ -516,7 +531,7 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
         const int grid2 = std::min(b.n_tiles, n_sm);
         {
             PROF("fused_score", s);
-            if (f.v3) fused3_kernel<true><<<grid2, kF3Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
+            if (f.v3) fused3_kernel<true><<<grid2, kF3Threads - kF3Drains * 32, f.plan2.smem_bytes, s>>>(f.plan2, b);   // no drain warps in a forward pass
             else fused2_kernel<true><<<grid2, kF2Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
         }
         CKL();

@@ -21,5 +21,5 @@ for rep in sys.argv[1:]:
         d = dict(zip(h, r)); un = dict(zip(h, u))
         print('## %s  kernel=%s' % (rep.split('/')[-1], d.get('Kernel Name')))
         for k in h:
-            if k in WANT or 'tensor' in k:
+            if k in WANT or k in ('sm__inst_executed_pipe_tensor.sum', 'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active', 'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed', 'sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_active') or ('issue_stalled' in k and 'per_issue_active' in k and 'not_issued' not in k):
                 print('%-95s %-12s %s' % (k, un[k], d[k]))
