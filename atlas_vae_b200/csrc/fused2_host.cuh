@@ -84,6 +84,9 @@ inline bool build_fused2_plan(const Engine& e, F2Plan& P, std::vector<int>& pos,
         int dwc = 64;
         for (int s = 1; s < P.S; ++s) dwc = std::max(dwc, P.st[s].kin);
         P.dw_cols = dwc; P.n_dwbuf = (2 * dwc <= 192) ? 2 : 1;
+        const int stg = 64 * P.st[0].out * 4;
+        const int lo = (P.tile_off[1] + 127) / 128 * 128;
+        P.stg0_off = (n >= 1 && P.st[0].out % 4 == 0 && lo + 2 * stg <= P.wring_off) ? lo : -1;
     }
     P.smem_bytes = off + 1024;
     if (P.smem_bytes > 227 * 1024) return false;

@@ -273,13 +273,16 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                                 const int nk = min(4, (D - 64 * (2 * c + b) + 15) >> 4);
                                 issue_e(tm + T_CH, opnd_k(wslot_addr(ob + 2 * c + b), part_b), opnd_mn(gy_a + b * 8192, 16384, 8192), nk, kF2Jets, c > 0 || b > 0);
                             }
+                            // the chunk's weight ops are free once these MMAs complete: the ring can bring in chunk c+2
+                            for (int b = 0; b < 2 && 2 * c + b < P.nX; ++b) wrel(ob + 2 * c + b);
                             // dW_out^T[chunk] = g_y (A: K-major, K = jets) x d_n (B: K-major, N = in features)
                             const uint32_t tdw = dw_acquire();
                             issue_e(tdw, opnd_k(gy_a, 16384), opnd_k(tile_a((2 * n)), P.tile_rows[2 * n] * 128), 4, st.kin, false);
                             commit_e(&gyempty); ++gk;
                             dw_commit();
+                        } else {
+                            for (int b = 0; b < 2 && 2 * c + b < P.nX; ++b) wrel(ob + 2 * c + b);
                         }
-                        for (int b = 0; b < 2 && 2 * c + b < P.nX; ++b) wrel(ob + 2 * c + b);
                     }
                     if (is_train) commit_e(&accB[so]);
                 }
@@ -395,8 +398,48 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     }
                     dw_release();
                 }
-                // ---- layer 0: one 64-feature chunk of dW_0^T per accumulator
-                {
+                // ---- layer 0: one 64-feature chunk of dW_0^T per accumulator.  Rows 64c..64c+63 of the Keras [D, out_0]
+                // kernel gradient are one contiguous block, so each chunk is transposed through shared memory (tiles 1..2n are
+                // dead) and leaves as ONE bulk copy (bulk reduce-add on later tiles) instead of 16 scalar stores per thread:
+                // an SM stores ~17 B/clk through the LSU, which is what bounded this phase.
+                if (P.stg0_off >= 0) {
+                    const F2Stage& st = P.st[0];
+                    const bool leader = warp == kF3Workers + 2 && lane == 0;
+                    const int out0 = st.out;
+                    mbar_wait(&gready[0], tp);
+                    for (int c = 0; c < P.nX; ++c) {
+                        const uint32_t tdw = dw_wait();
+                        float* stg = reinterpret_cast<float*>(sm + P.stg0_off) + (c & 1) * 64 * out0;
+                        if (leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");     // chunk c-2 has left this buffer
+                        asm volatile("bar.sync 2, %0;" ::"n"(kF3Drains * 32) : "memory");
+                        if (32 * q < out0) {
+                            const bool valid = frow < out0;
+                            for (int g = 0; g < 4; ++g) {
+                                float v[16];
+                                tmem_ld16(tdw + 16 * g, v);
+                                if (valid) {
+#pragma unroll
+                                    for (int j = 0; j < 16; ++j) stg[(16 * g + j) * out0 + frow] = v[j];
+                                }
+                            }
+                            if (valid && c == 0) put_db(part + st.seg_b[0] + frow, 0, frow);
+                        }
+                        fence_async_smem();
+                        dw_release();
+                        asm volatile("bar.sync 2, %0;" ::"n"(kF3Drains * 32) : "memory");
+                        if (leader) {
+                            const uint32_t bytes = (uint32_t)(min(64, D - 64 * c) * out0 * 4);
+                            float* dst = part + st.seg_w[0] + (long)64 * c * out0;
+                            if (tile_iter == 0)
+                                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(stg)), "r"(bytes) : "memory");
+                            else
+                                asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(stg)), "r"(bytes) : "memory");
+                            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                        }
+                    }
+                    if (leader) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");              // stores performed before the CTA moves on
+                    asm volatile("bar.sync 2, %0;" ::"n"(kF3Drains * 32) : "memory");
+                } else {
                     const F2Stage& st = P.st[0];
                     mbar_wait(&gready[0], tp);
                     for (int c = 0; c < P.nX; ++c) {
@@ -494,9 +537,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                 const F2Stage& st = P.st[s];
                 if (32 * q >= P.tile_rows[s]) return;
                 float v[16];
-                stamp();
                 tmem_ld16(t_lane + T_CH + jc0, v);
-                stamp();
                 if (two) {
                     float u[16];
                     tmem_ld16(t_lane + T_Y0 + jc0, u);
@@ -504,7 +545,6 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     for (int j = 0; j < 16; ++j) v[j] += u[j];
                 }
                 if (frow < P.tile_rows[s]) {
-#pragma unroll
                     // rows out..tile_rows-1 hold exact zeros (zero image rows, bias_of() = 0 there)
                     if (st.relu) {
 #pragma unroll
@@ -595,6 +635,11 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
             {
                 const F2Stage& st = P.st[so];
                 const float inv_d = 1.f / (float)D;
+                float wsc[SCORE ? 1 : 16];                               // jet weight / D of this thread's 16 jets
+                if constexpr (!SCORE) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) wsc[j] = s_w[jc0 + j] * inv_d;
+                }
                 for (int c = 0; c < P.nC; ++c) {
                     const int f = 128 * c + frow;
                     const bool valid = f < D;
@@ -624,18 +669,30 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                             }
                         }
                     } else {
-                        // reconstruction loss (models.py:66,72-78) and its gradient through clip_values
+                        // reconstruction loss (models.py:66,72-78) and its gradient through clip_values: X_hat = clip_values(y)
+                        // is 0 for a non-finite y and +-1e6 beyond the clip; the gradient passes only where |y| <= 1e6
                         float dbs = 0.f;
+                        if (a.mse) {
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            float gy = 0.f;
-                            if (valid) {
-                                const float yr = y[j] + bias, d = clipv(yr) - xv[j], wj = s_w[jc0 + j];
-                                rec_acc[j] += a.mse ? d * d : fabsf(d);
-                                const float gg = a.mse ? wj * 2.f * d * inv_d : wj * (float)((d > 0.f) - (d < 0.f)) * inv_d;
-                                gy = clip_pass(yr) ? gg : 0.f;
+                            for (int j = 0; j < 16; ++j) {
+                                const float yr = y[j] + bias, ay = fabsf(yr);
+                                const float cl = ay < __int_as_float(0x7f800000) ? fminf(fmaxf(yr, -kClip), kClip) : 0.f;
+                                const float d = valid ? cl - xv[j] : 0.f;
+                                rec_acc[j] = fmaf(d, d, rec_acc[j]);
+                                const float gy = ay <= kClip ? 2.f * wsc[j] * d : 0.f;
+                                dbs += gy; y[j] = gy;
                             }
-                            dbs += gy; y[j] = gy;
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                const float yr = y[j] + bias, ay = fabsf(yr);
+                                const float cl = ay < __int_as_float(0x7f800000) ? fminf(fmaxf(yr, -kClip), kClip) : 0.f;
+                                const float d = valid ? cl - xv[j] : 0.f;
+                                rec_acc[j] += fabsf(d);
+                                const float sg = d == 0.f ? 0.f : copysignf(wsc[j], d);      // w * sign(d) / D
+                                const float gy = ay <= kClip ? sg : 0.f;
+                                dbs += gy; y[j] = gy;
+                            }
                         }
                         stamp();
                         if (is_train) {

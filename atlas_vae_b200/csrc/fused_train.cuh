@@ -524,29 +524,36 @@ struct AdamImgArgs {
     unsigned char* wimg; const int* pos;                    // pos: [4][n] byte offsets (fwd hi, fwd lo, dx hi, dx lo), -1 = none
 };
 
-// block = (32 parameters) x (8 slices of the partial-gradient list): slice y sums parts y, y+8, ... in order, the eight
-// slice sums are combined in a fixed tree, so the result does not depend on scheduling.
-__global__ void __launch_bounds__(256) adam_img_kernel(AdamImgArgs a) {
-    __shared__ float red[8][33];
+// block = (64 parameters) x (4 slices of the partial-gradient list): slice y sums parts y, y+4, ... in order, eight
+// independent loads in flight at a time (the kernel is bound by L2 latency, not bandwidth); the four slice sums are
+// combined in a fixed tree, so the result does not depend on scheduling.
+constexpr int kAdamCols = 64, kAdamSlices = 4;
+__global__ void __launch_bounds__(kAdamCols * kAdamSlices) adam_img_kernel(AdamImgArgs a) {
+    __shared__ float red[kAdamSlices][kAdamCols + 1];
     // programmatic dependent launch (no-ops otherwise): let the next training kernel begin its set-up, then wait for
     // the kernel that produced the partial gradients
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const long i = (long)blockIdx.x * 32 + tx;
+    const int tx = threadIdx.x & (kAdamCols - 1), ty = threadIdx.x / kAdamCols;
+    const long i = (long)blockIdx.x * kAdamCols + tx;
     const bool in = i < a.n;
     float g = 0.f;
     if (a.parts) {
         if (in) {
-            float g0 = 0.f, g1 = 0.f;
-            int sidx = ty;
-            for (; sidx + 8 < a.n_parts; sidx += 16) { g0 += a.parts[(long)sidx * a.part_stride + i]; g1 += a.parts[(long)(sidx + 8) * a.part_stride + i]; }
-            if (sidx < a.n_parts) g0 += a.parts[(long)sidx * a.part_stride + i];
-            g = g0 + g1;
+            const float* src = a.parts + i;
+            for (int base = ty; base < a.n_parts; base += 8 * kAdamSlices) {
+                float t[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int sidx = base + kAdamSlices * k;
+                    t[k] = sidx < a.n_parts ? __ldcg(src + (long)sidx * a.part_stride) : 0.f;
+                }
+                g += ((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]));
+            }
         }
         red[ty][tx] = g;
         __syncthreads();
-        if (ty == 0) g = ((red[0][tx] + red[1][tx]) + (red[2][tx] + red[3][tx])) + ((red[4][tx] + red[5][tx]) + (red[6][tx] + red[7][tx]));
+        if (ty == 0) g = (red[0][tx] + red[1][tx]) + (red[2][tx] + red[3][tx]);
     }
     if (ty != 0 || !in) return;
     float th = a.theta[i];

@@ -169,7 +169,7 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
     if (f.img_dirty) {                                      // weights were set from the host: rebuild the bf16 images
         AdamImgArgs ai{};
         ai.theta = theta; ai.n = P; ai.wimg = f.wimg; ai.pos = f.pos;
-        { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, 32), 256, 0, s>>>(ai); }
+        { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, kAdamCols), kAdamCols * kAdamSlices, 0, s>>>(ai); }
         CKL();
         f.img_dirty = false;
     }
@@ -495,7 +495,7 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
         ai.theta = theta; ai.m = m; ai.v = v; ai.n = P;
         ai.alpha = a.alpha; ai.b1 = a.b1; ai.b2 = a.b2; ai.eps = a.eps; ai.apply = apply;
         ai.wimg = fz->wimg; ai.pos = fz->pos;
-        { PROF("adam", s); CK(launch_pdl(adam_img_kernel, dim3((unsigned)cdiv(P, 32)), dim3(256), 0, s, ai)); }
+        { PROF("adam", s); CK(launch_pdl(adam_img_kernel, dim3((unsigned)cdiv(P, kAdamCols)), dim3(kAdamCols * kAdamSlices), 0, s, ai)); }
         CKL();
         if (apply) fz->img_dirty = false;
         return 0;
@@ -517,7 +517,7 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
         if (f.img_dirty) {
             AdamImgArgs ai{};
             ai.theta = theta; ai.n = P; ai.wimg = f.wimg; ai.pos = f.pos;
-            { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, 32), 256, 0, s>>>(ai); }
+            { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, kAdamCols), kAdamCols * kAdamSlices, 0, s>>>(ai); }
             CKL();
             f.img_dirty = false;
         }
