@@ -45,6 +45,9 @@ SIGNATURES = {
     'oevae_train_step': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _f32, _f32, _f32, _f32, _vp, _vp, _vp]),
     'oevae_loss_and_grad': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _f32, _f32, _f32, _vp, _vp, _vp, _vp]),
     'oevae_apply_update': (C.c_int, [_vp, _vp, _f32, _vp]),
+    'oevae_dp_export': (C.c_int, [_vp, _vp]),
+    'oevae_dp_connect': (C.c_int, [_vp, _i32, _i32, _vp]),
+    'oevae_train_step_dp': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _f32, _f32, _f32, _f32, _vp, _vp, _vp]),
     'oevae_eval_losses': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _f32, _f32, _f32, _vp, _vp, _vp]),
     'oevae_encode': (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     'oevae_score': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -1,0 +1,111 @@
+// Data-parallel update over NVLink peer memory: ONE kernel replaces "sum the partial slices" +
+// ncclAllReduce(SUM) + "clip_values + Adam" of the NCCL path.
+//   phase 1  block b sums this rank's partial-gradient slices for its 128 parameters (fixed order) and stores the result
+//            in the rank's exchange buffer, then pushes sequence number `seq` into flag [rank][b] of EVERY peer (P2P store);
+//   phase 2  it waits until flags [q][b] of all peers q have reached `seq` (they are written into LOCAL memory by the
+//            peers), reads the same 128 values from every peer's exchange buffer (P2P loads), adds the ranks in rank
+//            order -- every rank computes bit-identical sums, so the replicas stay bit-identical -- and applies
+//            clip_values (models.py:185) + Keras Adam (models.py:138,186) + the bf16 weight-image refresh.
+// Nothing is grid-wide: a block depends only on block b of each peer.  All blocks of the launch must be co-resident
+// (a waiting block must never keep a producing block of this rank from being scheduled); the host checks that.
+// The exchange buffer is double-buffered by step parity: a peer overwrites buffer p of step k+2 only after its own
+// step k+1 update, which waited for this rank's step k+1 flags, which this rank raised after its step k kernel
+// (and with it every read of buffer p) had completed.
+#pragma once
+#include "common.cuh"
+#include "umma.cuh"
+
+namespace oevae {
+
+constexpr int kDpCols = 128, kDpSlices = 4, kDpMaxWorld = 8;
+
+struct DpArgs {
+    const float* parts; int n_parts; long part_stride;
+    float* my_gred;                          // this rank's exchange buffer of the step (local)
+    const float* peer_gred[kDpMaxWorld];     // the same buffer of every rank (own entry = my_gred)
+    unsigned int* my_flags;                  // [world][gridDim.x], written by the peers
+    unsigned int* peer_flags[kDpMaxWorld];   // every rank's flag array (own entry unused)
+    int rank, world; unsigned int seq;
+    float* theta; float* m; float* v; long n;
+    float alpha, b1, b2, eps;
+    unsigned char* wimg; const int* pos;
+};
+
+__global__ void __launch_bounds__(kDpCols * kDpSlices, 4) dp_adam_kernel(DpArgs a) {
+    __shared__ float red[kDpSlices][kDpCols + 1];
+    asm volatile("griddepcontrol.wait;" ::: "memory");      // PDL: the training kernel's partial slices are complete
+    const int tx = threadIdx.x & (kDpCols - 1), ty = threadIdx.x / kDpCols;
+    const long i = (long)blockIdx.x * kDpCols + tx;
+    const bool in = i < a.n;
+    // the update's own operands do not depend on the exchange: their loads fly during phase 1
+    float th0 = 0.f, m0 = 0.f, v0 = 0.f;
+    int p0 = -1, p1 = -1, p2 = -1, p3 = -1;
+    if (ty == 0 && in) {
+        th0 = a.theta[i]; m0 = a.m[i]; v0 = a.v[i];
+        if (a.wimg) { p0 = a.pos[i]; p1 = a.pos[a.n + i]; p2 = a.pos[2 * a.n + i]; p3 = a.pos[3 * a.n + i]; }
+    }
+    float g = 0.f;
+    if (in) {
+        const float* src = a.parts + i;
+        for (int base = ty; base < a.n_parts; base += 8 * kDpSlices) {
+            float t[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int sidx = base + kDpSlices * k;
+                t[k] = sidx < a.n_parts ? __ldcg(src + (long)sidx * a.part_stride) : 0.f;
+            }
+            g += ((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]));
+        }
+    }
+    red[ty][tx] = g;
+    __syncthreads();
+    if (ty == 0) {
+        g = (red[0][tx] + red[1][tx]) + (red[2][tx] + red[3][tx]);
+        if (in) __stcg(a.my_gred + i, g);
+    }
+    __syncthreads();
+    // ---- publish: this block's 128 sums are visible system-wide before any peer sees the flag
+    // (st.release.sys is cumulative over the block's stores ordered before it by the barrier above)
+    if (threadIdx.x < a.world && (int)threadIdx.x != a.rank) {
+        unsigned int* f = a.peer_flags[threadIdx.x] + (long)a.rank * gridDim.x + blockIdx.x;
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(a.seq) : "memory");
+    }
+    // ---- wait for block blockIdx.x of every peer
+    if (threadIdx.x < a.world && (int)threadIdx.x != a.rank) {
+        const unsigned int* f = a.my_flags + (long)threadIdx.x * gridDim.x + blockIdx.x;
+        unsigned int seen;
+        const long long t0 = clock64();
+        do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
+            if ((int)(seen - a.seq) < 0 && clock64() - t0 > 20000000000ll) __trap();   // ~10 s: a peer died; fail loudly instead of hanging
+        } while ((int)(seen - a.seq) < 0);
+    }
+    __syncthreads();
+    if (ty != 0 || !in) return;
+    float tq[kDpMaxWorld];
+#pragma unroll
+    for (int q = 0; q < kDpMaxWorld; ++q) {                  // all peers' loads in flight together
+        tq[q] = 0.f;
+        if (q < a.world && q != a.rank) asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(tq[q]) : "l"(a.peer_gred[q] + i) : "memory");
+    }
+    float gs = 0.f;
+#pragma unroll
+    for (int q = 0; q < kDpMaxWorld; ++q) if (q < a.world) gs += (q == a.rank) ? g : tq[q];
+    gs = clipv(gs);
+    float m = m0, v = v0;
+    m += (gs - m) * (1.f - a.b1);
+    v += (gs * gs - v) * (1.f - a.b2);
+    a.m[i] = m; a.v[i] = v;
+    const float th = th0 - (m * a.alpha) / (sqrtf(v) + a.eps);
+    a.theta[i] = th;
+    if (a.wimg) {
+        __nv_bfloat16 hi, lo;
+        umma::split_bf16(th, hi, lo);
+        if (p0 >= 0) *reinterpret_cast<__nv_bfloat16*>(a.wimg + p0) = hi;
+        if (p1 >= 0) *reinterpret_cast<__nv_bfloat16*>(a.wimg + p1) = lo;
+        if (p2 >= 0) *reinterpret_cast<__nv_bfloat16*>(a.wimg + p2) = hi;
+        if (p3 >= 0) *reinterpret_cast<__nv_bfloat16*>(a.wimg + p3) = lo;
+    }
+}
+
+}  // namespace oevae

@@ -46,6 +46,9 @@ struct Engine {
     float *kld = nullptr, *rec = nullptr, *g_rec = nullptr, *g_kld = nullptr;
     int Sg = 1, chunk_rows = 0, n_slots_used = 0;
     FusedState* fz = nullptr;      // fused tcgen05 training kernel (bf16x3, small nets); null when not applicable
+    // data-parallel exchange over NVLink peer memory (dp_kernels.cuh): [2][Ppad] reduced gradients + [8][dp_nblk] flags
+    float* dp_buf = nullptr; void* dp_peer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int dp_rank = -1, dp_world = 0, dp_nblk = 0; unsigned int dp_seq = 0;
 
     ~Engine();
     int fail(int code, const char* fmt, ...);
@@ -69,6 +72,9 @@ struct Engine {
     int fused_losses(const float* x, const float* w, const float* eps, long B, float beta, float* per_jet, double* sums,
                      bool want_grad, cudaStream_t s);
     int reduce_and_update(float* grad_out, const float* grad_in, bool apply, float lr, cudaStream_t s);
+    int dp_export(void* handle_out64);
+    int dp_connect(int rank, int world, const void* handles);
+    int dp_update(float lr, cudaStream_t s);
     int score(const float* x, long N, int n_iter, const float* eps, float* o_mse, float* o_mae, float* o_kld, float* o_jsd,
               float* o_lat, unsigned char* o_fin, float* o_xhat, cudaStream_t s);
     int encode(const float* x, long N, const float* eps, float* o_mu, float* o_lv, float* o_z, cudaStream_t s);

@@ -10,6 +10,7 @@
 #include "fused_host.cuh"
 #include "fused2_train.cuh"
 #include "fused3_train.cuh"
+#include "dp_kernels.cuh"
 #include "fused2_host.cuh"
 #include <cstdlib>
 #include <utility>
@@ -98,6 +99,8 @@ struct FusedState {
 }
 
 Engine::~Engine() {
+    for (int q = 0; q < 8; ++q) if (dp_peer[q] && q != dp_rank) cudaIpcCloseMemHandle(dp_peer[q]);
+    if (dp_buf) cudaFree(dp_buf);
     if (theta) cudaFree(theta);
     if (arena) cudaFree(arena);
     if (fz) { if (fz->wimg) cudaFree(fz->wimg); if (fz->pos) cudaFree(fz->pos); if (fz->parts) cudaFree(fz->parts); delete fz; }
@@ -505,6 +508,65 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------- data parallel over peer memory
+static size_t dp_bytes(long Ppad, int nblk) { return (size_t)2 * Ppad * sizeof(float) + (size_t)kDpMaxWorld * nblk * sizeof(unsigned int); }
+
+int Engine::dp_export(void* handle_out) {
+    if (!handle_out) return fail(OEVAE_EINVAL, "dp_export: null handle");
+    if (!dp_buf) {
+        dp_nblk = (int)cdiv(P, kDpCols);
+        CK(cudaMalloc(&dp_buf, dp_bytes(Ppad, dp_nblk)));
+        CK(cudaMemset(dp_buf, 0, dp_bytes(Ppad, dp_nblk)));
+        CK(cudaDeviceSynchronize());
+    }
+    CK(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(handle_out), dp_buf));
+    return 0;
+}
+
+int Engine::dp_connect(int rank, int world, const void* handles) {
+    if (!dp_buf) return fail(OEVAE_EINVAL, "dp_connect before dp_export");
+    if (world < 2 || world > kDpMaxWorld || rank < 0 || rank >= world || !handles) return fail(OEVAE_EINVAL, "dp_connect: bad rank/world");
+    int per_sm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dp_adam_kernel, kDpCols * kDpSlices, 0));
+    if ((long)per_sm * n_sm < dp_nblk)                      // all blocks must be co-resident (see dp_kernels.cuh)
+        return fail(OEVAE_EUNSUPPORTED, "dp: %d blocks exceed the %d resident blocks of this GPU; use the all-reduce path", dp_nblk, per_sm * n_sm);
+    const cudaIpcMemHandle_t* hs = reinterpret_cast<const cudaIpcMemHandle_t*>(handles);
+    for (int q = 0; q < world; ++q) {
+        if (q == rank) { dp_peer[q] = dp_buf; continue; }
+        CK(cudaIpcOpenMemHandle(&dp_peer[q], hs[q], cudaIpcMemLazyEnablePeerAccess));
+    }
+    dp_rank = rank; dp_world = world; dp_seq = 0;
+    return 0;
+}
+
+// after a gradient pass: local sum of the partial slices + exchange with the peers + clip_values + Adam, one kernel
+int Engine::dp_update(float lr, cudaStream_t s) {
+    if (dp_world < 2) return fail(OEVAE_EINVAL, "dp_update: not connected");
+    DpArgs a{};
+    if (fz && fz->last_fused) { a.parts = fz->parts; a.n_parts = fz->last_grid; }
+    else { a.parts = parts; a.n_parts = n_slots_used; }
+    a.part_stride = Ppad;
+    ++step; ++dp_seq;
+    const int b = (int)(dp_seq & 1u);
+    a.my_gred = dp_buf + (size_t)b * Ppad;
+    a.my_flags = reinterpret_cast<unsigned int*>(dp_buf + (size_t)2 * Ppad);
+    for (int q = 0; q < dp_world; ++q) {
+        float* base = static_cast<float*>(dp_peer[q]);
+        a.peer_gred[q] = base + (size_t)b * Ppad;
+        a.peer_flags[q] = reinterpret_cast<unsigned int*>(base + (size_t)2 * Ppad);
+    }
+    a.rank = dp_rank; a.world = dp_world; a.seq = dp_seq;
+    a.theta = theta; a.m = m; a.v = v; a.n = P;
+    const double t = (double)step;
+    a.alpha = (float)((double)lr * std::sqrt(1.0 - std::pow(0.999, t)) / (1.0 - std::pow(0.9, t)));
+    a.b1 = 0.9f; a.b2 = 0.999f; a.eps = 1e-7f;
+    if (fz) { a.wimg = fz->wimg; a.pos = fz->pos; }
+    { PROF("dp_adam", s); CK(launch_pdl(dp_adam_kernel, dim3((unsigned)dp_nblk), dim3(kDpCols * kDpSlices), 0, s, a)); }
+    CKL();
+    if (fz) fz->img_dirty = false;
+    return 0;
+}
+
 int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o_mse, float* o_mae, float* o_kld, float* o_jsd,
                   float* o_lat, unsigned char* o_fin, float* o_xhat, cudaStream_t s) {
     if (N < 0 || n_iter < 1) return fail(OEVAE_EINVAL, "bad N / n_iter");
@@ -693,6 +755,19 @@ int oevae_train_step(oevae_t h, const float* x_bkg, const float* w_bkg, const fl
     int rc = e->losses(x_bkg, w_bkg, x_ood, w_ood, eps, n_eps, B, beta, lamb, margin, per_jet_out, sums_acc, true, s);
     if (rc) return rc;
     return e->reduce_and_update(nullptr, nullptr, true, lr, s);
+}
+
+int oevae_dp_export(oevae_t h, void* handle_out64) { H(h); return e->dp_export(handle_out64); }
+int oevae_dp_connect(oevae_t h, int32_t rank, int32_t world, const void* handles) { H(h); return e->dp_connect(rank, world, handles); }
+int oevae_train_step_dp(oevae_t h, const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood,
+                        const float* eps, int32_t n_eps, int64_t B, float lr, float beta, float lamb, float margin,
+                        float* per_jet_out, double* sums_acc, void* stream) {
+    H(h);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (e->dp_world < 2) return e->fail(OEVAE_EINVAL, "train_step_dp: call oevae_dp_export / oevae_dp_connect first");
+    int rc = e->losses(x_bkg, w_bkg, x_ood, w_ood, eps, n_eps, B, beta, lamb, margin, per_jet_out, sums_acc, true, s);
+    if (rc) return rc;
+    return e->dp_update(lr, s);
 }
 
 int oevae_loss_and_grad(oevae_t h, const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood,

@@ -47,6 +47,7 @@ class DeviceVAE:
             raise OevaeError('oevae_create failed (%d): %s' % (rc, self.lib.oevae_last_error(None).decode()))
         self.h = h
         self.n_params = int(self.lib.oevae_n_params(self.h))
+        self.dp = False                                       # peer-memory data-parallel path connected (dp_connect)
 
     def close(self):
         if getattr(self, 'h', None):
@@ -119,6 +120,38 @@ class DeviceVAE:
         eps, n_eps = self._eps(eps, B)
         check(self.lib.oevae_train_step(self.h, ptr(x), ptr(w), ptr(x_ood), ptr(w_ood), ptr(eps), n_eps, B,
                                         lr, beta, lamb, margin, ptr(per_jet), ptr(sums), _stream()), self.h)
+
+    def dp_connect(self):
+        """Data parallel over NVLink peer memory: exchange the IPC handles of the per-rank gradient buffers (torch.distributed
+        is only the transport of 64 bytes per rank).  Returns False when the fast path does not apply (then use
+        loss_and_grad + all_reduce + apply_update)."""
+        import torch.distributed as td
+        if not (td.is_available() and td.is_initialized() and td.get_world_size() > 1):
+            return False
+        rank, world = td.get_rank(), td.get_world_size()
+        ok = world <= 8
+        raw = C.create_string_buffer(64)
+        if ok:
+            check(self.lib.oevae_dp_export(self.h, raw), self.h)
+        handles = [None] * world
+        td.all_gather_object(handles, raw.raw if ok else None)
+        if any(h is None for h in handles):
+            return False
+        blob = C.create_string_buffer(b''.join(handles), 64 * world)
+        rc = self.lib.oevae_dp_connect(self.h, rank, world, blob)
+        flags = [None] * world
+        td.all_gather_object(flags, int(rc))
+        self.dp = all(f == 0 for f in flags)                 # every rank takes the same path
+        td.barrier()
+        return self.dp
+
+    def train_step_dp(self, x, w, x_ood=None, w_ood=None, eps=None, lr=1e-3, beta=0., lamb=0., margin=0.,
+                      per_jet=None, sums=None):
+        x, w, x_ood, w_ood = self._f32(x), self._f32(w), self._f32(x_ood), self._f32(w_ood)
+        B = x.shape[0]
+        eps, n_eps = self._eps(eps, B)
+        check(self.lib.oevae_train_step_dp(self.h, ptr(x), ptr(w), ptr(x_ood), ptr(w_ood), ptr(eps), n_eps, B,
+                                           lr, beta, lamb, margin, ptr(per_jet), ptr(sums), _stream()), self.h)
 
     def loss_and_grad(self, x, w, x_ood=None, w_ood=None, eps=None, beta=0., lamb=0., margin=0.,
                       per_jet=None, sums=None, grad=None):

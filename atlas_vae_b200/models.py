@@ -278,6 +278,9 @@ def train_model(vae, train_sample, valid_sample, OE_type='KLD', n_epochs=1, batc
     sums = torch.zeros(4, dtype=torch.float64, device=dev.device)           # keras.metrics.Mean numerators
     vsum = torch.zeros(4, dtype=torch.float64, device=dev.device)
     grad = torch.empty(dev.n_params, dtype=torch.float32, device=dev.device) if world > 1 else None
+    # n_gpus > 1: the update kernel exchanges the per-rank gradient sums over NVLink peer memory (one node, NCCL backend);
+    # otherwise (gloo test boxes, nets too large for a co-resident launch) SUM all-reduce of the flat gradient
+    peer = world > 1 and torch.distributed.get_backend() == 'nccl' and (getattr(dev, 'dp', False) or dev.dp_connect())
     total_batches = 0; count = 0
     beta, lamb, margin = float(beta), float(lamb), float(margin)
     for epoch in range(n_epochs):
@@ -295,6 +298,9 @@ def train_model(vae, train_sample, valid_sample, OE_type='KLD', n_epochs=1, batc
                     lo, hi, glo = stager.bounds(batch_idx)
                     if world == 1:
                         dev.train_step(x, w, xo, wo, None, optimizer.learning_rate, beta, lamb, margin, None, sums)
+                    elif peer:
+                        dev.set_noise_offset(lo - glo)
+                        dev.train_step_dp(x, w, xo, wo, None, optimizer.learning_rate, beta, lamb, margin, None, sums)
                     else:
                         dev.set_noise_offset(lo - glo)
                         dev.loss_and_grad(x, w, xo, wo, None, beta, lamb, margin, None, sums, grad)

@@ -107,6 +107,22 @@ OEVAE_API int oevae_loss_and_grad(oevae_t h, const float* x_bkg, const float* w_
                         float beta, float lamb, float margin,
                         float* per_jet_out, double* sums_acc, float* grad_out, void* stream);
 
+/* ---- data parallel over NVLink peer memory (replaces jet-ID's MirroredStrategy semantics, jet-ID/classifier.py:136-138,
+ * for --n_gpus N; one process per GPU on one node).  oevae_dp_export allocates this rank's exchange buffer and writes
+ * its 64-byte cudaIpcMemHandle_t; the caller gathers the handles of all ranks (any transport) and passes the
+ * world x 64 bytes to oevae_dp_connect.  oevae_train_step_dp is oevae_train_step for one rank's slice of the global
+ * batch: its update kernel sums this rank's partial gradients, exchanges the result with the peers through P2P loads /
+ * stores and applies clip + Adam to the SUM over ranks (models.py:183), identically on every rank.
+ * OEVAE_EUNSUPPORTED from oevae_dp_connect (network too large for a co-resident launch): use oevae_loss_and_grad +
+ * all-reduce + oevae_apply_update. */
+OEVAE_API int oevae_dp_export(oevae_t h, void* handle_out64);
+OEVAE_API int oevae_dp_connect(oevae_t h, int32_t rank, int32_t world, const void* handles);
+OEVAE_API int oevae_train_step_dp(oevae_t h, const float* x_bkg, const float* w_bkg,
+                        const float* x_ood, const float* w_ood,
+                        const float* eps, int32_t n_eps, int64_t B,
+                        float lr, float beta, float lamb, float margin,
+                        float* per_jet_out, double* sums_acc, void* stream);
+
 /* clip_values(grad) + Adam with the given (possibly all-reduced) gradient; increments the step. */
 OEVAE_API int oevae_apply_update(oevae_t h, const float* grad, float lr, void* stream);
 
