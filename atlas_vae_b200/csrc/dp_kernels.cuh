@@ -17,7 +17,7 @@
 
 namespace oevae {
 
-constexpr int kDpCols = 128, kDpSlices = 4, kDpMaxWorld = 8;
+constexpr int kDpCols = 128, kDpSlices = 4, kDpMaxWorld = 8;   // 573 blocks at cfg-2: one co-resident wave of 512-thread blocks
 
 struct DpArgs {
     const float* parts; int n_parts; long part_stride;
@@ -47,14 +47,14 @@ __global__ void __launch_bounds__(kDpCols * kDpSlices, 4) dp_adam_kernel(DpArgs 
     float g = 0.f;
     if (in) {
         const float* src = a.parts + i;
-        for (int base = ty; base < a.n_parts; base += 8 * kDpSlices) {
-            float t[8];
+        for (int base = ty; base < a.n_parts; base += 10 * kDpSlices) {
+            float t[10];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
+            for (int k = 0; k < 10; ++k) {
                 const int sidx = base + kDpSlices * k;
                 t[k] = sidx < a.n_parts ? __ldcg(src + (long)sidx * a.part_stride) : 0.f;
             }
-            g += ((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]));
+            g += (((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]))) + (t[8] + t[9]);
         }
     }
     red[ty][tx] = g;

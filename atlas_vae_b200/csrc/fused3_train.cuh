@@ -129,6 +129,10 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
     unsigned char* gy_hi = sm + P.s_off; unsigned char* gy_lo = gy_hi + 16384;
     auto db_at = [&](int buf, int hh, int row) -> float& { return s_db[(buf * 4 + hh) * 128 + row]; };
 
+    unsigned long long dbg_t0 = 0;
+    if (a.dbg && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
+    long long dbg_c[6] = {0, 0, 0, 0, 0, 0};
+    dbg_c[0] = clock64();
     // the first tile's rows of X start moving towards L2 while the CTA sets itself up
     if (warp < kF3Workers && (int)blockIdx.x < a.n_tiles) {
         const long r0 = (long)blockIdx.x * kF2Jets;
@@ -136,22 +140,27 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
         const char* px = reinterpret_cast<const char*>(a.x + r0 * P.D);
         for (long o = (long)tid * 128; o < nbytes; o += kF3Workers * 32 * 128) prefetch_l2(px + o);
     }
+    dbg_c[1] = clock64();
     // ---- one-time setup
-    if (tid == 0) {
-        for (int i = 0; i < kF2WSlots; ++i) { mbar_init(&wfull[i], 1); mbar_init(&wempty[i], 1); }
-        for (int i = 0; i < kF2XSlots; ++i) { mbar_init(&xfull[i], kF3Workers); mbar_init(&xempty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&yfull[i], 1); mbar_init(&yempty[i], kF3Workers); mbar_init(&dwfull[i], 1); mbar_init(&dwempty[i], kF3Drains); }
-        for (int i = 0; i < kF3MaxChunks; ++i) mbar_init(&gyfull[i], kF3Workers);
-        mbar_init(&gyempty, 1);
-        for (int i = 0; i < kF2MaxStages; ++i) { mbar_init(&acc[i], 1); mbar_init(&tready[i], kF3Workers); mbar_init(&accB[i], 1); mbar_init(&gready[i], kF3Workers); }
-        mbar_fence_init();
-    }
+    // barrier init spread over the threads (one thread doing all ~110 of them costs ~1.3 k cycles)
+    if (tid < kF2MaxStages) { mbar_init(&acc[tid], 1); mbar_init(&tready[tid], kF3Workers); mbar_init(&accB[tid], 1); mbar_init(&gready[tid], kF3Workers); }
+    else if (tid >= 32 && tid < 32 + kF3MaxChunks) mbar_init(&gyfull[tid - 32], kF3Workers);
+    else if (tid >= 64 && tid < 64 + kF2WSlots) { mbar_init(&wfull[tid - 64], 1); mbar_init(&wempty[tid - 64], 1); }
+    else if (tid >= 96 && tid < 96 + kF2XSlots) { mbar_init(&xfull[tid - 96], kF3Workers); mbar_init(&xempty[tid - 96], 1); }
+    else if (tid >= 128 && tid < 130) { mbar_init(&yfull[tid - 128], 1); mbar_init(&yempty[tid - 128], kF3Workers); mbar_init(&dwfull[tid - 128], 1); mbar_init(&dwempty[tid - 128], kF3Drains); }
+    else if (tid == 160) mbar_init(&gyempty, 1);
+    mbar_fence_init();
+    dbg_c[2] = clock64();
     for (int i = tid * 16; i < P.zero_bytes; i += (int)blockDim.x * 16) *reinterpret_cast<uint4*>(sm + i) = make_uint4(0, 0, 0, 0);
+    dbg_c[3] = clock64();
     if (warp == 0) tmem_alloc(&tmem_base_s, 512);
+    dbg_c[4] = clock64();
     fence_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    dbg_c[5] = clock64();
+    if (a.dbg && blockIdx.x == 0 && tid == 0) for (int i = 0; i < 6; ++i) a.dbg[900 + i] = dbg_c[i];
     // Programmatic dependent launch: everything above (X prefetch, barriers, TMEM, zeroed tiles) overlaps the tail of the
     // previous kernel in the stream (the Adam / weight-image kernel); its results (weight image, biases) and the partial-
     // gradient slices it reads are only touched below.  Both instructions are no-ops for an ordinary launch.
@@ -800,6 +809,11 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
         }
     }
     stamp();
+    if (a.dbg && tid == 0 && blockIdx.x < 160) {              // per-CTA wall-clock span: a.dbg[512 + 2 b] = entry, [513 + 2 b] = exit (ns)
+        unsigned long long t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        a.dbg[512 + 2 * blockIdx.x] = (long long)dbg_t0; a.dbg[513 + 2 * blockIdx.x] = (long long)t1;
+    }
     if (a.dbg && blockIdx.x == 0 && tid == 0) a.dbg[0] = n_dbg;
     if (a.dbg && blockIdx.x == 0 && warp == kF3Workers && lane == 0) a.dbg[256] = n_dbg2;
     tc_fence_before();

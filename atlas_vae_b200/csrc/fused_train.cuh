@@ -524,11 +524,12 @@ struct AdamImgArgs {
     unsigned char* wimg; const int* pos;                    // pos: [4][n] byte offsets (fwd hi, fwd lo, dx hi, dx lo), -1 = none
 };
 
-// block = (64 parameters) x (4 slices of the partial-gradient list): slice y sums parts y, y+4, ... in order, eight
-// independent loads in flight at a time (the kernel is bound by L2 latency, not bandwidth); the four slice sums are
+// block = (64 parameters) x (8 slices of the partial-gradient list): slice y sums parts y, y+8, ... in order, ten
+// independent loads in flight at a time (one L2 round trip for the 79 slices of a B=5000 step: the kernel is bound by
+// L2 latency, not bandwidth), one resident wave of 512-thread blocks; the eight slice sums are
 // combined in a fixed tree, so the result does not depend on scheduling.
-constexpr int kAdamCols = 64, kAdamSlices = 4;
-__global__ void __launch_bounds__(kAdamCols * kAdamSlices) adam_img_kernel(AdamImgArgs a) {
+constexpr int kAdamCols = 64, kAdamSlices = 8;
+__global__ void __launch_bounds__(kAdamCols * kAdamSlices, 4) adam_img_kernel(AdamImgArgs a) {
     __shared__ float red[kAdamSlices][kAdamCols + 1];
     // programmatic dependent launch (no-ops otherwise): let the next training kernel begin its set-up, then wait for
     // the kernel that produced the partial gradients
@@ -541,19 +542,19 @@ __global__ void __launch_bounds__(kAdamCols * kAdamSlices) adam_img_kernel(AdamI
     if (a.parts) {
         if (in) {
             const float* src = a.parts + i;
-            for (int base = ty; base < a.n_parts; base += 8 * kAdamSlices) {
-                float t[8];
+            for (int base = ty; base < a.n_parts; base += 10 * kAdamSlices) {
+                float t[10];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
+                for (int k = 0; k < 10; ++k) {
                     const int sidx = base + kAdamSlices * k;
                     t[k] = sidx < a.n_parts ? __ldcg(src + (long)sidx * a.part_stride) : 0.f;
                 }
-                g += ((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]));
+                g += (((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]))) + (t[8] + t[9]);
             }
         }
         red[ty][tx] = g;
         __syncthreads();
-        if (ty == 0) g = (red[0][tx] + red[1][tx]) + (red[2][tx] + red[3][tx]);
+        if (ty == 0) g = ((red[0][tx] + red[1][tx]) + (red[2][tx] + red[3][tx])) + ((red[4][tx] + red[5][tx]) + (red[6][tx] + red[7][tx]));
     }
     if (ty != 0 || !in) return;
     float th = a.theta[i];

@@ -178,7 +178,7 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
     }
     static long long* dbg_buf = nullptr;
     const bool dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
-    if (dbg && !dbg_buf) { cudaMalloc(&dbg_buf, 512 * sizeof(long long)); cudaMemset(dbg_buf, 0, 512 * sizeof(long long)); }
+    if (dbg && !dbg_buf) { cudaMalloc(&dbg_buf, 1024 * sizeof(long long)); cudaMemset(dbg_buf, 0, 1024 * sizeof(long long)); }
     if (f.v2) {
         F2Args b{};
         b.x = x; b.w = w; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = f.parts + (getenv("OEVAE_PART_SHIFT") ? atoi(getenv("OEVAE_PART_SHIFT")) : 0);
@@ -197,10 +197,23 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
         CKL();
         if (want_grad) { f.last_fused = true; f.last_grid = grid2; }
         if (dbg) {
-            long long hbuf[512]; cudaStreamSynchronize(s); cudaMemcpy(hbuf, dbg_buf, sizeof hbuf, cudaMemcpyDeviceToHost);
+            long long hbuf[1024]; cudaStreamSynchronize(s); cudaMemcpy(hbuf, dbg_buf, sizeof hbuf, cudaMemcpyDeviceToHost);
             fprintf(stderr, "[fused%d dbg] grid=%d stamps(cycles since start):", f.v3 ? 3 : 2, grid2);
             for (int i = 2; i <= (int)hbuf[0]; ++i) fprintf(stderr, " %lld", hbuf[i] - hbuf[1]);
             fprintf(stderr, "\n");
+            if (f.v3) {
+                long long t0min = 1ll << 62, t1max = 0, dmax = 0, dmin = 1ll << 62; int imax = 0;
+                for (int b2 = 0; b2 < grid2 && b2 < 160; ++b2) {
+                    const long long t0 = hbuf[512 + 2 * b2], t1 = hbuf[513 + 2 * b2];
+                    t0min = std::min(t0min, t0); t1max = std::max(t1max, t1);
+                    if (t1 - t0 > dmax) { dmax = t1 - t0; imax = b2; }
+                    dmin = std::min(dmin, t1 - t0);
+                }
+                fprintf(stderr, "[fused3 dbg] set-up cycles (tid 0): prefetch %lld, barrier init %lld, zero %lld, tmem alloc %lld, sync %lld; first stamp at +%lld\n",
+                        hbuf[901] - hbuf[900], hbuf[902] - hbuf[901], hbuf[903] - hbuf[902], hbuf[904] - hbuf[903], hbuf[905] - hbuf[904], hbuf[1] - hbuf[900]);
+                fprintf(stderr, "[fused3 dbg] CTA spans (ns): first entry -> last exit %lld, per-CTA min %lld max %lld (cta %d), cta0 %lld, entry skew %lld\n",
+                        t1max - t0min, dmin, dmax, imax, hbuf[513] - hbuf[512], hbuf[512 + 2 * (grid2 - 1)] - t0min);
+            }
             if (f.v3 && hbuf[256] > 0) {
                 fprintf(stderr, "[fused3 dbg] issuer stamps:");
                 for (int i = 0; i < (int)hbuf[256]; ++i) fprintf(stderr, " %lld", hbuf[257 + i] - hbuf[1]);
