@@ -71,6 +71,8 @@ struct Engine {
     int fused_init();
     int fused_losses(const float* x, const float* w, const float* eps, long B, float beta, float* per_jet, double* sums,
                      bool want_grad, cudaStream_t s);
+    int fused_oe(const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood, const float* eps, long B,
+                 float beta, float lamb, float margin, float* per_jet, double* sums, bool want_grad, cudaStream_t s);
     int reduce_and_update(float* grad_out, const float* grad_in, bool apply, float lr, cudaStream_t s);
     int dp_export(void* handle_out64);
     int dp_connect(int rank, int world, const void* handles);

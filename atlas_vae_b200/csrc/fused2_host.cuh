@@ -79,7 +79,7 @@ inline bool build_fused2_plan(const Engine& e, F2Plan& P, std::vector<int>& pos,
     P.wring_off = off; off += kF2WSlots * P.wslot_bytes;
     P.zero_bytes = P.wring_off;                                        // tiles only: the ring is being filled during set-up
     P.s_off = off; off += std::max(kF2XSlots * 16384, 32768);
-    P.scratch_off = off; off += (13824 + 256 * L + 255) / 256 * 256;  // s_w, s_rec, s_kld, s_db [6][4][128] (fused2 uses 4), s_eps
+    P.scratch_off = off; off += (14080 + 256 * L + 255) / 256 * 256;  // s_w, s_rec, s_kld, s_db [6][4][128] (fused2 uses 4), s_eps, s_wk
     {
         int dwc = 64;
         for (int s = 1; s < P.S; ++s) dwc = std::max(dwc, P.st[s].kin);

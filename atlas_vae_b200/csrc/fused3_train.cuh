@@ -123,6 +123,10 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                                                                        // chain stage k -> buffer k % 3, output chunk c -> 3 + c % 3 (a buffer
                                                                        // is rewritten two worker_sync()s after its last reader)
     float* s_eps = s_db + 3072;                                        // [L][64]
+    float* s_wk = s_eps + 64 * L;                                      // [64] per-jet coefficient of the KLD term (beta * w, or c_kld)
+    // row r of the (virtual) batch: rows >= a.B1 come from the second input a.x2 (the OoD sample of the outlier-exposure step)
+    auto xrow = [&](long r) -> const float* { return (a.x2 && r >= a.B1) ? a.x2 + (r - a.B1) * (long)P.D : a.x + r * (long)P.D; };
+    auto nrow = [&](long r) -> long { return a.noise_mod > 0 ? r % a.noise_mod : r; };   // row index the reparameterisation noise is drawn for
     auto tile_hi = [&](int k) { return sm + P.tile_off[k]; };
     auto tile_lo = [&](int k) { return sm + P.tile_off[k] + P.tile_rows[k] * 128; };
     auto xslot = [&](int s) { return sm + P.s_off + s * 16384; };      // hi 8 KB, lo 8 KB
@@ -137,7 +141,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
     if (warp < kF3Workers && (int)blockIdx.x < a.n_tiles) {
         const long r0 = (long)blockIdx.x * kF2Jets;
         const long nbytes = min((long)kF2Jets, a.B - r0) * P.D * 4;
-        const char* px = reinterpret_cast<const char*>(a.x + r0 * P.D);
+        const char* px = reinterpret_cast<const char*>(xrow(r0));
         for (long o = (long)tid * 128; o < nbytes; o += kF3Workers * 32 * 128) prefetch_l2(px + o);
     }
     dbg_c[1] = clock64();
@@ -355,12 +359,12 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                         for (int j = 0; j < 16; ++j) { if (j < cnt) *d = v[j]; d += ld; }
                     } else {
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) { if (j < cnt) *d += v[j]; d += ld; }
+                        for (int j = 0; j < 16; ++j) { if (j < cnt) atomicAdd(d, v[j]); d += ld; }   // RED: no load -> add -> store chain
                     }
                 };
                 auto put_db = [&](float* d, int buf, int row) {
                     const float t = (db_at(buf, 0, row) + db_at(buf, 1, row)) + (db_at(buf, 2, row) + db_at(buf, 3, row));
-                    *d = tile_iter ? *d + t : t;
+                    if (tile_iter) atomicAdd(d, t); else *d = t;
                 };
                 auto dw_wait = [&]() -> uint32_t {
                     const uint32_t b = dk % ndw, r = dk / ndw;
@@ -475,23 +479,33 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
             const uint32_t tp = (uint32_t)(tile_iter & 1);
             const long row0 = (long)tile * kF2Jets;
             const int nvalid = (int)min((long)kF2Jets, a.B - row0);
-            if (tid < 64) s_w[tid] = (tid < nvalid && !SCORE) ? a.w[row0 + tid] : 0.f;
+            if (tid < 64) {
+                // coefficients of the two loss terms: (w, beta w) of get_losses, unit weights for the raw pre-pass, or the per-jet
+                // derivatives of the outlier-exposure loss (combine_kernel) when the step trains on bkg + OoD rows at once
+                float cr = 0.f, ck = 0.f;
+                if (tid < nvalid && !SCORE) {
+                    if (a.c_rec) { cr = a.c_rec[row0 + tid]; ck = a.c_kld[row0 + tid]; }
+                    else if (a.w) { cr = a.w[row0 + tid]; ck = a.beta * cr; }
+                    else { cr = 1.f; ck = 1.f; }
+                }
+                s_w[tid] = cr; s_wk[tid] = ck;
+            }
             {   // pull the next tile's rows of X towards L2
                 const long nrow0 = row0 + (long)gridDim.x * kF2Jets;
                 const long nbytes = min((long)kF2Jets, a.B - nrow0) * D * 4;
-                const char* nx = reinterpret_cast<const char*>(a.x + nrow0 * D);
+                const char* nx = reinterpret_cast<const char*>(xrow(nrow0));
                 for (long o = (long)tid * 128; o < nbytes; o += kF3Workers * 32 * 128) prefetch_l2(nx + o);
             }
             // reparameterisation noise of the tile -> s_eps[l][jet]: external eps, or one Philox counter (row, quad, step)
             if (a.eps) {
                 for (int i = tid; i < 64 * L; i += kF3Workers * 32) {
                     const int j = i / L, l = i - j * L;
-                    s_eps[l * 64 + j] = j < nvalid ? __ldg(a.eps + (row0 + j) * L + l) : 0.f;
+                    s_eps[l * 64 + j] = j < nvalid ? __ldg(a.eps + nrow(row0 + j) * L + l) : 0.f;
                 }
             } else if (tid < 64 * ((L + 3) >> 2)) {
                 const int j = tid & 63, quad = tid >> 6;
                 float nrm[4];
-                philox_normal4(a.seed, a.row_offset + (unsigned long long)(row0 + j), (unsigned)quad, a.step, nrm);
+                philox_normal4(a.seed, a.row_offset + (unsigned long long)nrow(row0 + j), (unsigned)quad, a.step, nrm);
 #pragma unroll
                 for (int t = 0; t < 4; ++t) if (4 * quad + t < L) s_eps[(4 * quad + t) * 64 + j] = nrm[t];
             }
@@ -504,7 +518,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     const int idx = tid + kF3Workers * 32 * it, rr = idx >> 4, c4 = (idx & 15) << 2, col = 64 * c + c4;
                     float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (c < P.nX && rr < nvalid) {
-                        const float* p = a.x + (row0 + rr) * D + col;
+                        const float* p = xrow(row0 + rr) + col;
                         if (col + 3 < D && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) t = __ldg(reinterpret_cast<const float4*>(p));
                         else {
                             if (col < D) t.x = __ldg(p);
@@ -655,7 +669,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     // this thread's 16 x values of the chunk (L2-resident since stage 0), issued before the accumulator wait
                     float xv[16];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) xv[j] = (valid && jc0 + j < nvalid) ? __ldg(a.x + (row0 + jc0 + j) * D + f) : 0.f;
+                    for (int j = 0; j < 16; ++j) xv[j] = (valid && jc0 + j < nvalid) ? __ldg(xrow(row0 + jc0 + j) + f) : 0.f;
                     const float bias = valid ? __ldg(a.theta + st.seg_b[0] + f) : 0.f;
                     const uint32_t yb = yk & 1;
                     wait_acc(&yfull[yb], (yk >> 1) & 1);
@@ -698,7 +712,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                                 const float cl = ay < __int_as_float(0x7f800000) ? fminf(fmaxf(yr, -kClip), kClip) : 0.f;
                                 const float d = valid ? cl - xv[j] : 0.f;
                                 rec_acc[j] += fabsf(d);
-                                const float sg = d == 0.f ? 0.f : copysignf(wsc[j], d);      // w * sign(d) / D
+                                const float sg = d == 0.f ? 0.f : (d < 0.f ? -wsc[j] : wsc[j]);   // coefficient * sign(d) / D (the OE coefficient can be negative)
                                 const float gy = ay <= kClip ? sg : 0.f;
                                 dbs += gy; y[j] = gy;
                             }
@@ -749,7 +763,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                         for (int j = 0; j < 16; ++j) {
                             float gm = 0.f, gl = 0.f;
                             if (lane < L) {
-                                const float m = mu[j] + b_mu, v = lv[j] + b_lv, gkw = a.beta * s_w[jc0 + j];
+                                const float m = mu[j] + b_mu, v = lv[j] + b_lv, gkw = s_wk[jc0 + j];
                                 const float s_raw = __expf(v * 0.5f), e_raw = s_raw * s_raw;
                                 gm = gz[j] + gkw * m * inv_l;
                                 gl = gkw * (-(1.f - (clip_pass(e_raw) ? e_raw : 0.f)) * 0.5f * inv_l)
@@ -795,7 +809,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                 float lr_ = 0.f, lk = 0.f, tot = 0.f;
                 if (j < nvalid) {
                     const float rec = (s_rec[j] + s_rec[64 + j] + s_rec[128 + j] + s_rec[192 + j]) / (float)D, wj = s_w[j];
-                    lr_ = rec * wj; lk = s_kld[j] * wj * a.beta; tot = lr_ + lk + 0.f;
+                    lr_ = rec * wj; lk = s_kld[j] * s_wk[j]; tot = lr_ + lk + 0.f;
                     if (a.per_jet) {
                         a.per_jet[row0 + j] = lr_; a.per_jet[a.B + row0 + j] = lk;
                         a.per_jet[2 * a.B + row0 + j] = 0.f; a.per_jet[3 * a.B + row0 + j] = tot;

@@ -95,6 +95,7 @@ struct FusedState {
     uint32_t img_bytes = 0;
     bool img_dirty = true, last_fused = false;
     int last_grid = 0;
+    float* oe_pj = nullptr; float* oe_c = nullptr; long oe_cap = 0;   // fused outlier-exposure step: raw [4][2B] losses, [2][2B] coefficients
 };
 }
 
@@ -103,7 +104,7 @@ Engine::~Engine() {
     if (dp_buf) cudaFree(dp_buf);
     if (theta) cudaFree(theta);
     if (arena) cudaFree(arena);
-    if (fz) { if (fz->wimg) cudaFree(fz->wimg); if (fz->pos) cudaFree(fz->pos); if (fz->parts) cudaFree(fz->parts); delete fz; }
+    if (fz) { if (fz->wimg) cudaFree(fz->wimg); if (fz->pos) cudaFree(fz->pos); if (fz->parts) cudaFree(fz->parts); if (fz->oe_pj) cudaFree(fz->oe_pj); if (fz->oe_c) cudaFree(fz->oe_c); delete fz; }
 }
 
 // launch with the programmatic-stream-serialization attribute (PDL): the kernel may start while its predecessor in the
@@ -476,6 +477,13 @@ int Engine::losses(const float* x_bkg, const float* w_bkg, const float* x_ood, c
         } else if (eps) return fail(OEVAE_EINVAL, "eps given but noise_mode is not EXTERNAL");
         return fused_losses(x_bkg, w_bkg, eps, B, beta, per_jet, sums, want_grad, s);
     }
+    const bool same_eps = cfg.noise_mode == OEVAE_NOISE_FIXED || (cfg.noise_mode == OEVAE_NOISE_EXTERNAL && n_eps == 1);
+    if (fz && fz->v2 && fz->v3 && x_ood && B > 0 && x_bkg && same_eps && !getenv("OEVAE_OE_LAYERED")) {
+        if (cfg.noise_mode == OEVAE_NOISE_EXTERNAL) {
+            if (!eps) return fail(OEVAE_EINVAL, "noise_mode EXTERNAL needs eps");
+        } else if (eps) return fail(OEVAE_EINVAL, "eps given but noise_mode is not EXTERNAL");
+        return fused_oe(x_bkg, w_bkg, x_ood, w_ood, eps, B, beta, lamb, margin, per_jet, sums, want_grad, s);
+    }
     if (fz && want_grad) fz->last_fused = false;
     Pass p;
     TRY(plan(p, x_bkg, x_ood, eps, n_eps, B));
@@ -489,6 +497,56 @@ int Engine::losses(const float* x_bkg, const float* w_bkg, const float* x_ood, c
     { PROF("combine", s); combine_kernel<<<cdiv(B, 256), 256, 0, s>>>(ca); }
     CKL();
     if (want_grad) TRY(backward(p, s));
+    return 0;
+}
+
+// Outlier-exposure step (models.py:86-132, train_step 147-155) on the fused kernel, for the noise modes in which the bkg and OoD
+// passes see the same eps (the reference's fixed-seed Sampling layer; EXTERNAL with one eps block):
+//   1. forward-only fused3 pass over the virtual batch [bkg ; OoD] with unit weights -> raw per-jet rec / kld of both halves,
+//   2. combine_kernel: per-jet OE loss, per-jet outputs / sums, and d loss / d rec, d loss / d kld of every row,
+//   3. fused3 training pass over the same 2B rows with those derivatives as the per-jet coefficients of the two loss terms.
+int Engine::fused_oe(const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood, const float* eps, long B,
+                     float beta, float lamb, float margin, float* per_jet, double* sums, bool want_grad, cudaStream_t s) {
+    FusedState& f = *fz;
+    if (f.img_dirty) {
+        AdamImgArgs ai{};
+        ai.theta = theta; ai.n = P; ai.wimg = f.wimg; ai.pos = f.pos;
+        { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, kAdamCols), kAdamCols * kAdamSlices, 0, s>>>(ai); }
+        CKL();
+        f.img_dirty = false;
+    }
+    const long Bt = 2 * B;
+    if (Bt > f.oe_cap) {
+        CK(cudaStreamSynchronize(s));
+        if (f.oe_pj) cudaFree(f.oe_pj);
+        if (f.oe_c) cudaFree(f.oe_c);
+        f.oe_pj = f.oe_c = nullptr; f.oe_cap = 0;
+        CK(cudaMalloc(&f.oe_pj, 4 * Bt * sizeof(float)));
+        CK(cudaMalloc(&f.oe_c, 2 * Bt * sizeof(float)));
+        f.oe_cap = Bt;
+    }
+    F2Args b{};
+    b.x = x_bkg; b.x2 = x_ood; b.B1 = B; b.noise_mod = B; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = f.parts;
+    b.B = Bt; b.n_tiles = (int)((Bt + kF2Jets - 1) / kF2Jets); b.mse = mse_type();
+    b.beta = 1.f; b.seed = cfg.seed; b.row_offset = row_offset; b.step = 0u;
+    ++calls;
+    const int grid = std::min(b.n_tiles, n_sm);
+    b.w = nullptr; b.per_jet = f.oe_pj; b.train = 0;        // raw rec -> oe_pj[0..2B), raw kld -> oe_pj[2B..4B)
+    { PROF("fused_oe_fwd", s); CK(launch_pdl(fused3_kernel<false>, dim3(grid), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b)); }
+    CKL();
+    CombineArgs ca{};
+    ca.rec = f.oe_pj; ca.kld = f.oe_pj + Bt; ca.w = w_bkg; ca.w_ood = w_ood;
+    ca.g_rec = want_grad ? f.oe_c : nullptr; ca.g_kld = want_grad ? f.oe_c + Bt : nullptr;
+    ca.per_jet = per_jet; ca.sums = sums;
+    ca.B = B; ca.n_groups = 2; ca.oe_type = cfg.oe_type; ca.have_ood = 1;
+    ca.beta = beta; ca.lamb = lamb; ca.margin = margin;
+    { PROF("combine", s); combine_kernel<<<cdiv(B, 256), 256, 0, s>>>(ca); }
+    CKL();
+    if (!want_grad) return 0;
+    b.c_rec = f.oe_c; b.c_kld = f.oe_c + Bt; b.per_jet = nullptr; b.sums = nullptr; b.train = 1;
+    { PROF("fused_oe_train", s); CK(launch_pdl(fused3_kernel<false>, dim3(grid), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b)); }
+    CKL();
+    f.last_fused = true; f.last_grid = grid;
     return 0;
 }
 
