@@ -27,36 +27,7 @@ constexpr uint32_t kF3_TDW = 320;
 
 namespace f3 {
 using namespace umma;
-// Single-thread tcgen05 instructions issued from WARP-UNIFORM code: every lane of the issuer warp runs the same control
-// flow with the same values and elect.sync picks the lane that executes the instruction.  The operands then stay in
-// uniform registers; issuing from a divergent `if (lane == 0)` region makes ptxas wrap every MMA in an
-// ELECT / 7x R2UR.BROADCAST / BRA.U.ANY loop (~110 cycles per MMA measured, against ~48 of operand fetch).
-__device__ __forceinline__ void mma_e(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred p, pe;\n\t"
-        "elect.sync _|pe, 0xffffffff;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-        "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
-}
-__device__ __forceinline__ void commit_e(uint64_t* bar) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred pe;\n\t"
-        "elect.sync _|pe, 0xffffffff;\n\t"
-        "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t"
-        "}" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void arrive_e(uint64_t* bar) {
-    asm volatile(
-        "{\n\t"
-        ".reg .pred pe;\n\t"
-        ".reg .b64 st;\n\t"
-        "elect.sync _|pe, 0xffffffff;\n\t"
-        "@pe mbarrier.arrive.shared::cta.b64 st, [%0];\n\t"
-        "}" ::"r"(smem_u32(bar)) : "memory");
-}
+// mma_e / commit_e / arrive_e (umma.cuh): single-thread tcgen05 instructions issued from warp-uniform code
 // D[128 x N] (+)= A * B over nk k-steps, bf16x3 (Ahi*Bhi + Ahi*Blo + Alo*Bhi); see f2::issue_core
 __device__ __forceinline__ void issue_e(uint32_t d, const f2::Opnd& A, const f2::Opnd& B, int nk, int N, bool acc) {
     uint64_t ah = f2::desc(A, 0, false), al = f2::desc(A, 0, true), bh = f2::desc(B, 0, false), bl = f2::desc(B, 0, true);

@@ -272,7 +272,7 @@ int Engine::reserve(long rows) {
 
 // ---------------------------------------------------------------------------------------------- GEMM launchers
 template <bool SPLIT>
-static int umma_smem_bytes(int BN) { return 2 * (128 * 128 + BN * 128) * (SPLIT ? 2 : 1) + 1024; }
+static int umma_smem_bytes(int BN) { return 2 * (128 * 128 + (BN + 63) / 64 * 8192) * (SPLIT ? 2 : 1) + 1024; }   // MN-major B: whole 64-row blocks
 
 template <bool A_TC, bool B_TC, bool SPLIT>
 static cudaError_t umma_launch(const GemmArgs& g, int n_slots, cudaStream_t s) {
@@ -285,7 +285,7 @@ static cudaError_t umma_launch(const GemmArgs& g, int n_slots, cudaStream_t s) {
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    dim3 grid(cdiv(g.R, 128), cdiv(g.Cn, BN), n_slots);
+    dim3 grid((unsigned)(cdiv(g.R, 128) * cdiv(g.Cn, BN)), 1, n_slots);
     umma_gemm_kernel<A_TC, B_TC, SPLIT><<<grid, 256, smem, s>>>(g, BN, tmem_cols);
     return cudaSuccess;
 }

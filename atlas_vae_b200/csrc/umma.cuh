@@ -108,5 +108,66 @@ __device__ __forceinline__ uint32_t sw128_off(int r, int c) {
     return (uint32_t)(r * 128 + ((((c >> 3) ^ (r & 7)) << 4) | ((c & 7) << 1)));
 }
 
+// Single-thread tcgen05 instructions issued from WARP-UNIFORM code: every lane of the issuer warp runs the same control
+// flow with the same values and elect.sync picks the lane that executes the instruction.  The operands then stay in
+// uniform registers; issuing from a divergent `if (lane == 0)` region makes ptxas wrap every MMA in an
+// ELECT / 7x R2UR.BROADCAST / BRA.U.ANY loop (~110 cycles per MMA measured, against ~48 of operand fetch).
+__device__ __forceinline__ void mma_e(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p, pe;\n\t"
+        "elect.sync _|pe, 0xffffffff;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "@pe tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+        "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void commit_e(uint64_t* bar) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred pe;\n\t"
+        "elect.sync _|pe, 0xffffffff;\n\t"
+        "@pe tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t"
+        "}" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void arrive_e(uint64_t* bar) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred pe;\n\t"
+        ".reg .b64 st;\n\t"
+        "elect.sync _|pe, 0xffffffff;\n\t"
+        "@pe mbarrier.arrive.shared::cta.b64 st, [%0];\n\t"
+        "}" ::"r"(smem_u32(bar)) : "memory");
+}
+// x0, x1 -> packed bf16 hi parts and packed bf16 lo parts (x ~= hi + lo); residuals of non-finite x are dropped
+__device__ __forceinline__ void split_pair(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+    const __nv_bfloat162 hh = __floats2bfloat162_rn(x0, x1);
+    hi = *reinterpret_cast<const uint32_t*>(&hh);
+    float r0 = x0 - __uint_as_float(hi << 16), r1 = x1 - __uint_as_float(hi & 0xffff0000u);
+    r0 = (fabsf(x0) <= 3.0e38f) ? r0 : 0.f; r1 = (fabsf(x1) <= 3.0e38f) ? r1 : 0.f;
+    const __nv_bfloat162 ll = __floats2bfloat162_rn(r0, r1);
+    lo = *reinterpret_cast<const uint32_t*>(&ll);
+}
+__device__ __forceinline__ uint32_t round_pair(float x0, float x1) {
+    const __nv_bfloat162 hh = __floats2bfloat162_rn(x0, x1);
+    return *reinterpret_cast<const uint32_t*>(&hh);
+}
+// MN-major SWIZZLE_128B descriptor (tile = [K rows x 64 MN elements], 128 B per K row; lbo = distance between 64-element MN
+// blocks) and the instruction descriptor with per-operand major flags
+__device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t saddr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+__host__ __device__ __forceinline__ uint32_t idesc_bf16_major(int M, int N, int a_mn, int b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
 }  // namespace umma
+using umma::smem_desc_sw128_mn;
+using umma::idesc_bf16_major;
 }  // namespace oevae

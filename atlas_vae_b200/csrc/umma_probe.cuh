@@ -6,22 +6,6 @@
 
 namespace oevae {
 
-// MN-major SWIZZLE_128B descriptor: rows = K (128 B each, 8-row groups SBO = 1024 B apart),
-// 64-element MN blocks lbo_bytes apart.
-__device__ __forceinline__ uint64_t smem_desc_sw128_mn(uint32_t saddr, uint32_t lbo_bytes) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
-    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
-    d |= (uint64_t)(1024 >> 4) << 32;
-    d |= (uint64_t)1 << 46;
-    d |= (uint64_t)2 << 61;
-    return d;
-}
-__host__ __device__ __forceinline__ uint32_t idesc_bf16_major(int M, int N, int a_mn, int b_mn) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
-           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
-
 // one CTA, 128 threads.  K <= 128 rows (multiple of 16), M in {64,128}, N multiple of 16 <= 128.
 // raw_out: [128 lanes][N] dump of the TMEM accumulator region.
 __global__ void __launch_bounds__(128, 1) umma_probe_kernel(const float* __restrict__ A, const float* __restrict__ B,
