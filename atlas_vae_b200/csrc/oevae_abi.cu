@@ -272,10 +272,12 @@ int Engine::reserve(long rows) {
 
 // ---------------------------------------------------------------------------------------------- GEMM launchers
 template <bool SPLIT>
-static int umma_smem_bytes(int BN) { return 2 * (128 * 128 + (BN + 63) / 64 * 8192) * (SPLIT ? 2 : 1) + 1024; }   // MN-major B: whole 64-row blocks
+static int umma_smem_bytes(int BN) {                        // two operand stages (MN-major B: whole 64-row blocks) or the epilogue staging tile
+    return std::max(2 * (128 * 128 + (BN + 63) / 64 * 8192) * (SPLIT ? 2 : 1), 128 * (BN + 4) * 4) + 1024;
+}
 
 template <bool A_TC, bool B_TC, bool SPLIT>
-static cudaError_t umma_launch(const GemmArgs& g, int n_slots, cudaStream_t s) {
+static cudaError_t umma_launch(const GemmArgs& g, int n_slots, int n_sm, cudaStream_t s) {
     int BN = std::min(128, (g.Cn + 15) / 16 * 16);
     int tmem_cols = 32; while (tmem_cols < BN) tmem_cols <<= 1;
     int smem = umma_smem_bytes<SPLIT>(BN);
@@ -285,8 +287,8 @@ static cudaError_t umma_launch(const GemmArgs& g, int n_slots, cudaStream_t s) {
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    dim3 grid((unsigned)(cdiv(g.R, 128) * cdiv(g.Cn, BN)), 1, n_slots);
-    umma_gemm_kernel<A_TC, B_TC, SPLIT><<<grid, 256, smem, s>>>(g, BN, tmem_cols);
+    const long n_tiles = (long)cdiv(g.R, 128) * cdiv(g.Cn, BN) * n_slots;
+    umma_gemm_kernel<A_TC, B_TC, SPLIT><<<(unsigned)std::min<long>(n_tiles, n_sm), kGT, smem, s>>>(g, BN, tmem_cols, n_slots);
     return cudaSuccess;
 }
 
@@ -302,9 +304,9 @@ int Engine::launch_gemm(const GemmArgs& g, int kind, int n_slots, cudaStream_t s
     } else {
         const bool split = cfg.precision == OEVAE_PREC_BF16X3;
         cudaError_t e;
-        if (kind == 0) e = split ? umma_launch<true, false, true>(g, n_slots, s) : umma_launch<true, false, false>(g, n_slots, s);
-        else if (kind == 1) e = split ? umma_launch<true, true, true>(g, n_slots, s) : umma_launch<true, true, false>(g, n_slots, s);
-        else e = split ? umma_launch<false, false, true>(g, n_slots, s) : umma_launch<false, false, false>(g, n_slots, s);
+        if (kind == 0) e = split ? umma_launch<true, false, true>(g, n_slots, n_sm, s) : umma_launch<true, false, false>(g, n_slots, n_sm, s);
+        else if (kind == 1) e = split ? umma_launch<true, true, true>(g, n_slots, n_sm, s) : umma_launch<true, true, false>(g, n_slots, n_sm, s);
+        else e = split ? umma_launch<false, false, true>(g, n_slots, n_sm, s) : umma_launch<false, false, false>(g, n_slots, n_sm, s);
         CK(e);
     }
     CKL();
