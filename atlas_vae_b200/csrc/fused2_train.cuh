@@ -141,11 +141,11 @@ struct F2Args {
     // SCORE instantiation only (anomaly scoring, vae.py:163-167 + utils.py:346-386): nullable [B] outputs
     float* s_mse; float* s_mae; float* s_kld; float* s_jsd; float* s_lat; unsigned char* s_fin;
     float* s_xhat;                                          // nullable [B, D]: clip_values(X_hat) of the pass (vae.py:165)
-    // fused3 only — outlier-exposure step (models.py:86-132): rows [B1, B) of the batch are read from x2 (the OoD sample), the
-    // loss-term coefficients come per jet from c_rec / c_kld (nullable pair; else w and beta w, or 1 and 1 when w is null too),
-    // and the noise of row r is the noise of row r % noise_mod (0 = off: both halves see the same eps, as the reference's
-    // fixed-seed Sampling layer gives them)
-    const float* x2; long B1; const float* c_rec; const float* c_kld; long noise_mod;
+    // fused3 only -- outlier-exposure step (models.py:86-132): rows [B1, B) of the batch are read from x2 (the OoD sample) and
+    // start at a tile boundary (n_tiles = ceil(B1 / 64) + ceil((B - B1) / 64)); the loss-term coefficients come per jet from
+    // c_rec / c_kld (nullable pair; else w and beta w, or 1 and 1 when w is null too); row i of either half is given the noise
+    // of row i, as the reference's fixed-seed Sampling layer gives them
+    const float* x2; long B1; const float* c_rec; const float* c_kld;
 };
 
 

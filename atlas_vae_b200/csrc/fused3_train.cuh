@@ -95,9 +95,16 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                                                                        // is rewritten two worker_sync()s after its last reader)
     float* s_eps = s_db + 3072;                                        // [L][64]
     float* s_wk = s_eps + 64 * L;                                      // [64] per-jet coefficient of the KLD term (beta * w, or c_kld)
-    // row r of the (virtual) batch: rows >= a.B1 come from the second input a.x2 (the OoD sample of the outlier-exposure step)
-    auto xrow = [&](long r) -> const float* { return (a.x2 && r >= a.B1) ? a.x2 + (r - a.B1) * (long)P.D : a.x + r * (long)P.D; };
-    auto nrow = [&](long r) -> long { return a.noise_mod > 0 ? r % a.noise_mod : r; };   // row index the reparameterisation noise is drawn for
+    // Tiles of an outlier-exposure batch (a.x2 != null): the bkg rows [0, B1) fill tiles 0 .. ceil(B1 / 64) - 1 and the OoD rows
+    // [B1, B) start at the NEXT tile, so a tile never mixes the two inputs.  tile_src: first row of the tile in its input, the
+    // input pointer at that row, and how many of the 64 jets exist.
+    auto tile_src = [&](int tile, int& local0, int& nvalid) -> const float* {          // row counts fit 31 bits (oevae.h)
+        const int t1 = a.x2 ? (int)((a.B1 + kF2Jets - 1) / kF2Jets) : 0x7fffffff;        // first tile of the second input
+        const bool second = tile >= t1;
+        local0 = (second ? tile - t1 : tile) * kF2Jets;
+        nvalid = max(0, min(kF2Jets, (int)(second ? a.B - a.B1 : (a.x2 ? a.B1 : a.B)) - local0));
+        return (second ? a.x2 : a.x) + (long)local0 * P.D;
+    };
     auto tile_hi = [&](int k) { return sm + P.tile_off[k]; };
     auto tile_lo = [&](int k) { return sm + P.tile_off[k] + P.tile_rows[k] * 128; };
     auto xslot = [&](int s) { return sm + P.s_off + s * 16384; };      // hi 8 KB, lo 8 KB
@@ -110,9 +117,9 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
     dbg_c[0] = clock64();
     // the first tile's rows of X start moving towards L2 while the CTA sets itself up
     if (warp < kF3Workers && (int)blockIdx.x < a.n_tiles) {
-        const long r0 = (long)blockIdx.x * kF2Jets;
-        const long nbytes = min((long)kF2Jets, a.B - r0) * P.D * 4;
-        const char* px = reinterpret_cast<const char*>(xrow(r0));
+        int l0, nv;
+        const char* px = reinterpret_cast<const char*>(tile_src((int)blockIdx.x, l0, nv));
+        const long nbytes = (long)nv * P.D * 4;
         for (long o = (long)tid * 128; o < nbytes; o += kF3Workers * 32 * 128) prefetch_l2(px + o);
     }
     dbg_c[1] = clock64();
@@ -448,13 +455,16 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
         int tile_iter = 0;
         for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_iter) {
             const uint32_t tp = (uint32_t)(tile_iter & 1);
-            const long row0 = (long)tile * kF2Jets;
-            const int nvalid = (int)min((long)kF2Jets, a.B - row0);
+            int local0, nvalid;                                       // local0: row inside its input = the row the noise is drawn for
+            const float* xa = tile_src(tile, local0, nvalid);
+            // row in the per-jet arrays ([bkg ; OoD], compact); recomputed where it is used instead of living through the tile
+            auto row0_of = [&]() -> long { int l0, nv; tile_src(tile, l0, nv); return (tile * kF2Jets == l0) ? (long)l0 : a.B1 + l0; };
             if (tid < 64) {
                 // coefficients of the two loss terms: (w, beta w) of get_losses, unit weights for the raw pre-pass, or the per-jet
                 // derivatives of the outlier-exposure loss (combine_kernel) when the step trains on bkg + OoD rows at once
                 float cr = 0.f, ck = 0.f;
                 if (tid < nvalid && !SCORE) {
+                    const long row0 = row0_of();
                     if (a.c_rec) { cr = a.c_rec[row0 + tid]; ck = a.c_kld[row0 + tid]; }
                     else if (a.w) { cr = a.w[row0 + tid]; ck = a.beta * cr; }
                     else { cr = 1.f; ck = 1.f; }
@@ -462,21 +472,21 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                 s_w[tid] = cr; s_wk[tid] = ck;
             }
             {   // pull the next tile's rows of X towards L2
-                const long nrow0 = row0 + (long)gridDim.x * kF2Jets;
-                const long nbytes = min((long)kF2Jets, a.B - nrow0) * D * 4;
-                const char* nx = reinterpret_cast<const char*>(xrow(nrow0));
+                int l0, nv;
+                const char* nx = reinterpret_cast<const char*>(tile_src(tile + (int)gridDim.x, l0, nv));
+                const long nbytes = (tile + (int)gridDim.x < a.n_tiles) ? (long)nv * D * 4 : 0;
                 for (long o = (long)tid * 128; o < nbytes; o += kF3Workers * 32 * 128) prefetch_l2(nx + o);
             }
             // reparameterisation noise of the tile -> s_eps[l][jet]: external eps, or one Philox counter (row, quad, step)
             if (a.eps) {
                 for (int i = tid; i < 64 * L; i += kF3Workers * 32) {
                     const int j = i / L, l = i - j * L;
-                    s_eps[l * 64 + j] = j < nvalid ? __ldg(a.eps + nrow(row0 + j) * L + l) : 0.f;
+                    s_eps[l * 64 + j] = j < nvalid ? __ldg(a.eps + (local0 + j) * L + l) : 0.f;
                 }
             } else if (tid < 64 * ((L + 3) >> 2)) {
                 const int j = tid & 63, quad = tid >> 6;
                 float nrm[4];
-                philox_normal4(a.seed, a.row_offset + (unsigned long long)nrow(row0 + j), (unsigned)quad, a.step, nrm);
+                philox_normal4(a.seed, a.row_offset + (unsigned long long)(local0 + j), (unsigned)quad, a.step, nrm);
 #pragma unroll
                 for (int t = 0; t < 4; ++t) if (4 * quad + t < L) s_eps[(4 * quad + t) * 64 + j] = nrm[t];
             }
@@ -489,7 +499,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     const int idx = tid + kF3Workers * 32 * it, rr = idx >> 4, c4 = (idx & 15) << 2, col = 64 * c + c4;
                     float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
                     if (c < P.nX && rr < nvalid) {
-                        const float* p = xrow(row0 + rr) + col;
+                        const float* p = xa + (long)rr * D + col;
                         if (col + 3 < D && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) t = __ldg(reinterpret_cast<const float4*>(p));
                         else {
                             if (col < D) t.x = __ldg(p);
@@ -640,7 +650,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     // this thread's 16 x values of the chunk (L2-resident since stage 0), issued before the accumulator wait
                     float xv[16];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) xv[j] = (valid && jc0 + j < nvalid) ? __ldg(xrow(row0 + jc0 + j) + f) : 0.f;
+                    for (int j = 0; j < 16; ++j) xv[j] = (valid && jc0 + j < nvalid) ? __ldg(xa + (jc0 + j) * D + f) : 0.f;
                     const float bias = valid ? __ldg(a.theta + st.seg_b[0] + f) : 0.f;
                     const uint32_t yb = yk & 1;
                     wait_acc(&yfull[yb], (yk >> 1) & 1);
@@ -659,7 +669,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                                 rec_acc[j] += d * d; sc_mae[j] += fabsf(d);
                                 if (a.s_kld) sc_kl[j] += kld_term_fast(p, qv);
                                 if (a.s_jsd) { const float mm = (p + qv) / 2.f; sc_js[j] += (kld_term_fast(p, mm) + kld_term_fast(qv, mm)) / 2.f; }
-                                if (a.s_xhat) a.s_xhat[(row0 + jc0 + j) * D + f] = qv;
+                                if (a.s_xhat) a.s_xhat[(row0_of() + jc0 + j) * D + f] = qv;
                             }
                         }
                     } else {
@@ -768,6 +778,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                 if (tid < nvalid) {
                     const int j = tid;
                     auto q4 = [&](const float* b) { return (b[j] + b[64 + j]) + (b[128 + j] + b[192 + j]); };
+                    const long row0 = row0_of();
                     if (a.s_mse) a.s_mse[row0 + j] = q4(s_rec) / (float)D;
                     if (a.s_mae) a.s_mae[row0 + j] = q4(s_db) / (float)D;
                     if (a.s_kld) a.s_kld[row0 + j] = q4(s_db + 256);
@@ -782,6 +793,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     const float rec = (s_rec[j] + s_rec[64 + j] + s_rec[128 + j] + s_rec[192 + j]) / (float)D, wj = s_w[j];
                     lr_ = rec * wj; lk = s_kld[j] * s_wk[j]; tot = lr_ + lk + 0.f;
                     if (a.per_jet) {
+                        const long row0 = row0_of();
                         a.per_jet[row0 + j] = lr_; a.per_jet[a.B + row0 + j] = lk;
                         a.per_jet[2 * a.B + row0 + j] = 0.f; a.per_jet[3 * a.B + row0 + j] = tot;
                     }

@@ -528,8 +528,8 @@ int Engine::fused_oe(const float* x_bkg, const float* w_bkg, const float* x_ood,
         f.oe_cap = Bt;
     }
     F2Args b{};
-    b.x = x_bkg; b.x2 = x_ood; b.B1 = B; b.noise_mod = B; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = f.parts;
-    b.B = Bt; b.n_tiles = (int)((Bt + kF2Jets - 1) / kF2Jets); b.mse = mse_type();
+    b.x = x_bkg; b.x2 = x_ood; b.B1 = B; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = f.parts;
+    b.B = Bt; b.n_tiles = 2 * (int)((B + kF2Jets - 1) / kF2Jets); b.mse = mse_type();   // each half starts at a tile boundary
     b.beta = 1.f; b.seed = cfg.seed; b.row_offset = row_offset; b.step = 0u;
     ++calls;
     const int grid = std::min(b.n_tiles, n_sm);

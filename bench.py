@@ -252,6 +252,55 @@ def run_ours(args):
                'kernels': [{'name': r[0], 'launches_per_pass': r[1] / n_sp, 'us_per_launch': 1e3 * r[2] / r[1], 'share': r[2] / stot} for r in srows[:4]]}
     del mass, jzw
 
+    # ---- the other two training shapes of BASELINE.json, one rank, device-resident (reported beside the headline, not as it):
+    #   oe   = cfg-3 step: batch of 5000 QCD jets paired with 5000 OoD jets, OE_type 'KLD' (models.py:86-132), fused path
+    #   wide = cfg-5 step: FC_layers [1024, 512, 256, 64], batch 65536 (layered tcgen05 GEMM path, tensor-bound regime)
+    extra = {}
+    if world == 1 and not args.no_extra:
+        def timed(fn, n_warm, n):
+            for i in range(n_warm): fn(i)
+            torch.cuda.synchronize()
+            e0.record()
+            for i in range(n_warm, n_warm + n): fn(i)
+            e1.record(); torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / n
+        n_ob = 40
+        Xo = make_workload(dev, n_ob * BATCH, 4321)               # stand-in OoD sample (320 MB, larger than L2)
+        voe = DeviceVAE(FC, D, 'KLD', args.precision, 'fixed', 0, local, BATCH)
+        voe.set_params(init_params(FC, D, 0))
+        def oe_step(i):
+            b, o = i % n_batches, i % n_ob
+            voe.train_step(X[b * BATCH:(b + 1) * BATCH], wts[:BATCH], Xo[o * BATCH:(o + 1) * BATCH], wts[:BATCH], None, LR, BETA, 1.0, 1.0, None, sums)
+        oe_ms = timed(oe_step, 5, 100)
+        OE_ALG = 2 * (D * 4 + 4)                                  # 3,208 B per (bkg, OoD) pair
+        extra['oe'] = {'metric': 'train pairs/s (cfg-3: bkg + OoD batch, OE_type KLD)', 'value': BATCH / (oe_ms * 1e-3), 'unit': 'pairs/s',
+                       'ms_per_step': oe_ms, 'pairs_per_step': BATCH,
+                       'roofline': {'bound': 'hbm', 'achieved': OE_ALG * BATCH / (oe_ms * 1e-3) / 1e9, 'peak': peak, 'unit': 'GB/s',
+                                    'frac': OE_ALG * BATCH / (oe_ms * 1e-3) / 1e9 / peak, 'alg_bytes_per_pair': OE_ALG}}
+        del voe, Xo
+        FCW, BW = [1024, 512, 256, 64], 65536
+        vw = DeviceVAE(FCW, D, 'KLD', args.precision, 'fixed', 0, local, BW)
+        vw.set_params(init_params(FCW, D, 0))
+        n_wb = n_jets // BW
+        if n_wb >= 1:
+            def wide_step(i):
+                b = i % n_wb
+                vw.train_step(X[b * BW:(b + 1) * BW], wts[:BW], None, None, None, LR, BETA, 0., 0., None, sums)
+            w_ms = timed(wide_step, 3, 10)
+            hid = FCW[:-1]; L = FCW[-1]
+            enc = D * hid[0] + sum(a * b for a, b in zip(hid[:-1], hid[1:])) + 2 * hid[-1] * L
+            dec = L * hid[-1] + sum(a * b for a, b in zip(hid[::-1][:-1], hid[::-1][1:])) + hid[0] * D
+            f_train = 3 * 2 * (enc + dec) - 2 * D * hid[0]        # 12,255,232 FLOP per jet
+            try: tpk = float(json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))['bf16_tflops_sustained']); tsrc = 'measured (sustained cuBLAS bf16)'
+            except Exception: tpk, tsrc = 1500.0, 'fallback'
+            ach = f_train * BW / (w_ms * 1e-3) / 1e12
+            extra['wide'] = {'metric': 'train jets/s (cfg-5: FC_layers [1024,512,256,64], batch 65536)', 'value': BW / (w_ms * 1e-3), 'unit': UNIT,
+                             'ms_per_step': w_ms, 'flop_per_jet': f_train,
+                             'roofline': {'bound': 'tensor', 'achieved': ach, 'peak': tpk, 'unit': 'TFLOP/s', 'frac': ach / tpk, 'peak_source': tsrc,
+                                          'note': 'algorithmic FLOP (one pass); precision bf16x3 issues three bf16 MMAs per product'}}
+        del vw
+        sums.zero_()
+
     # ---- end to end through the host API: pinned host arrays, H2D per step, D2H of the loss sums per step
     n_e2e = min(n_batches, K)
     Xh = X[:n_e2e * BATCH].cpu().numpy(); wh = np.ones(n_e2e * BATCH, np.float32)
@@ -283,6 +332,7 @@ def run_ours(args):
             'clocks': clk, 'gpu_launches': int(launches),
             'e2e': {'value': e2e_val, 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': 32, 'ms_per_step': e2e_ms / n_e2e},
             'roofline': roof, 'kernels': kernels[:8], 'scoring': scoring}
+    line.update(extra)
     if world == 1 and not args.no_cpu:
         jps, cores, dt, done = cpu_reference_steps(args.cpu_steps, 5, budget_s=20.0)
         line['cpu_baseline'] = {'value': jps, 'unit': UNIT, 'cores': cores, 'kind': 'port',
@@ -299,6 +349,7 @@ def main():
     ap.add_argument('--precision', default='bf16x3', choices=['fp32', 'bf16x3', 'tf32', 'bf16'])
     ap.add_argument('--cpu-steps', type=int, default=300)
     ap.add_argument('--no-cpu', action='store_true')
+    ap.add_argument('--no-extra', action='store_true', help='skip the cfg-3 (OE) and cfg-5 (wide) legs')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)
