@@ -146,6 +146,9 @@ struct F2Args {
     // c_rec / c_kld (nullable pair; else w and beta w, or 1 and 1 when w is null too); row i of either half is given the noise
     // of row i, as the reference's fixed-seed Sampling layer gives them
     const float* x2; long B1; const float* c_rec; const float* c_kld;
+    // paired mode (OE_type 'KLD'): B = number of (bkg, OoD) pairs, tile t = pairs [32 t, 32 t + 32) with the bkg rows (x, w) on jet
+    // columns 0..31 and their OoD partners (x2, w2) on columns 32..63; per_jet / sums get all four loss rows of models.py:123-132
+    int paired; const float* w2; float lamb, margin;
 };
 
 

@@ -65,11 +65,14 @@ __device__ __forceinline__ void warp_arrive(uint64_t* bar, int lane) {
 }
 }  // namespace f3
 
-template <bool SCORE>
+// MODE 0: one input (training step, get_losses, scoring).  MODE 1: paired tiles (OE_type 'KLD').  MODE 2: two inputs [bkg ; OoD] with
+// per-jet loss-term coefficients (raw pre-pass and training pass of the reconstruction-based OE types).
+template <bool SCORE, int MODE = 0>
 __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threads, 1) fused3_kernel(const __grid_constant__ F2Plan P, F2Args a) {
     using namespace umma;
     using namespace f2;
     using namespace f3;
+    constexpr bool PAIRED = MODE == 1, TWOIN = MODE == 2;
     const bool is_train = !SCORE && a.train;
     extern __shared__ unsigned char smem_dyn[];
     __shared__ uint64_t wfull[kF2WSlots], wempty[kF2WSlots], xfull[kF2XSlots], xempty[kF2XSlots];
@@ -98,11 +101,22 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
     // Tiles of an outlier-exposure batch (a.x2 != null): the bkg rows [0, B1) fill tiles 0 .. ceil(B1 / 64) - 1 and the OoD rows
     // [B1, B) start at the NEXT tile, so a tile never mixes the two inputs.  tile_src: first row of the tile in its input, the
     // input pointer at that row, and how many of the 64 jets exist.
+    // Paired mode (PAIRED, OE_type 'KLD', models.py:88-96): tile t holds pairs [32 t, 32 t + 32) -- jet columns 0..31 are the bkg
+    // rows, columns 32..63 their OoD partners -- so relu(KLD(bkg) - KLD(OoD) + margin) and its derivative are formed inside the
+    // tile right after the heads and the whole step is one launch.  tile_src then returns the bkg pointer of the tile.
     auto tile_src = [&](int tile, int& local0, int& nvalid) -> const float* {          // row counts fit 31 bits (oevae.h)
-        const int t1 = a.x2 ? (int)((a.B1 + kF2Jets - 1) / kF2Jets) : 0x7fffffff;        // first tile of the second input
+        if (PAIRED) {
+            local0 = tile * 32; nvalid = max(0, min(32, (int)a.B - local0));
+            return a.x + (long)local0 * P.D;
+        }
+        if (!TWOIN) {
+            local0 = tile * kF2Jets; nvalid = max(0, min(kF2Jets, (int)a.B - local0));
+            return a.x + (long)local0 * P.D;
+        }
+        const int t1 = (int)((a.B1 + kF2Jets - 1) / kF2Jets);                             // first tile of the second input
         const bool second = tile >= t1;
         local0 = (second ? tile - t1 : tile) * kF2Jets;
-        nvalid = max(0, min(kF2Jets, (int)(second ? a.B - a.B1 : (a.x2 ? a.B1 : a.B)) - local0));
+        nvalid = max(0, min(kF2Jets, (int)(second ? a.B - a.B1 : a.B1) - local0));
         return (second ? a.x2 : a.x) + (long)local0 * P.D;
     };
     auto tile_hi = [&](int k) { return sm + P.tile_off[k]; };
@@ -458,16 +472,28 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
             int local0, nvalid;                                       // local0: row inside its input = the row the noise is drawn for
             const float* xa = tile_src(tile, local0, nvalid);
             // row in the per-jet arrays ([bkg ; OoD], compact); recomputed where it is used instead of living through the tile
-            auto row0_of = [&]() -> long { int l0, nv; tile_src(tile, l0, nv); return (tile * kF2Jets == l0) ? (long)l0 : a.B1 + l0; };
-            if (tid < 64) {
+            auto row0_of = [&]() -> long { int l0, nv; tile_src(tile, l0, nv); return (!TWOIN || tile * kF2Jets == l0) ? (long)l0 : a.B1 + l0; };
+            // jets 32..63 of a paired tile sit at xb + j D; column j is a real jet iff (j & cmask) < nvalid
+            const float* xb = PAIRED ? a.x2 + (long)(local0 - 32) * D : xa;
+            auto cidx = [&](int j) { return PAIRED ? (j & 31) : j; };             // index of column j inside its input
+            auto colv = [&](int j) { return cidx(j) < nvalid; };
+            if (PAIRED) {
+                // s_w: coefficient of the reconstruction term (w_bkg | 0); s_wk: beta w_bkg | lambda w_OoD -- the latent backward
+                // turns them into the KLD coefficients of the pair once both KLDs are known
+                if (tid < 64) {
+                    const bool on = (tid & 31) < nvalid;
+                    const float wv = on ? (tid < 32 ? a.w[local0 + tid] : a.w2[local0 + tid - 32]) : 0.f;
+                    s_w[tid] = tid < 32 ? wv : 0.f; s_wk[tid] = (tid < 32 ? a.beta : a.lamb) * wv;
+                }
+            } else if (tid < 64) {
                 // coefficients of the two loss terms: (w, beta w) of get_losses, unit weights for the raw pre-pass, or the per-jet
                 // derivatives of the outlier-exposure loss (combine_kernel) when the step trains on bkg + OoD rows at once
                 float cr = 0.f, ck = 0.f;
                 if (tid < nvalid && !SCORE) {
                     const long row0 = row0_of();
-                    if (a.c_rec) { cr = a.c_rec[row0 + tid]; ck = a.c_kld[row0 + tid]; }
-                    else if (a.w) { cr = a.w[row0 + tid]; ck = a.beta * cr; }
-                    else { cr = 1.f; ck = 1.f; }
+                    if (TWOIN && a.c_rec) { cr = a.c_rec[row0 + tid]; ck = a.c_kld[row0 + tid]; }
+                    else if (TWOIN) { cr = 1.f; ck = 1.f; }
+                    else { cr = a.w[row0 + tid]; ck = a.beta * cr; }
                 }
                 s_w[tid] = cr; s_wk[tid] = ck;
             }
@@ -476,17 +502,21 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                 const char* nx = reinterpret_cast<const char*>(tile_src(tile + (int)gridDim.x, l0, nv));
                 const long nbytes = (tile + (int)gridDim.x < a.n_tiles) ? (long)nv * D * 4 : 0;
                 for (long o = (long)tid * 128; o < nbytes; o += kF3Workers * 32 * 128) prefetch_l2(nx + o);
+                if (PAIRED) {
+                    const char* nx2 = reinterpret_cast<const char*>(a.x2 + (long)l0 * D);
+                    for (long o = (long)tid * 128; o < nbytes; o += kF3Workers * 32 * 128) prefetch_l2(nx2 + o);
+                }
             }
             // reparameterisation noise of the tile -> s_eps[l][jet]: external eps, or one Philox counter (row, quad, step)
             if (a.eps) {
                 for (int i = tid; i < 64 * L; i += kF3Workers * 32) {
                     const int j = i / L, l = i - j * L;
-                    s_eps[l * 64 + j] = j < nvalid ? __ldg(a.eps + (local0 + j) * L + l) : 0.f;
+                    s_eps[l * 64 + j] = colv(j) ? __ldg(a.eps + (local0 + cidx(j)) * L + l) : 0.f;
                 }
             } else if (tid < 64 * ((L + 3) >> 2)) {
                 const int j = tid & 63, quad = tid >> 6;
                 float nrm[4];
-                philox_normal4(a.seed, a.row_offset + (unsigned long long)(local0 + j), (unsigned)quad, a.step, nrm);
+                philox_normal4(a.seed, a.row_offset + (unsigned long long)(local0 + cidx(j)), (unsigned)quad, a.step, nrm);
 #pragma unroll
                 for (int t = 0; t < 4; ++t) if (4 * quad + t < L) s_eps[(4 * quad + t) * 64 + j] = nrm[t];
             }
@@ -498,8 +528,8 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                 for (int it = 0; it < 2; ++it) {
                     const int idx = tid + kF3Workers * 32 * it, rr = idx >> 4, c4 = (idx & 15) << 2, col = 64 * c + c4;
                     float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (c < P.nX && rr < nvalid) {
-                        const float* p = xa + (long)rr * D + col;
+                    if (c < P.nX && colv(rr)) {
+                        const float* p = ((PAIRED && it) ? xb : xa) + (long)rr * D + col;        // it = 1: rows 32..63
                         if (col + 3 < D && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) t = __ldg(reinterpret_cast<const float4*>(p));
                         else {
                             if (col < D) t.x = __ldg(p);
@@ -627,6 +657,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                 publish(&tready[s]);
                 stamp();
             }
+            if (!SCORE && PAIRED) worker_sync();                       // both KLDs of every pair are in s_kld
             // =========================================================== output layer in 128-feature chunks
             float rec_acc[16];
             float sc_mae[SCORE ? 16 : 1], sc_kl[SCORE ? 16 : 1], sc_js[SCORE ? 16 : 1];   // rec_acc doubles as the MSE sum
@@ -650,7 +681,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     // this thread's 16 x values of the chunk (L2-resident since stage 0), issued before the accumulator wait
                     float xv[16];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) xv[j] = (valid && jc0 + j < nvalid) ? __ldg(xa + (jc0 + j) * D + f) : 0.f;
+                    for (int j = 0; j < 16; ++j) xv[j] = (valid && colv(jc0 + j)) ? __ldg(((PAIRED && jc0 >= 32) ? xb : xa) + (jc0 + j) * D + f) : 0.f;
                     const float bias = valid ? __ldg(a.theta + st.seg_b[0] + f) : 0.f;
                     const uint32_t yb = yk & 1;
                     wait_acc(&yfull[yb], (yk >> 1) & 1);
@@ -744,7 +775,14 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                         for (int j = 0; j < 16; ++j) {
                             float gm = 0.f, gl = 0.f;
                             if (lane < L) {
-                                const float m = mu[j] + b_mu, v = lv[j] + b_lv, gkw = s_wk[jc0 + j];
+                                const float m = mu[j] + b_mu, v = lv[j] + b_lv;
+                                float gkw = s_wk[jc0 + j];
+                                if (PAIRED) {
+                                    // d/dKLD of beta w KLD_b + lambda w_o relu(KLD_b - KLD_o + margin): bkg column / OoD column
+                                    const int pc = (jc0 + j) & 31;
+                                    const bool act = s_kld[pc] - s_kld[pc + 32] + a.margin > 0.f;
+                                    gkw = jc0 < 32 ? gkw + (act ? s_wk[pc + 32] : 0.f) : (act ? -gkw : 0.f);
+                                }
                                 const float s_raw = __expf(v * 0.5f), e_raw = s_raw * s_raw;
                                 gm = gz[j] + gkw * m * inv_l;
                                 gl = gkw * (-(1.f - (clip_pass(e_raw) ? e_raw : 0.f)) * 0.5f * inv_l)
@@ -789,18 +827,21 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
             } else if (tid < 64) {
                 const int j = tid;
                 float lr_ = 0.f, lk = 0.f, tot = 0.f;
-                if (j < nvalid) {
+                float lo_ = 0.f;
+                if (j < nvalid && (j < 32 || !PAIRED)) {
                     const float rec = (s_rec[j] + s_rec[64 + j] + s_rec[128 + j] + s_rec[192 + j]) / (float)D, wj = s_w[j];
-                    lr_ = rec * wj; lk = s_kld[j] * s_wk[j]; tot = lr_ + lk + 0.f;
+                    lr_ = rec * wj; lk = s_kld[j] * s_wk[j];
+                    if (PAIRED) lo_ = fmaxf(s_kld[j] - s_kld[j + 32] + a.margin, 0.f) * s_wk[j + 32];    // lambda w_OoD relu(.)
+                    tot = lr_ + lk + lo_;
                     if (a.per_jet) {
                         const long row0 = row0_of();
                         a.per_jet[row0 + j] = lr_; a.per_jet[a.B + row0 + j] = lk;
-                        a.per_jet[2 * a.B + row0 + j] = 0.f; a.per_jet[3 * a.B + row0 + j] = tot;
+                        a.per_jet[2 * a.B + row0 + j] = lo_; a.per_jet[3 * a.B + row0 + j] = tot;
                     }
                 }
                 if (a.sums) {
-                    const double v0 = warp_sum((double)lr_), v1 = warp_sum((double)lk), v3 = warp_sum((double)tot);
-                    if (lane == 0) { atomicAdd(a.sums, v0); atomicAdd(a.sums + 1, v1); atomicAdd(a.sums + 3, v3); }
+                    const double v0 = warp_sum((double)lr_), v1 = warp_sum((double)lk), v2 = warp_sum((double)lo_), v3 = warp_sum((double)tot);
+                    if (lane == 0) { atomicAdd(a.sums, v0); atomicAdd(a.sums + 1, v1); if (PAIRED) atomicAdd(a.sums + 2, v2); atomicAdd(a.sums + 3, v3); }
                 }
             }
         }

@@ -143,6 +143,8 @@ int Engine::fused_init() {
             CK(cudaFuncSetAttribute(fused2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
             CK(cudaFuncSetAttribute(fused3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
             CK(cudaFuncSetAttribute(fused3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+            CK(cudaFuncSetAttribute(fused3_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+            CK(cudaFuncSetAttribute(fused3_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
             { const char* ev = getenv("OEVAE_FUSED_V"); f->v3 = !(ev && atoi(ev) == 2); }   // 3: warp-specialised kernel (default), 2: fused2
             fz = f;
             return 0;
@@ -517,6 +519,20 @@ int Engine::fused_oe(const float* x_bkg, const float* w_bkg, const float* x_ood,
         CKL();
         f.img_dirty = false;
     }
+    if (cfg.oe_type == OEVAE_OE_KLD) {
+        // paired tiles: the hinge on KLD(bkg) - KLD(OoD) and its derivative are formed inside the kernel -> one launch
+        F2Args b{};
+        b.paired = 1; b.x = x_bkg; b.x2 = x_ood; b.w = w_bkg; b.w2 = w_ood; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = f.parts;
+        b.per_jet = per_jet; b.sums = sums;
+        b.B = B; b.n_tiles = (int)((B + 31) / 32); b.train = want_grad; b.mse = mse_type();
+        b.beta = beta; b.lamb = lamb; b.margin = margin; b.seed = cfg.seed; b.row_offset = row_offset; b.step = 0u;
+        ++calls;
+        const int grid = std::min(b.n_tiles, n_sm);
+        { PROF(want_grad ? "fused_oe_pair_train" : "fused_oe_pair_eval", s); CK(launch_pdl(fused3_kernel<false, 1>, dim3(grid), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b)); }
+        CKL();
+        if (want_grad) { f.last_fused = true; f.last_grid = grid; }
+        return 0;
+    }
     const long Bt = 2 * B;
     if (Bt > f.oe_cap) {
         CK(cudaStreamSynchronize(s));
@@ -534,7 +550,7 @@ int Engine::fused_oe(const float* x_bkg, const float* w_bkg, const float* x_ood,
     ++calls;
     const int grid = std::min(b.n_tiles, n_sm);
     b.w = nullptr; b.per_jet = f.oe_pj; b.train = 0;        // raw rec -> oe_pj[0..2B), raw kld -> oe_pj[2B..4B)
-    { PROF("fused_oe_fwd", s); CK(launch_pdl(fused3_kernel<false>, dim3(grid), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b)); }
+    { PROF("fused_oe_fwd", s); CK(launch_pdl(fused3_kernel<false, 2>, dim3(grid), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b)); }
     CKL();
     CombineArgs ca{};
     ca.rec = f.oe_pj; ca.kld = f.oe_pj + Bt; ca.w = w_bkg; ca.w_ood = w_ood;
@@ -546,7 +562,7 @@ int Engine::fused_oe(const float* x_bkg, const float* w_bkg, const float* x_ood,
     CKL();
     if (!want_grad) return 0;
     b.c_rec = f.oe_c; b.c_kld = f.oe_c + Bt; b.per_jet = nullptr; b.sums = nullptr; b.train = 1;
-    { PROF("fused_oe_train", s); CK(launch_pdl(fused3_kernel<false>, dim3(grid), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b)); }
+    { PROF("fused_oe_train", s); CK(launch_pdl(fused3_kernel<false, 2>, dim3(grid), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b)); }
     CKL();
     f.last_fused = true; f.last_grid = grid;
     return 0;

@@ -1,4 +1,5 @@
 """GPU parity of the FUSED outlier-exposure step (precision bf16x3, bkg + OoD batch; models.py:86-132 / 147-155):
+OE_type 'KLD': one launch on paired tiles (32 bkg jets + their 32 OoD partners per tile); the reconstruction-based types:
 forward pre-pass over [bkg ; OoD] -> combine_kernel -> fused3 training pass with per-jet loss-term coefficients.
 Checked against the float64 oracle with the tolerances tests/test_gpu_tensorcore.py states for bf16x3, and against the
 layered tensor-core path (OEVAE_OE_LAYERED=1) that it replaces."""
@@ -28,8 +29,9 @@ def _data(FC, D, B, seed=11):
     return X, Xo, w, wo, eps
 
 
-def _ran(names):
-    return 'fused_oe_fwd' in names and 'fused_oe_train' in names and not any(n.startswith('gemm') for n in names)
+def _ran(names, oe):
+    want = ('fused_oe_pair_train',) if oe == 'KLD' else ('fused_oe_fwd', 'fused_oe_train')     # KLD: paired tiles, one launch
+    return all(w in names for w in want) and not any(n.startswith('gemm') for n in names)
 
 
 @pytest.mark.parametrize('oe', V.OE_TYPES)
@@ -48,7 +50,7 @@ def test_fused_oe_vs_oracle(FC, D, B, fused, oe):
     torch.cuda.synchronize()
     names = [r[0] for r in _ffi.profile_report()]
     _ffi.profile(False)
-    assert _ran(names) == fused, names
+    assert _ran(names, oe) == fused, names
     out, gref = V.losses_and_grad(flat, FC, D, X, w, Xo, wo, eps, OE_type=oe, beta=0.7, lamb=1.3, margin=0.2)
     ref = np.stack(out)
     _close_losses(pj.cpu().numpy(), ref, T['l_rtol'], T['l_atol'], 'losses %s' % oe)
