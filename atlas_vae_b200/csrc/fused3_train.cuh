@@ -57,6 +57,25 @@ __device__ __forceinline__ void issue2_e(uint32_t d0, uint32_t d1, const f2::Opn
         ah += a_step; al += a_step; bh += b_step; bl += b_step;
     }
 }
+// One element of utils.py:346-375's KLD and JSD sums: kl += nan_to_num(p log2(p/q)), js += (nan_to_num(p log2(p/m)) +
+// nan_to_num(q log2(q/m))) / 2 with m = (p + q) / 2.  With a = p/m, b = q/m (one SFU reciprocal): log2(p/q) = log2 a - log2 b.
+// Operands of different sign give a NaN logarithm -> 0 and p = 0 gives 0 * -inf -> 0, as the quotient form does; q == 0 and
+// an m outside [1e-30, 1e30] (or NaN) keep the quotient form, where the signs of the infinities matter.
+__device__ __forceinline__ void score_kj(float p, float q, float& kl, float& js) {
+    const float m = (p + q) * 0.5f, am = fabsf(m);
+    if (q != 0.f && am > 1e-30f && am < 1e30f) {
+        float rm;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rm) : "f"(m));
+        const float la = __log2f(p * rm), lb = __log2f(q * rm);
+        float t = p * (la - lb), t1 = p * la, t2 = q * lb;
+        t = (t != t) ? 0.f : t; t1 = (t1 != t1) ? 0.f : t1; t2 = (t2 != t2) ? 0.f : t2;
+        kl += fminf(fmaxf(t, -3.402823466e+38f), 3.402823466e+38f);
+        js += (fminf(fmaxf(t1, -3.402823466e+38f), 3.402823466e+38f) + fminf(fmaxf(t2, -3.402823466e+38f), 3.402823466e+38f)) * 0.5f;
+    } else {
+        kl += f2::kld_term_fast(p, q);
+        js += (f2::kld_term_fast(p, m) + f2::kld_term_fast(q, m)) / 2.f;
+    }
+}
 __device__ __forceinline__ void worker_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kF3Workers * 32) : "memory"); }
 // every lane has fenced its own writes / TMEM reads; one arrival per warp
 __device__ __forceinline__ void warp_arrive(uint64_t* bar, int lane) {
@@ -675,13 +694,25 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
 #pragma unroll
                     for (int j = 0; j < 16; ++j) wsc[j] = s_w[jc0 + j] * inv_d;
                 }
+                // column jc0 + j of the tile is a real jet iff j < nj; xcol: x of this thread's first jet at feature frow
+                const int nj = max(0, min(16, nvalid - cidx(jc0)));
+                const float* xcol = ((PAIRED && jc0 >= 32) ? xb : xa) + (long)jc0 * D + frow;
+                const bool want_kj = SCORE && (a.s_kld || a.s_jsd);
                 for (int c = 0; c < P.nC; ++c) {
                     const int f = 128 * c + frow;
                     const bool valid = f < D;
                     // this thread's 16 x values of the chunk (L2-resident since stage 0), issued before the accumulator wait
                     float xv[16];
+                    {
+                        const float* px = xcol + 128 * c;
+                        if (valid && nj == 16) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) xv[j] = (valid && colv(jc0 + j)) ? __ldg(((PAIRED && jc0 >= 32) ? xb : xa) + (jc0 + j) * D + f) : 0.f;
+                            for (int j = 0; j < 16; ++j) xv[j] = __ldg(px + j * D);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) xv[j] = (valid && j < nj) ? __ldg(px + j * D) : 0.f;
+                        }
+                    }
                     const float bias = valid ? __ldg(a.theta + st.seg_b[0] + f) : 0.f;
                     const uint32_t yb = yk & 1;
                     wait_acc(&yfull[yb], (yk >> 1) & 1);
@@ -693,14 +724,29 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     stamp();
                     if constexpr (SCORE) {
                         // loss_function (utils.py:346-375) terms of this thread's feature for its 16 jets; Q = clip_values(X_hat)
+                        // Columns j >= nj accumulate values that are never written.  KLD and JSD share one reciprocal and two
+                        // logarithms per element (score_kj); both are formed when either is asked for.
+                        if (valid) {
+                            if (want_kj) {
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            if (valid && jc0 + j < nvalid) {
-                                const float p = xv[j], qv = clipv(y[j] + bias), d = p - qv;
-                                rec_acc[j] += d * d; sc_mae[j] += fabsf(d);
-                                if (a.s_kld) sc_kl[j] += kld_term_fast(p, qv);
-                                if (a.s_jsd) { const float mm = (p + qv) / 2.f; sc_js[j] += (kld_term_fast(p, mm) + kld_term_fast(qv, mm)) / 2.f; }
-                                if (a.s_xhat) a.s_xhat[(row0_of() + jc0 + j) * D + f] = qv;
+                                for (int j = 0; j < 16; ++j) {
+                                    const float p = xv[j], qv = clipv(y[j] + bias), d = p - qv;
+                                    y[j] = qv;
+                                    rec_acc[j] = fmaf(d, d, rec_acc[j]); sc_mae[j] += fabsf(d);
+                                    score_kj(p, qv, sc_kl[j], sc_js[j]);
+                                }
+                            } else {
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) {
+                                    const float p = xv[j], qv = clipv(y[j] + bias), d = p - qv;
+                                    y[j] = qv;
+                                    rec_acc[j] = fmaf(d, d, rec_acc[j]); sc_mae[j] += fabsf(d);
+                                }
+                            }
+                            if (a.s_xhat) {
+                                float* px = a.s_xhat + (row0_of() + jc0) * D + f;
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) if (j < nj) px[j * D] = y[j];
                             }
                         }
                     } else {

@@ -680,12 +680,24 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
         ++calls;
         b.s_mse = o_mse; b.s_mae = o_mae; b.s_kld = o_kld; b.s_jsd = o_jsd; b.s_lat = o_lat; b.s_fin = o_fin; b.s_xhat = o_xhat;
         const int grid2 = std::min(b.n_tiles, n_sm);
+        static long long* sdbg = nullptr;
+        const bool dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
+        if (dbg && !sdbg) { cudaMalloc(&sdbg, 1024 * sizeof(long long)); cudaMemset(sdbg, 0, 1024 * sizeof(long long)); }
+        b.dbg = dbg ? sdbg : nullptr;
         {
             PROF("fused_score", s);
             if (f.v3) fused3_kernel<true><<<grid2, kF3Threads - kF3Drains * 32, f.plan2.smem_bytes, s>>>(f.plan2, b);   // no drain warps in a forward pass
             else fused2_kernel<true><<<grid2, kF2Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
         }
         CKL();
+        if (dbg) {
+            long long hbuf[1024]; cudaStreamSynchronize(s); cudaMemcpy(hbuf, sdbg, sizeof hbuf, cudaMemcpyDeviceToHost);
+            fprintf(stderr, "[score dbg] grid=%d worker stamps:", grid2);
+            for (int i = 2; i <= (int)hbuf[0]; ++i) fprintf(stderr, " %lld", hbuf[i] - hbuf[1]);
+            fprintf(stderr, "\n[score dbg] issuer stamps:");
+            for (int i = 0; i < (int)hbuf[256]; ++i) fprintf(stderr, " %lld", hbuf[257 + i] - hbuf[1]);
+            fprintf(stderr, "\n");
+        }
         return 0;
     }
     long chunk = std::min<long>(N, std::max<long>(cap_rows, 65536));

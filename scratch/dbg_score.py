@@ -1,0 +1,22 @@
+import sys, os, numpy as np, torch
+sys.path.insert(0, '.')
+from atlas_vae_b200.engine import DeviceVAE
+from atlas_vae_b200.models import init_params
+FC, D = [80, 40, 20, 10], 400
+N = 1_000_000
+X = torch.rand(N, D, device='cuda') * 0.3
+dev = DeviceVAE(FC, D, 'KLD', 'bf16x3', 'fixed', 0, None, 5000); dev.set_params(init_params(FC, D, 0))
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+def t(n, metrics, reps=3):
+    best = 1e9
+    for r in range(reps):
+        e0.record(); dev.score(X[:n], metrics=metrics, want_finite=False); e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    print('N', n, metrics, 'ms', round(best, 4), 'Mjets/s', round(n / best / 1e3, 1), flush=True)
+for n in (148 * 64, 148 * 64 * 2, 148 * 64 * 8, N):
+    t(n, ('MAE', 'KLD', 'JSD', 'Latent'))
+    t(n, ('MAE', 'Latent'))
+    t(n, ('Latent',))
+os.environ['OEVAE_FUSED_DBG'] = '1'
+dev.score(X[:148 * 64 * 4], metrics=('MAE', 'KLD', 'JSD', 'Latent'), want_finite=False)
+dev.score(X[:148 * 64 * 4], metrics=('MAE', 'Latent'), want_finite=False)
