@@ -22,6 +22,9 @@ namespace oevae {
 constexpr int kF3Workers = 16;                               // worker warps
 constexpr int kF3Drains = 4;                                 // drain warps, one per TMEM lane quarter
 constexpr int kF3Threads = (kF3Workers + 2 + kF3Drains) * 32;
+constexpr int kF3XSlotsMax = 4;                              // SCORE: X ring slots (2 in the plan's X region + 2 over the aliased decoder tiles)
+constexpr int kF3Stagers = 2;                                // SCORE: X stager warps (run one tile ahead of the workers)
+constexpr int kF3ScoreThreads = (kF3Workers + 2 + kF3Stagers) * 32;
 constexpr int kF3MaxChunks = 24;                             // 128-feature chunks of the output layer (plan: 2 nX + 4 n + 8 <= 96 ops)
 constexpr uint32_t kF3_TDW = 320;
 
@@ -57,24 +60,32 @@ __device__ __forceinline__ void issue2_e(uint32_t d0, uint32_t d1, const f2::Opn
         ah += a_step; al += a_step; bh += b_step; bl += b_step;
     }
 }
-// One element of utils.py:346-375's KLD and JSD sums: kl += nan_to_num(p log2(p/q)), js += (nan_to_num(p log2(p/m)) +
-// nan_to_num(q log2(q/m))) / 2 with m = (p + q) / 2.  With a = p/m, b = q/m (one SFU reciprocal): log2(p/q) = log2 a - log2 b.
-// Operands of different sign give a NaN logarithm -> 0 and p = 0 gives 0 * -inf -> 0, as the quotient form does; q == 0 and
-// an m outside [1e-30, 1e30] (or NaN) keep the quotient form, where the signs of the infinities matter.
+// One element of utils.py:346-375's KLD and JSD sums for tame operands (see the caller): kl += nan_to_num(p log2(p/q)),
+// js += nan_to_num(p log2(p/m)) + nan_to_num(q log2(q/m)) with m = (p + q) / 2 -- the caller halves the JSD sum once at the end
+// (exact in binary).  With a = p/m, b = q/m (one SFU reciprocal, a + b = 2): log2(p/q) = log2 a - log2 b.  A term whose ratio is
+// not positive is NaN (sign differs) or 0 * -inf (p = 0) in NumPy, which nan_to_num turns into 0: those terms are skipped.
 __device__ __forceinline__ void score_kj(float p, float q, float& kl, float& js) {
-    const float m = (p + q) * 0.5f, am = fabsf(m);
-    if (q != 0.f && am > 1e-30f && am < 1e30f) {
-        float rm;
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rm) : "f"(m));
-        const float la = __log2f(p * rm), lb = __log2f(q * rm);
-        float t = p * (la - lb), t1 = p * la, t2 = q * lb;
-        t = (t != t) ? 0.f : t; t1 = (t1 != t1) ? 0.f : t1; t2 = (t2 != t2) ? 0.f : t2;
-        kl += fminf(fmaxf(t, -3.402823466e+38f), 3.402823466e+38f);
-        js += (fminf(fmaxf(t1, -3.402823466e+38f), 3.402823466e+38f) + fminf(fmaxf(t2, -3.402823466e+38f), 3.402823466e+38f)) * 0.5f;
-    } else {
-        kl += f2::kld_term_fast(p, q);
-        js += (f2::kld_term_fast(p, m) + f2::kld_term_fast(q, m)) / 2.f;
-    }
+    const float m = (p + q) * 0.5f;
+    // one block, so that ptxas keeps the three accumulations as predicated FFMAs (as C++ it turned each element into a branch)
+    asm("{\n\t.reg .pred pa, pb, pc;\n\t.reg .f32 rm, av, bv, la, lb, dl;\n\t"
+        "rcp.approx.ftz.f32 rm, %4;\n\t"
+        "mul.f32 av, %2, rm;\n\t"
+        "mul.f32 bv, %3, rm;\n\t"
+        "lg2.approx.ftz.f32 la, av;\n\t"
+        "lg2.approx.ftz.f32 lb, bv;\n\t"
+        "setp.gt.f32 pa, av, 0f00000000;\n\t"
+        "setp.gt.f32 pb, bv, 0f00000000;\n\t"
+        "and.pred pc, pa, pb;\n\t"
+        "sub.f32 dl, la, lb;\n\t"
+        "@pa fma.rn.f32 %1, %2, la, %1;\n\t"
+        "@pb fma.rn.f32 %1, %3, lb, %1;\n\t"
+        "@pc fma.rn.f32 %0, %2, dl, %0;\n\t}"
+        : "+f"(kl), "+f"(js) : "f"(p), "f"(q), "f"(m));
+}
+__device__ __forceinline__ void score_kj_slow(float p, float q, float& kl, float& js) {
+    const float m = (p + q) * 0.5f;
+    kl += f2::kld_term_fast(p, q);
+    js += f2::kld_term_fast(p, m) + f2::kld_term_fast(q, m);              // halved by the caller
 }
 __device__ __forceinline__ void worker_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kF3Workers * 32) : "memory"); }
 // every lane has fenced its own writes / TMEM reads; one arrival per warp
@@ -87,14 +98,18 @@ __device__ __forceinline__ void warp_arrive(uint64_t* bar, int lane) {
 // MODE 0: one input (training step, get_losses, scoring).  MODE 1: paired tiles (OE_type 'KLD').  MODE 2: two inputs [bkg ; OoD] with
 // per-jet loss-term coefficients (raw pre-pass and training pass of the reconstruction-based OE types).
 template <bool SCORE, int MODE = 0>
-__global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threads, 1) fused3_kernel(const __grid_constant__ F2Plan P, F2Args a) {
+__global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused3_kernel(const __grid_constant__ F2Plan P, F2Args a) {
     using namespace umma;
     using namespace f2;
     using namespace f3;
     constexpr bool PAIRED = MODE == 1, TWOIN = MODE == 2;
+    constexpr bool NOMSE = SCORE && MODE == 3;               // scoring pass without the MSE vector: 16 fewer live accumulators
+    // Second layer-0 accumulator.  SCORE: the X stager warps and the issuer run layer 0 of tile t+1 while the workers are still in the
+    // output epilogues of tile t, so it must not be a y-chunk accumulator; the dW^T columns are free in a forward pass.
+    constexpr uint32_t T_L0B = SCORE ? kF3_TDW : f2::T_Y0;
     const bool is_train = !SCORE && a.train;
     extern __shared__ unsigned char smem_dyn[];
-    __shared__ uint64_t wfull[kF2WSlots], wempty[kF2WSlots], xfull[kF2XSlots], xempty[kF2XSlots];
+    __shared__ uint64_t wfull[kF2WSlots], wempty[kF2WSlots], xfull[kF3XSlotsMax], xempty[kF3XSlotsMax];
     __shared__ uint64_t yfull[2], yempty[2], gyfull[kF3MaxChunks], gyempty, dwfull[2], dwempty[2];
     __shared__ uint64_t acc[kF2MaxStages], tready[kF2MaxStages], accB[kF2MaxStages], gready[kF2MaxStages];
     __shared__ uint32_t tmem_base_s;
@@ -138,9 +153,17 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
         nvalid = max(0, min(kF2Jets, (int)(second ? a.B - a.B1 : a.B1) - local0));
         return (second ? a.x2 : a.x) + (long)local0 * P.D;
     };
-    auto tile_hi = [&](int k) { return sm + P.tile_off[k]; };
-    auto tile_lo = [&](int k) { return sm + P.tile_off[k] + P.tile_rows[k] * 128; };
-    auto xslot = [&](int s) { return sm + P.s_off + s * 16384; };      // hi 8 KB, lo 8 KB
+    // SCORE (forward only): decoder tile k reuses the bytes of encoder tile 2n - k (same rows in the mirrored decoder, and H_{2n-k}
+    // is dead once stage 2n-k+1 has run), and the bytes of tiles n+1..2n hold two more X ring slots when they fit, so the stagers
+    // run up to four chunks ahead of the layer-0 MMAs.
+    const bool alias_ok = SCORE && [&] { for (int k = n + 1; k <= 2 * n; ++k) if (P.tile_rows[k] != P.tile_rows[2 * n - k]) return false; return n >= 1; }();
+    const int xs_log = (alias_ok && P.wring_off - P.tile_off[n + 1] >= 32768) ? 2 : 1;       // log2(X ring slots)
+    const uint32_t xs_mask = (1u << xs_log) - 1u;
+    auto toff = [&](int k) { return P.tile_off[(alias_ok && k > n) ? 2 * n - k : k]; };
+    auto tile_hi = [&](int k) { return sm + toff(k); };
+    auto tile_lo = [&](int k) { return sm + toff(k) + P.tile_rows[k] * 128; };
+    auto xslot_off = [&](int s) { return s < 2 ? P.s_off + s * 16384 : P.tile_off[n + 1] + (s - 2) * 16384; };
+    auto xslot = [&](int s) { return sm + xslot_off(s); };             // hi 8 KB, lo 8 KB
     unsigned char* gy_hi = sm + P.s_off; unsigned char* gy_lo = gy_hi + 16384;
     auto db_at = [&](int buf, int hh, int row) -> float& { return s_db[(buf * 4 + hh) * 128 + row]; };
 
@@ -161,7 +184,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
     if (tid < kF2MaxStages) { mbar_init(&acc[tid], 1); mbar_init(&tready[tid], kF3Workers); mbar_init(&accB[tid], 1); mbar_init(&gready[tid], kF3Workers); }
     else if (tid >= 32 && tid < 32 + kF3MaxChunks) mbar_init(&gyfull[tid - 32], kF3Workers);
     else if (tid >= 64 && tid < 64 + kF2WSlots) { mbar_init(&wfull[tid - 64], 1); mbar_init(&wempty[tid - 64], 1); }
-    else if (tid >= 96 && tid < 96 + kF2XSlots) { mbar_init(&xfull[tid - 96], kF3Workers); mbar_init(&xempty[tid - 96], 1); }
+    else if (tid >= 96 && tid < 96 + kF3XSlotsMax) { mbar_init(&xfull[tid - 96], SCORE ? kF3Stagers : kF3Workers); mbar_init(&xempty[tid - 96], 1); }
     else if (tid >= 128 && tid < 130) { mbar_init(&yfull[tid - 128], 1); mbar_init(&yempty[tid - 128], kF3Workers); mbar_init(&dwfull[tid - 128], 1); mbar_init(&dwempty[tid - 128], kF3Drains); }
     else if (tid == 160) mbar_init(&gyempty, 1);
     mbar_fence_init();
@@ -210,8 +233,8 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
         {
             const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base_s, 0);
             const uint32_t smu = __shfl_sync(0xffffffffu, smem_u32(sm), 0);      // shared-window address of the aligned base
-            auto tile_a = [&](int k) { return smu + (uint32_t)P.tile_off[k]; };
-            auto xslot_a = [&](uint32_t b) { return smu + (uint32_t)P.s_off + b * 16384u; };
+            auto tile_a = [&](int k) { return smu + (uint32_t)toff(k); };
+            auto xslot_a = [&](uint32_t b) { return smu + (uint32_t)xslot_off((int)b); };
             const uint32_t gy_a = smu + (uint32_t)P.s_off;
             long gbase = 0;                                  // ops consumed by earlier tiles
             uint32_t xk = 0, yk = 0, gk = 0, dk = 0;         // cumulative uses of the X ring, y slots, g_y slot, dW^T accumulators
@@ -238,12 +261,13 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     const F2Stage& st = P.st[0];
                     for (int c = 0; c < P.nX; ++c, ++xk) {
                         const uint32_t wb = wget(P.op_first[0] + c);
-                        mbar_wait(&xfull[xk & 1], (xk >> 1) & 1);
+                        const uint32_t xb_ = xk & xs_mask;
+                        mbar_wait(&xfull[xb_], (xk >> xs_log) & 1);
                         tc_fence_after();
                         stamp2();
                         const int nk = min(4, (D - 64 * c + 15) >> 4);
-                        issue2_e(tm + T_CH, tm + T_Y0, opnd_k(wb, st.rows * 128), opnd_k(xslot_a(xk & 1), 8192), nk, kF2Jets, c > 0, c > 0);
-                        commit_e(&xempty[xk & 1]);
+                        issue2_e(tm + T_CH, tm + T_L0B, opnd_k(wb, st.rows * 128), opnd_k(xslot_a(xb_), 8192), nk, kF2Jets, c > 0, c > 0);
+                        commit_e(&xempty[xb_]);
                         wrel(P.op_first[0] + c);
                         stamp2();
                     }
@@ -352,6 +376,65 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
         }
         __syncwarp();
     } else if (warp >= kF3Workers + 2) {
+        if constexpr (SCORE) {
+            // =================================================================================== X stager warps (SCORE)
+            // X chunk c of a tile = [64 jets x features 64c..64c+63] fp32 -> bf16 hi/lo, K-major rows = jets, into the 2-slot X ring.
+            // Nothing here depends on the workers: the ring is freed by the layer-0 MMAs, so the stagers (and the issuer behind them)
+            // run layer 0 of tile t+1 under the output epilogues of tile t.
+            const int st_id = tid - (kF3Workers + 2) * 32;                  // 0 .. 63
+            uint32_t xk = 0;
+            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+                int local0, nvalid;
+                const float* xa = tile_src(tile, local0, nvalid);
+                {   // pull the rows of the tile after this one towards L2
+                    int l0, nv;
+                    const char* nx = reinterpret_cast<const char*>(tile_src(tile + (int)gridDim.x, l0, nv));
+                    const long nbytes = (tile + (int)gridDim.x < a.n_tiles) ? (long)nv * D * 4 : 0;
+                    for (long o = (long)st_id * 128; o < nbytes; o += kF3Stagers * 32 * 128) prefetch_l2(nx + o);
+                }
+                // a chunk is two halves of 8 float4 per thread; the loads of the next half are in flight while this one is converted
+                auto ldh = [&](int hc, float4 (&r)[8]) {                 // hc = 2 * chunk + half
+                    const int c = hc >> 1;
+#pragma unroll
+                    for (int it = 0; it < 8; ++it) {
+                        const int idx = st_id + 64 * (it + 8 * (hc & 1)), rr = idx >> 4, c4 = (idx & 15) << 2, col = 64 * c + c4;
+                        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (c < P.nX && rr < nvalid) {
+                            const float* p = xa + (long)rr * D + col;
+                            if (col + 3 < D && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) t = __ldg(reinterpret_cast<const float4*>(p));
+                            else {
+                                if (col < D) t.x = __ldg(p);
+                                if (col + 1 < D) t.y = __ldg(p + 1);
+                                if (col + 2 < D) t.z = __ldg(p + 2);
+                                if (col + 3 < D) t.w = __ldg(p + 3);
+                            }
+                        }
+                        r[it] = t;
+                    }
+                };
+                auto sth = [&](int hc, const float4 (&r)[8]) {
+                    const uint32_t b = xk & xs_mask, rnd = xk >> xs_log;
+                    if (!(hc & 1) && rnd >= 1) mbar_wait(&xempty[b], (rnd - 1) & 1);
+                    unsigned char* hi = xslot((int)b); unsigned char* lo = hi + 8192;
+#pragma unroll
+                    for (int it = 0; it < 8; ++it) {
+                        const int idx = st_id + 64 * (it + 8 * (hc & 1)), rr = idx >> 4, c4 = (idx & 15) << 2;
+                        uint32_t ha, la, hb, lb;
+                        split2(r[it].x, r[it].y, ha, la); split2(r[it].z, r[it].w, hb, lb);
+                        const uint32_t off = sw128_off(rr, c4);
+                        *reinterpret_cast<uint2*>(hi + off) = make_uint2(ha, hb);
+                        *reinterpret_cast<uint2*>(lo + off) = make_uint2(la, lb);
+                    }
+                    if (hc & 1) { fence_async_smem(); warp_arrive(&xfull[b], lane); ++xk; }
+                };
+                float4 ra[8], rb[8];
+                ldh(0, ra);
+                for (int hc = 0; hc < 2 * P.nX; hc += 2) {
+                    ldh(hc + 1, rb); sth(hc, ra);
+                    ldh(hc + 2, ra); sth(hc + 1, rb);
+                }
+            }
+        }
         // ======================================================================================= drain warps
         // dW^T accumulators (lane = output feature, column = input feature) -> rows of the Keras [in, out] kernel gradients
         // in this CTA's partial-gradient slice; a warp writes 32 consecutive outputs per row (one 128-byte segment per
@@ -593,7 +676,7 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                 tmem_ld16(t_lane + T_CH + jc0, v);
                 if (two) {
                     float u[16];
-                    tmem_ld16(t_lane + T_Y0 + jc0, u);
+                    tmem_ld16(t_lane + T_L0B + jc0, u);
 #pragma unroll
                     for (int j = 0; j < 16; ++j) v[j] += u[j];
                 }
@@ -629,11 +712,13 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
             worker_sync();                                               // s_w / s_eps visible; previous tile's scratch reads done
             // =========================================================== forward, stage 0: X streamed in 64-feature chunks
             {
-                float4 ra[2], rb[2];
-                ldx(0, ra); ldx(1, rb);
-                for (int c = 0; c < P.nX; c += 2) {
-                    stage_x(ra); ldx(c + 2, ra);
-                    if (c + 1 < P.nX) { stage_x(rb); ldx(c + 3, rb); }
+                if constexpr (!SCORE) {                                   // SCORE: the stager warps fill the X ring
+                    float4 ra[2], rb[2];
+                    ldx(0, ra); ldx(1, rb);
+                    for (int c = 0; c < P.nX; c += 2) {
+                        stage_x(ra); ldx(c + 2, ra);
+                        if (c + 1 < P.nX) { stage_x(rb); ldx(c + 3, rb); }
+                    }
                 }
                 const float bias0 = bias_of(0);
                 wait_acc(&acc[0], tp);
@@ -724,23 +809,45 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     stamp();
                     if constexpr (SCORE) {
                         // loss_function (utils.py:346-375) terms of this thread's feature for its 16 jets; Q = clip_values(X_hat)
-                        // Columns j >= nj accumulate values that are never written.  KLD and JSD share one reciprocal and two
-                        // logarithms per element (score_kj); both are formed when either is asked for.
+                        // Columns j >= nj accumulate values that are never written.  Pass 1 forms y + bias and four cheap range
+                        // checks over the thread's 16 elements; when they hold (|y|, |x| < 1e5, |y| and |x + y| > 1e-30 -- anything a
+                        // trained model produces) clip_values is the identity, every logarithm below is finite or belongs to a
+                        // term that nan_to_num zeroes, and pass 2 is ~20 instructions per element.  Otherwise the thread takes the
+                        // exact path (clip_values + the quotient form with its NaN / infinity rules) for this chunk.
                         if (valid) {
-                            if (want_kj) {
+                            float ssx = 0.f, ssp = 0.f, mnx = 3.0e38f, mns = 3.0e38f;
 #pragma unroll
-                                for (int j = 0; j < 16; ++j) {
-                                    const float p = xv[j], qv = clipv(y[j] + bias), d = p - qv;
-                                    y[j] = qv;
-                                    rec_acc[j] = fmaf(d, d, rec_acc[j]); sc_mae[j] += fabsf(d);
-                                    score_kj(p, qv, sc_kl[j], sc_js[j]);
+                            for (int j = 0; j < 16; ++j) {
+                                y[j] += bias;
+                                ssx = fmaf(y[j], y[j], ssx); ssp = fmaf(xv[j], xv[j], ssp);
+                                mnx = fminf(mnx, fabsf(y[j])); mns = fminf(mns, fabsf(xv[j] + y[j]));
+                            }
+                            const bool tame = ssx < 1e10f && ssp < 1e10f;
+                            if (tame && (!want_kj || (mnx > 1e-30f && mns > 4e-30f))) {
+                                if (want_kj) {
+#pragma unroll
+                                    for (int j = 0; j < 16; ++j) {
+                                        const float p = xv[j], qv = y[j], d = p - qv;
+                                        if constexpr (!NOMSE) rec_acc[j] = fmaf(d, d, rec_acc[j]);
+                                        sc_mae[j] += fabsf(d);
+                                        score_kj(p, qv, sc_kl[j], sc_js[j]);
+                                    }
+                                } else {
+#pragma unroll
+                                    for (int j = 0; j < 16; ++j) {
+                                        const float d = xv[j] - y[j];
+                                        if constexpr (!NOMSE) rec_acc[j] = fmaf(d, d, rec_acc[j]);
+                                        sc_mae[j] += fabsf(d);
+                                    }
                                 }
                             } else {
 #pragma unroll
                                 for (int j = 0; j < 16; ++j) {
-                                    const float p = xv[j], qv = clipv(y[j] + bias), d = p - qv;
+                                    const float p = xv[j], qv = clipv(y[j]), d = p - qv;
                                     y[j] = qv;
-                                    rec_acc[j] = fmaf(d, d, rec_acc[j]); sc_mae[j] += fabsf(d);
+                                    if constexpr (!NOMSE) rec_acc[j] = fmaf(d, d, rec_acc[j]);
+                                    sc_mae[j] += fabsf(d);
+                                    if (want_kj) score_kj_slow(p, qv, sc_kl[j], sc_js[j]);
                                 }
                             }
                             if (a.s_xhat) {
@@ -788,8 +895,10 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     }
                     stamp();
                 }
-                const float rs = transpose_reduce16(rec_acc, lane);
-                if (lane < 16) s_rec[q * 64 + jc0 + lane] = rs;
+                if constexpr (!NOMSE) {
+                    const float rs = transpose_reduce16(rec_acc, lane);
+                    if (lane < 16) s_rec[q * 64 + jc0 + lane] = rs;
+                }
                 if constexpr (SCORE) {                                       // s_db is free outside training: [3][4 quarters][64 jets]
                     const float r1 = transpose_reduce16(sc_mae, lane), r2 = transpose_reduce16(sc_kl, lane), r3 = transpose_reduce16(sc_js, lane);
                     if (lane < 16) { s_db[q * 64 + jc0 + lane] = r1; s_db[256 + q * 64 + jc0 + lane] = r2; s_db[512 + q * 64 + jc0 + lane] = r3; }
@@ -863,10 +972,10 @@ __global__ void __launch_bounds__(SCORE ? kF3Threads - kF3Drains * 32 : kF3Threa
                     const int j = tid;
                     auto q4 = [&](const float* b) { return (b[j] + b[64 + j]) + (b[128 + j] + b[192 + j]); };
                     const long row0 = row0_of();
-                    if (a.s_mse) a.s_mse[row0 + j] = q4(s_rec) / (float)D;
+                    if (!NOMSE && a.s_mse) a.s_mse[row0 + j] = q4(s_rec) / (float)D;
                     if (a.s_mae) a.s_mae[row0 + j] = q4(s_db) / (float)D;
                     if (a.s_kld) a.s_kld[row0 + j] = q4(s_db + 256);
-                    if (a.s_jsd) a.s_jsd[row0 + j] = q4(s_db + 512);
+                    if (a.s_jsd) a.s_jsd[row0 + j] = q4(s_db + 512) * 0.5f;
                     if (a.s_lat) a.s_lat[row0 + j] = isfinite(s_kld[j]) ? s_kld[j] : 0.f;       // latent_loss, utils.py:378-386
                     if (a.s_fin) a.s_fin[row0 + j] = 1;                                         // clip_values leaves no non-finite X_hat
                 }

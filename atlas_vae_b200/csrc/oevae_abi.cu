@@ -143,6 +143,7 @@ int Engine::fused_init() {
             CK(cudaFuncSetAttribute(fused2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
             CK(cudaFuncSetAttribute(fused3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
             CK(cudaFuncSetAttribute(fused3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+            CK(cudaFuncSetAttribute(fused3_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
             CK(cudaFuncSetAttribute(fused3_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
             CK(cudaFuncSetAttribute(fused3_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
             { const char* ev = getenv("OEVAE_FUSED_V"); f->v3 = !(ev && atoi(ev) == 2); }   // 3: warp-specialised kernel (default), 2: fused2
@@ -686,7 +687,9 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
         b.dbg = dbg ? sdbg : nullptr;
         {
             PROF("fused_score", s);
-            if (f.v3) fused3_kernel<true><<<grid2, kF3Threads - kF3Drains * 32, f.plan2.smem_bytes, s>>>(f.plan2, b);   // no drain warps in a forward pass
+            // workers + issuer + producer + X stagers; the instantiation without the MSE vector keeps 16 more registers for the rest
+            if (f.v3 && o_mse) fused3_kernel<true><<<grid2, kF3ScoreThreads, f.plan2.smem_bytes, s>>>(f.plan2, b);
+            else if (f.v3) fused3_kernel<true, 3><<<grid2, kF3ScoreThreads, f.plan2.smem_bytes, s>>>(f.plan2, b);
             else fused2_kernel<true><<<grid2, kF2Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
         }
         CKL();
