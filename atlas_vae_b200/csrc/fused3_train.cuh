@@ -309,6 +309,9 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                               opnd_mn(tile_a((2 * n)), P.tile_rows[2 * n] * 128, 8192), st.kin >> 4, kF2Jets, false);
                         commit_e(&yfull[b]);
                         ++yk;
+                        // forward pass: nothing else reads the chunk's weight ops, so they leave the ring with THIS product (released
+                        // after issue_y(c + 1) they waited for the next product and the ring ran one chunk late)
+                        if (!is_train) for (int b2 = 0; b2 < 2 && 2 * c + b2 < P.nX; ++b2) wrel(ob + 2 * c + b2);
                     };
                     issue_y(0);
                     for (int c = 0; c < P.nC; ++c) {
@@ -328,8 +331,6 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                             issue_e(tdw, opnd_k(gy_a, 16384), opnd_k(tile_a((2 * n)), P.tile_rows[2 * n] * 128), 4, st.kin, false);
                             commit_e(&gyempty); ++gk;
                             dw_commit();
-                        } else {
-                            for (int b = 0; b < 2 && 2 * c + b < P.nX; ++b) wrel(ob + 2 * c + b);
                         }
                     }
                     if (is_train) commit_e(&accB[so]);
