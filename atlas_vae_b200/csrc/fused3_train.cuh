@@ -382,7 +382,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
             // X chunk c of a tile = [64 jets x features 64c..64c+63] fp32 -> bf16 hi/lo, K-major rows = jets, into the 2-slot X ring.
             // Nothing here depends on the workers: the ring is freed by the layer-0 MMAs, so the stagers (and the issuer behind them)
             // run layer 0 of tile t+1 under the output epilogues of tile t.
-            const int st_id = tid - (kF3Workers + 2) * 32;                  // 0 .. 63
+            const int st_id = tid - (kF3Workers + 2) * 32;                  // 0 .. 32 kF3Stagers - 1
             uint32_t xk = 0;
             for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
                 int local0, nvalid;
@@ -393,14 +393,15 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                     const long nbytes = (tile + (int)gridDim.x < a.n_tiles) ? (long)nv * D * 4 : 0;
                     for (long o = (long)st_id * 128; o < nbytes; o += kF3Stagers * 32 * 128) prefetch_l2(nx + o);
                 }
-                // a chunk is two halves of 8 float4 per thread; the loads of the next half are in flight while this one is converted
-                auto ldh = [&](int hc, float4 (&r)[8]) {                 // hc = 2 * chunk + half
+                // a chunk is two halves of 512 float4; the loads of the next half are in flight while this one is converted
+                constexpr int kSt = kF3Stagers * 32, kIt = (512 + kSt - 1) / kSt;      // float4 per thread and half
+                auto ldh = [&](int hc, float4 (&r)[kIt]) {               // hc = 2 * chunk + half
                     const int c = hc >> 1;
 #pragma unroll
-                    for (int it = 0; it < 8; ++it) {
-                        const int idx = st_id + 64 * (it + 8 * (hc & 1)), rr = idx >> 4, c4 = (idx & 15) << 2, col = 64 * c + c4;
+                    for (int it = 0; it < kIt; ++it) {
+                        const int ih = st_id + kSt * it, idx = ih + 512 * (hc & 1), rr = idx >> 4, c4 = (idx & 15) << 2, col = 64 * c + c4;
                         float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (c < P.nX && rr < nvalid) {
+                        if (c < P.nX && rr < nvalid && ih < 512) {
                             const float* p = xa + (long)rr * D + col;
                             if (col + 3 < D && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) t = __ldg(reinterpret_cast<const float4*>(p));
                             else {
@@ -413,22 +414,24 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                         r[it] = t;
                     }
                 };
-                auto sth = [&](int hc, const float4 (&r)[8]) {
+                auto sth = [&](int hc, const float4 (&r)[kIt]) {
                     const uint32_t b = xk & xs_mask, rnd = xk >> xs_log;
                     if (!(hc & 1) && rnd >= 1) mbar_wait(&xempty[b], (rnd - 1) & 1);
                     unsigned char* hi = xslot((int)b); unsigned char* lo = hi + 8192;
 #pragma unroll
-                    for (int it = 0; it < 8; ++it) {
-                        const int idx = st_id + 64 * (it + 8 * (hc & 1)), rr = idx >> 4, c4 = (idx & 15) << 2;
-                        uint32_t ha, la, hb, lb;
-                        split2(r[it].x, r[it].y, ha, la); split2(r[it].z, r[it].w, hb, lb);
-                        const uint32_t off = sw128_off(rr, c4);
-                        *reinterpret_cast<uint2*>(hi + off) = make_uint2(ha, hb);
-                        *reinterpret_cast<uint2*>(lo + off) = make_uint2(la, lb);
+                    for (int it = 0; it < kIt; ++it) {
+                        const int ih = st_id + kSt * it, idx = ih + 512 * (hc & 1), rr = idx >> 4, c4 = (idx & 15) << 2;
+                        if (ih < 512) {
+                            uint32_t ha, la, hb, lb;
+                            split2(r[it].x, r[it].y, ha, la); split2(r[it].z, r[it].w, hb, lb);
+                            const uint32_t off = sw128_off(rr, c4);
+                            *reinterpret_cast<uint2*>(hi + off) = make_uint2(ha, hb);
+                            *reinterpret_cast<uint2*>(lo + off) = make_uint2(la, lb);
+                        }
                     }
                     if (hc & 1) { fence_async_smem(); warp_arrive(&xfull[b], lane); ++xk; }
                 };
-                float4 ra[8], rb[8];
+                float4 ra[kIt], rb[kIt];
                 ldh(0, ra);
                 for (int hc = 0; hc < 2 * P.nX; hc += 2) {
                     ldh(hc + 1, rb); sth(hc, ra);

@@ -120,6 +120,57 @@ def test_fused_score_vs_oracle(N):
         _close(out[m], ref2[m], 1e-3, 1e-4 * scale, m)
 
 
+def _close_inf(a, b, rtol, atol, what):
+    """allclose that also wants the same +-inf entries (sums of +-FLT_MAX terms overflow in NumPy's float32 too)."""
+    fa, fb = np.isfinite(a), np.isfinite(b)
+    assert (fa == fb).all(), f'{what}: finite masks differ at {np.nonzero(fa != fb)[0][:5]}'
+    np.testing.assert_array_equal(a[~fa], b[~fb], err_msg=what)
+    if fa.any():
+        _close(a[fa], b[fb], rtol, atol, what)
+
+
+@pytest.mark.parametrize('case', ['zero_output', 'tiny_output', 'clipped_output', 'wild_inputs'])
+def test_fused_score_exact_path(case):
+    """The scoring epilogue has a range-checked fast path (one reciprocal + two logarithms per element) and an exact path
+    (clip_values + the quotient form of utils.py:347-350 with NumPy's NaN -> 0, +-inf -> +-FLT_MAX rules).  These inputs
+    force the exact path -- X_hat exactly 0 (dead output layer), |X_hat| < 1e-30, X_hat beyond the +-1e6 clip, huge and
+    denormal-range inputs -- and must agree with NumPy's float32 result on the device's own X_hat, infinities included."""
+    from atlas_vae_b200.engine import DeviceVAE
+    from oracle import scoring as S
+    rng = np.random.default_rng(17)
+    FC, D, N = [80, 40, 20, 10], 400, 64 * 3 + 21
+    flat = V.init_params(FC, D, 4).copy()
+    X = rng.normal(0, 0.4, (N, D)).astype(np.float32); X[:, 300:] = 0
+    n_out = FC[0] * D + D
+    if case == 'zero_output':
+        flat[-n_out:] = 0
+    elif case == 'tiny_output':
+        flat[-n_out:] = 0; flat[-D:] = rng.choice([1e-35, -1e-35, 3e-33], D).astype(np.float32)
+    elif case == 'clipped_output':
+        flat[-D:] += rng.choice([0, 0, 3e6, -5e7], D).astype(np.float32)
+    else:
+        X[::3, 5] = 2.5e6; X[1::4, 17] = -7e7; X[::5, 40] = 1e-33; X[2::7, 41] = -3e-36
+    eps = rng.normal(size=(1, N, 10)).astype(np.float32)
+    dev = DeviceVAE(FC, D, 'KLD', 'bf16x3', 'external', 0); dev.set_params(flat)
+    out = {k: v.cpu().numpy() for k, v in dev.score(X, 1, eps, metrics=('MSE', 'MAE', 'KLD', 'JSD', 'Latent'), want_xhat=True).items()}
+    slim = {k: v.cpu().numpy() for k, v in dev.score(X, 1, eps, metrics=('MAE', 'KLD', 'JSD')).items()}    # instantiation without MSE
+    for m in ('MAE', 'KLD', 'JSD'):
+        np.testing.assert_array_equal(slim[m], out[m], err_msg=m)
+    xhat = out['xhat']
+    assert np.isfinite(xhat).all() and np.abs(xhat).max() <= 1e6
+    if case == 'zero_output':
+        assert (xhat == 0).all()
+    if case == 'clipped_output':
+        assert (np.abs(xhat) == 1e6).any()
+    ref = S.score_metrics(X, xhat, ('MSE', 'MAE', 'KLD', 'JSD'))
+    for m in ('MSE', 'MAE'):
+        _close_inf(out[m], ref[m], 1e-4, 1e-6, m)
+    for m in ('KLD', 'JSD'):
+        fin = np.isfinite(ref[m])
+        scale = max(np.abs(ref[m][fin]).max(), 1e-6) if fin.any() else 1.0
+        _close_inf(out[m], ref[m], 1e-3, 1e-4 * scale, m)
+
+
 def test_fused2_kernel_still_matches(monkeypatch):
     """The non-specialised fused2 kernel (OEVAE_FUSED_V=2) stays available as a cross-check of fused3."""
     monkeypatch.setenv('OEVAE_FUSED_V', '2')
