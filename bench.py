@@ -30,8 +30,11 @@ D = N_CONST * N_DIMS
 ALG_BYTES_PER_JET = D * 4 + 4                      # X row + weight (1604 B)
 BETA, LR = 1.0, 1e-3
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed ncu --set full capture of the
-# same workload (profiles/r01_ncu_summary.txt: 8,578,560 B read + 4,096 B written; the partial gradients stay in L2)
-NCU_TRAFFIC = {'fused_train': 8578560 + 4096}
+# same workload (profiles/r01_ncu_fused3_train_details.txt: 8,576,768 B read + 1,024 B written; the partial gradients stay in L2)
+NCU_TRAFFIC = {'fused_train': 8576768 + 1024}
+# scoring pass: profiles/r01_ncu_score_fused3_details.txt, fused3_kernel<1,3> over 40,000 jets: 64,520,448 B read + 1,792,768 B
+# written = 1,657.8 B per jet (algorithmic 1,625: X is read from HBM exactly once; the epilogue's second read of x hits L2)
+NCU_SCORE_TRAFFIC_PER_JET = (64520448 + 1792768) / 40000.0
 METRIC, UNIT = 'train jets/s (fwd+bwd+Adam)', 'jets/s'
 WORKLOAD = 'cfg2: OE-VAE train step, n_constituents=100 x 4-vectors (D=400), FC_layers [80,40,20,10], batch 5000, 1M synthetic QCD jets, beta=1, no OoD term'
 
@@ -251,7 +254,8 @@ def run_ours(args):
     scoring = {'metric': 'anomaly-score jets/s (predict + Latent/MAE/KLD/JSD + cut + jet-mass histogram)', 'value': sc_val, 'unit': UNIT,
                'n_jets_per_gpu': n_jets, 'ms_per_pass': sc_ms,
                'roofline': {'bound': 'hbm', 'achieved': n_jets * SC_ALG / (sc_ms * 1e-3) / 1e9, 'peak': peak, 'unit': 'GB/s',
-                            'frac': n_jets * SC_ALG / (sc_ms * 1e-3) / 1e9 / peak, 'alg_bytes_per_jet': SC_ALG},
+                            'frac': n_jets * SC_ALG / (sc_ms * 1e-3) / 1e9 / peak, 'alg_bytes_per_jet': SC_ALG,
+                            'traffic': NCU_SCORE_TRAFFIC_PER_JET * n_jets},
                'kernels': [{'name': r[0], 'launches_per_pass': r[1] / n_sp, 'us_per_launch': 1e3 * r[2] / r[1], 'share': r[2] / stot} for r in srows[:4]]}
     del mass, jzw
 
