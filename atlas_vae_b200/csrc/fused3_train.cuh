@@ -32,9 +32,9 @@ namespace f3 {
 using namespace umma;
 // mma_e / commit_e / arrive_e (umma.cuh): single-thread tcgen05 instructions issued from warp-uniform code
 // D[128 x N] (+)= A * B over nk k-steps, bf16x3 (Ahi*Bhi + Ahi*Blo + Alo*Bhi); see f2::issue_core
-__device__ __forceinline__ void issue_e(uint32_t d, const f2::Opnd& A, const f2::Opnd& B, int nk, int N, bool acc) {
+__device__ __forceinline__ void issue_e(uint32_t d, const f2::Opnd& A, const f2::Opnd& B, int nk, int N, bool acc, int M = 128) {
     uint64_t ah = f2::desc(A, 0, false), al = f2::desc(A, 0, true), bh = f2::desc(B, 0, false), bl = f2::desc(B, 0, true);
-    const uint32_t a_step = A.kstep >> 4, b_step = B.kstep >> 4, idesc = idesc_bf16_major(128, N, A.mn, B.mn);
+    const uint32_t a_step = A.kstep >> 4, b_step = B.kstep >> 4, idesc = idesc_bf16_major(M, N, A.mn, B.mn);
     uint32_t ac = acc ? 1u : 0u;
 #pragma unroll 1
     for (int ks = 0; ks < nk; ++ks) {
@@ -86,6 +86,14 @@ __device__ __forceinline__ void score_kj_slow(float p, float q, float& kl, float
     const float m = (p + q) * 0.5f;
     kl += f2::kld_term_fast(p, q);
     js += f2::kld_term_fast(p, m) + f2::kld_term_fast(q, m);              // halved by the caller
+}
+// TMEM -> registers: 32 lanes x 4 consecutive columns
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float* v) {
+    uint32_t r[4];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v[i] = __uint_as_float(r[i]);
 }
 __device__ __forceinline__ void worker_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kF3Workers * 32) : "memory"); }
 // every lane has fenced its own writes / TMEM reads; one arrival per warp
@@ -285,7 +293,15 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                     const int nk = st.kin >> 4;
                     if (st.kind == 1) issue_e(tm + T_CH, opnd_mn(wb, part_b, part_b), B, nk, kF2Jets, false);
                     else if (st.kind == 2) issue_e(tm + T_CH, opnd_k(wb, part_b), B, nk, kF2Jets, false);
-                    else {                                                   // heads: mean block, log_var block
+                    else if (SCORE && a.heads_t) {
+                        // heads with the JETS on the lanes: D[64 jets x 16] = H_{n-1}^T (A: the activation tile, MN-major, M = jets) x
+                        // W (B: the image block, MN-major, N = out).  An M = 64 accumulator puts jet i on lane (i % 16) + 32 (i / 16),
+                        // so the Sampling epilogue runs on four warps of four different schedulers with the KLD sum thread-local
+                        // (features on the lanes it sits on 10 lanes of ONE quarter: 4.2 k cycles per tile).  A forward pass only:
+                        // the latent backward reads mu / log_var with the latent index on the lanes.
+                        issue_e(tm + T_MU, B, opnd_mn(wb, 2 * part_b, part_b), nk, 16, false, 64);
+                        issue_e(tm + T_LV, B, opnd_mn(wb + part_b, 2 * part_b, part_b), nk, 16, false, 64);
+                    } else {                                                 // heads: mean block, log_var block
                         issue_e(tm + T_MU, opnd_mn(wb, 2 * part_b, part_b), B, nk, kF2Jets, false);
                         issue_e(tm + T_LV, opnd_mn(wb + part_b, 2 * part_b, part_b), B, nk, kF2Jets, false);
                     }
@@ -736,7 +752,50 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                 const F2Stage& st = P.st[s];
                 float b_mu = 0.f, b_lv = 0.f;
                 if (s != n) b_mu = bias_of(s);
-                else if (lane < L) { b_mu = __ldg(a.theta + st.seg_b[0] + lane); b_lv = __ldg(a.theta + st.seg_b[1] + lane); }
+                else if (!SCORE && lane < L) { b_mu = __ldg(a.theta + st.seg_b[0] + lane); b_lv = __ldg(a.theta + st.seg_b[1] + lane); }
+                if (SCORE && a.heads_t && s == n) {                      // the plan has L <= 16
+                    // ---- heads, jets on the lanes (see the issuer): warp (q, h) owns jets 16 q .. 16 q + 15 and latent rows 4 h .. 4 h + 3;
+                    // the four partial KLD sums of a jet meet in the per-jet write at the end of the tile
+                    float bm[4], bl[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int l = 4 * h + i;
+                        bm[i] = l < L ? __ldg(a.theta + st.seg_b[0] + l) : 0.f; bl[i] = l < L ? __ldg(a.theta + st.seg_b[1] + l) : 0.f;
+                    }
+                    wait_acc(&acc[s], tp);
+                    stamp();
+                    float mu[4], lv[4];
+                    tmem_ld4(t_lane + T_MU + 4 * h, mu);
+                    tmem_ld4(t_lane + T_LV + 4 * h, lv);
+                    const int j = 16 * q + (lane & 15);
+                    float ks = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int l = 4 * h + i;
+                        const float m = mu[i] + bm[i], v = lv[i] + bl[i];
+                        const float sg = __expf(v * 0.5f);
+                        const float zz = m + clipv(sg) * s_eps[min(l, L - 1) * 64 + j];
+                        const float kk = 1.f + v - clipv(sg * sg) - m * m;
+                        mu[i] = l < L ? zz : 0.f;
+                        ks += l < L ? kk : 0.f;
+                    }
+                    if (lane < 16) {
+#pragma unroll
+                        for (int i = 0; i < 4; i += 2) {
+                            uint32_t hh, ll;
+                            split2(mu[i], mu[i + 1], hh, ll);
+                            const uint32_t o0 = sw128_off(4 * h + i, j), o1 = sw128_off(4 * h + i + 1, j);
+                            *reinterpret_cast<unsigned short*>(tile_hi(n) + o0) = (unsigned short)(hh & 0xffffu);
+                            *reinterpret_cast<unsigned short*>(tile_hi(n) + o1) = (unsigned short)(hh >> 16);
+                            *reinterpret_cast<unsigned short*>(tile_lo(n) + o0) = (unsigned short)(ll & 0xffffu);
+                            *reinterpret_cast<unsigned short*>(tile_lo(n) + o1) = (unsigned short)(ll >> 16);
+                        }
+                        s_db[1024 + 64 * h + j] = ks;                           // s_db[0, 768) holds the metric partials, the rest is free in a forward pass
+                    }
+                    publish(&tready[s]);
+                    stamp();
+                    continue;
+                }
                 wait_acc(&acc[s], tp);
                 stamp();
                 if (s != n) {
@@ -980,7 +1039,10 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                     if (a.s_mae) a.s_mae[row0 + j] = q4(s_db) / (float)D;
                     if (a.s_kld) a.s_kld[row0 + j] = q4(s_db + 256);
                     if (a.s_jsd) a.s_jsd[row0 + j] = q4(s_db + 512) * 0.5f;
-                    if (a.s_lat) a.s_lat[row0 + j] = isfinite(s_kld[j]) ? s_kld[j] : 0.f;       // latent_loss, utils.py:378-386
+                    if (a.s_lat) {                                                              // latent_loss, utils.py:378-386
+                        const float kl = a.heads_t ? -(q4(s_db + 1024) / (float)L) / 2.f : s_kld[j];
+                        a.s_lat[row0 + j] = isfinite(kl) ? kl : 0.f;
+                    }
                     if (a.s_fin) a.s_fin[row0 + j] = 1;                                         // clip_values leaves no non-finite X_hat
                 }
             } else if (tid < 64) {

@@ -680,6 +680,7 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
         b.step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
         ++calls;
         b.s_mse = o_mse; b.s_mae = o_mae; b.s_kld = o_kld; b.s_jsd = o_jsd; b.s_lat = o_lat; b.s_fin = o_fin; b.s_xhat = o_xhat;
+        { const char* e = getenv("OEVAE_SCORE_HEADS_T"); b.heads_t = e ? atoi(e) : 0; }      // 1: heads with the jets on the lanes (A/B timing: +5% with two metrics, -3% with four)
         const int grid2 = std::min(b.n_tiles, n_sm);
         static long long* sdbg = nullptr;
         const bool dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
