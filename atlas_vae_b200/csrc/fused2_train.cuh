@@ -141,6 +141,7 @@ struct F2Args {
     // SCORE instantiation only (anomaly scoring, vae.py:163-167 + utils.py:346-386): nullable [B] outputs
     float* s_mse; float* s_mae; float* s_kld; float* s_jsd; float* s_lat; unsigned char* s_fin;
     float* s_xhat;                                          // nullable [B, D]: clip_values(X_hat) of the pass (vae.py:165)
+    int* tile_ctr;                                          // fused3 SCORE: zeroed before the launch; tiles beyond the first gridDim.x are handed out from it
     int heads_t;                                            // fused3 SCORE: heads with the jets on the TMEM lanes (M = 64 accumulators)
     // fused3 only -- outlier-exposure step (models.py:86-132): rows [B1, B) of the batch are read from x2 (the OoD sample) and
     // start at a tile boundary (n_tiles = ceil(B1 / 64) + ceil((B - B1) / 64)); the loss-term coefficients come per jet from

@@ -114,13 +114,14 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
     constexpr bool NOMSE = SCORE && MODE == 3;               // scoring pass without the MSE vector: 16 fewer live accumulators
     // Second layer-0 accumulator.  SCORE: the X stager warps and the issuer run layer 0 of tile t+1 while the workers are still in the
     // output epilogues of tile t, so it must not be a y-chunk accumulator; the dW^T columns are free in a forward pass.
-    constexpr uint32_t T_L0B = SCORE ? kF3_TDW : f2::T_Y0;
+    constexpr uint32_t T_L0A = SCORE ? kF3_TDW : f2::T_CH, T_L0B = SCORE ? kF3_TDW + 64 : f2::T_Y0;
     const bool is_train = !SCORE && a.train;
     extern __shared__ unsigned char smem_dyn[];
     __shared__ uint64_t wfull[kF2WSlots], wempty[kF2WSlots], xfull[kF3XSlotsMax], xempty[kF3XSlotsMax];
     __shared__ uint64_t yfull[2], yempty[2], gyfull[kF3MaxChunks], gyempty, dwfull[2], dwempty[2];
     __shared__ uint64_t acc[kF2MaxStages], tready[kF2MaxStages], accB[kF2MaxStages], gready[kF2MaxStages];
     __shared__ uint32_t tmem_base_s;
+    __shared__ int tile_q[8], tile_seq[8];                   // SCORE: dynamic tile queue (iteration i -> slot i & 7), see tile_of
     unsigned char* sm = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler: role branches do not diverge
@@ -195,6 +196,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
     else if (tid >= 96 && tid < 96 + kF3XSlotsMax) { mbar_init(&xfull[tid - 96], SCORE ? kF3Stagers : kF3Workers); mbar_init(&xempty[tid - 96], 1); }
     else if (tid >= 128 && tid < 130) { mbar_init(&yfull[tid - 128], 1); mbar_init(&yempty[tid - 128], kF3Workers); mbar_init(&dwfull[tid - 128], 1); mbar_init(&dwempty[tid - 128], kF3Drains); }
     else if (tid == 160) mbar_init(&gyempty, 1);
+    if (tid >= 192 && tid < 200) tile_seq[tid - 192] = -1;
     mbar_fence_init();
     dbg_c[2] = clock64();
     for (int i = tid * 16; i < P.zero_bytes; i += (int)blockDim.x * 16) *reinterpret_cast<uint4*>(sm + i) = make_uint4(0, 0, 0, 0);
@@ -217,12 +219,161 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
     const int my_tiles = ((int)blockIdx.x < a.n_tiles) ? (a.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
 
     int n_dbg = 0;
-    auto stamp = [&]() { if (a.dbg && blockIdx.x == 0 && tid == 0 && n_dbg < 255) a.dbg[1 + n_dbg++] = clock64(); };
+    bool dbg_on = true;                                      // the workers switch the stamps on from their tile a.dbg[1000] on
+    const int dbg_skip = a.dbg ? (int)a.dbg[1000] : 0;
+    auto stamp = [&]() { if (a.dbg && dbg_on && blockIdx.x == 0 && tid == 0 && n_dbg < 255) a.dbg[1 + n_dbg++] = clock64(); };
     stamp();
     int n_dbg2 = 0;                                          // MMA issuer's own stamps: a.dbg[256] = count, [257..511]
     auto stamp2 = [&]() { if (a.dbg && blockIdx.x == 0 && n_dbg2 < 255) a.dbg[257 + n_dbg2++] = clock64(); };
 
-    if (warp == kF3Workers + 1) {
+    // SCORE tile schedule.  SMs do not run at the same speed (measured: the slowest CTA of a 100-tile pass needs 8 % longer than the
+    // median, single TPCs up to 30 %), so tiles beyond the first are handed out by an atomic counter instead of round-robin.  Lane 0 of
+    // the first stager warp (the role that runs furthest ahead) publishes the tile of iteration i + 2 when it starts iteration i; every
+    // role reads the tile of its iteration from the queue (-1 ends the pass).  No role can be more than 3 iterations behind the stagers
+    // (X ring and the acc[0] phase bound them), so 8 slots need no hand-back.
+    auto tile_pub = [&](int it) {
+        int id = it == 0 ? (int)blockIdx.x : (int)gridDim.x + atomicAdd(a.tile_ctr, 1);
+        if (id >= a.n_tiles) id = -1;
+        tile_q[it & 7] = id;
+        __threadfence_block();
+        *reinterpret_cast<volatile int*>(&tile_seq[it & 7]) = it;
+        return id;
+    };
+    auto tile_of = [&](int it) -> int {
+        if (!SCORE || !a.tile_ctr) { const long t_ = (long)blockIdx.x + (long)it * gridDim.x; return t_ < a.n_tiles ? (int)t_ : -1; }
+        else {
+            while (*reinterpret_cast<volatile int*>(&tile_seq[it & 7]) != it) __nanosleep(32);
+            __threadfence_block();
+            return *reinterpret_cast<volatile int*>(&tile_q[it & 7]);
+        }
+    };
+
+    // SCORE weight-op schedule.  The ring is consumed in order, so the order of the ops IS the issuer's schedule: layer 0 of tile
+    // t+1 is interleaved with the chain of tile t (the issuer is idle while the workers run a chain epilogue, the stagers have
+    // the X chunks ready, and the layer-0 accumulators [320, 448) are nobody else's in a forward pass).  Producer and issuer walk
+    // the same sequence:
+    //   prologue     L0 chunks 0..nX-1 of the CTA's first tile, dummies up to a multiple of the ring
+    //   per tile     for s = 1..2n: chain op s, then sc_cnt(s) L0' chunks (nX spread over the stages, the remainder from the heads
+    //                on: their epilogue is the longest); a dummy if the position is odd (an output chunk reads two adjacent
+    //                slots); the nX output ops; dummies up to a multiple of the ring
+    // L0' = chunk of the NEXT tile of this CTA (a 16-byte dummy after the last tile).
+    const int sc_n2 = 2 * n;
+    auto sc_cnt = [&](int st_) { return P.nX / sc_n2 + (((st_ - n + sc_n2) % sc_n2) < P.nX % sc_n2 ? 1 : 0); };
+
+    if (SCORE && warp == kF3Workers + 1) {
+        // ======================================================================================= weight producer (SCORE schedule)
+        if (lane == 0) {
+            long g = 0;
+            auto put = [&](int k) {                                          // plan op k, or -1 = 16-byte dummy
+                const int slot = (int)(g & (kF2WSlots - 1));
+                if (g >= kF2WSlots) mbar_wait(&wempty[slot], (uint32_t)(((g >> 2) - 1) & 1));
+                const uint32_t bytes = k >= 0 ? P.op_bytes[k] : 16u;
+                mbar_expect_tx(&wfull[slot], bytes);
+                bulk_g2s(sm + P.wring_off + slot * P.wslot_bytes, a.wimg + (k >= 0 ? P.op_off[k] : 0u), bytes, &wfull[slot]);
+                ++g;
+            };
+            for (int c = 0; c < P.nX; ++c) put(P.op_first[0] + c);
+            while (g & (kF2WSlots - 1)) put(-1);
+            for (int it = 0; tile_of(it) >= 0; ++it) {
+                const bool last = tile_of(it + 1) < 0;
+                int c = 0;
+                for (int st_ = 1; st_ <= sc_n2; ++st_) {
+                    put(P.op_first[st_]);
+                    for (int i = sc_cnt(st_); i > 0; --i, ++c) put(last ? -1 : P.op_first[0] + c);
+                }
+                if (g & 1) put(-1);
+                for (int c2 = 0; c2 < P.nX; ++c2) put(P.op_first[so] + c2);
+                while (g & (kF2WSlots - 1)) put(-1);
+            }
+        }
+        __syncwarp();
+    } else if (SCORE && warp == kF3Workers) {
+        // ======================================================================================= MMA issuer (SCORE schedule)
+        // every lane runs this code with identical values (see f3::mma_e)
+        const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base_s, 0);
+        const uint32_t smu = __shfl_sync(0xffffffffu, smem_u32(sm), 0);
+        auto tile_a = [&](int k) { return smu + (uint32_t)toff(k); };
+        auto xslot_a = [&](uint32_t b) { return smu + (uint32_t)xslot_off((int)b); };
+        long wseen = 0;                                                      // ring positions [0, wseen) have landed
+        long wp = 0;                                                         // next ring position to consume
+        auto slot_a = [&](long p_) { return smu + (uint32_t)P.wring_off + (uint32_t)(p_ & (kF2WSlots - 1)) * (uint32_t)P.wslot_bytes; };
+        auto wgetp = [&](long p_) -> uint32_t { for (; wseen <= p_; ++wseen) mbar_wait(&wfull[wseen & (kF2WSlots - 1)], (uint32_t)((wseen >> 2) & 1)); return slot_a(p_); };
+        auto wrelp = [&](long p_) { commit_e(&wempty[p_ & (kF2WSlots - 1)]); };
+        auto wskipp = [&](long p_) { wgetp(p_); arrive_e(&wempty[p_ & (kF2WSlots - 1)]); };
+        uint32_t xk = 0, yk = 0;
+        auto issue_l0 = [&](long p_, int c) {                                // chunk c of a layer 0, weights at ring position p_
+            const F2Stage& st = P.st[0];
+            const uint32_t wb = wgetp(p_);
+            const uint32_t xb_ = xk & xs_mask;
+            mbar_wait(&xfull[xb_], (xk >> xs_log) & 1);
+            tc_fence_after();
+            const int nk = min(4, (D - 64 * c + 15) >> 4);
+            issue2_e(tm + T_L0A, tm + T_L0B, opnd_k(wb, st.rows * 128), opnd_k(xslot_a(xb_), 8192), nk, kF2Jets, c > 0, c > 0);
+            commit_e(&xempty[xb_]);
+            wrelp(p_);
+            ++xk;
+            if (c == P.nX - 1) commit_e(&acc[0]);
+        };
+        {
+            for (int c = 0; c < P.nX; ++c) issue_l0(wp++, c);
+            while (wp & (kF2WSlots - 1)) wskipp(wp++);
+        }
+        for (int tile_iter = 0; tile_of(tile_iter) >= 0; ++tile_iter) {
+            const uint32_t tp = (uint32_t)(tile_iter & 1);
+            const bool has_next = tile_of(tile_iter + 1) >= 0;
+            int c_next = 0;
+            // ---- chain of this tile, layer-0 chunks of the next tile behind the stages
+            for (int s = 1; s <= sc_n2; ++s) {
+                const F2Stage& st = P.st[s];
+                const long p_ = wp++;
+                const uint32_t wb = wgetp(p_);
+                mbar_wait(&tready[s - 1], tp);
+                tc_fence_after();
+                const uint32_t part_b = st.rows * 128;
+                const Opnd B = opnd_mn(tile_a(s - 1), P.tile_rows[s - 1] * 128, 8192);
+                const int nk = st.kin >> 4;
+                if (st.kind == 1) issue_e(tm + T_CH, opnd_mn(wb, part_b, part_b), B, nk, kF2Jets, false);
+                else if (st.kind == 2) issue_e(tm + T_CH, opnd_k(wb, part_b), B, nk, kF2Jets, false);
+                else if (a.heads_t) {
+                    // heads with the JETS on the lanes: D[64 jets x 16] = H_{n-1}^T (A: the activation tile, MN-major, M = jets) x
+                    // W (B: the image block, MN-major, N = out).  An M = 64 accumulator puts jet i on lane (i % 16) + 32 (i / 16),
+                    // so the Sampling epilogue spreads over all 16 worker warps with the KLD sum thread-local (features on the
+                    // lanes it sits on 10 lanes of ONE quarter: 4.2 k cycles per tile).  A forward pass only: the latent backward
+                    // reads mu / log_var with the latent index on the lanes.
+                    issue_e(tm + T_MU, B, opnd_mn(wb, 2 * part_b, part_b), nk, 16, false, 64);
+                    issue_e(tm + T_LV, B, opnd_mn(wb + part_b, 2 * part_b, part_b), nk, 16, false, 64);
+                } else {
+                    issue_e(tm + T_MU, opnd_mn(wb, 2 * part_b, part_b), B, nk, kF2Jets, false);
+                    issue_e(tm + T_LV, opnd_mn(wb + part_b, 2 * part_b, part_b), B, nk, kF2Jets, false);
+                }
+                wrelp(p_);
+                commit_e(&acc[s]);
+                for (int i = sc_cnt(s); i > 0; --i, ++c_next) { if (has_next) issue_l0(wp, c_next); else wskipp(wp); ++wp; }
+            }
+            if (wp & 1) wskipp(wp++);
+            // ---- output layer: 128-feature chunks into two alternating accumulators
+            {
+                const F2Stage& st = P.st[so];
+                const uint32_t part_b = st.rows * 128;
+                mbar_wait(&tready[sc_n2], tp);
+                tc_fence_after();
+                for (int c = 0; c < P.nC; ++c) {
+                    const uint32_t b = yk & 1, r = yk >> 1;
+                    if (r >= 1) { mbar_wait(&yempty[b], (r - 1) & 1); tc_fence_after(); }
+                    const long p0 = wp + 2 * c;
+                    wgetp(wp + min(2 * c + 1, P.nX - 1));
+                    issue_e(tm + T_Y0 + 64 * b, opnd_mn(slot_a(p0), part_b, P.wslot_bytes),
+                            opnd_mn(tile_a(sc_n2), P.tile_rows[sc_n2] * 128, 8192), st.kin >> 4, kF2Jets, false);
+                    commit_e(&yfull[b]);
+                    ++yk;
+                    for (int b2 = 0; b2 < 2 && 2 * c + b2 < P.nX; ++b2) wrelp(p0 + b2);
+                }
+                wp += P.nX;
+            }
+            while (wp & (kF2WSlots - 1)) wskipp(wp++);
+        }
+        __syncwarp();
+    } else if (warp == kF3Workers + 1) {
         // ======================================================================================= weight producer
         if (lane == 0) {
             const long total = (long)my_tiles * nops;
@@ -274,7 +425,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                         tc_fence_after();
                         stamp2();
                         const int nk = min(4, (D - 64 * c + 15) >> 4);
-                        issue2_e(tm + T_CH, tm + T_L0B, opnd_k(wb, st.rows * 128), opnd_k(xslot_a(xb_), 8192), nk, kF2Jets, c > 0, c > 0);
+                        issue2_e(tm + T_L0A, tm + T_L0B, opnd_k(wb, st.rows * 128), opnd_k(xslot_a(xb_), 8192), nk, kF2Jets, c > 0, c > 0);
                         commit_e(&xempty[xb_]);
                         wrel(P.op_first[0] + c);
                         stamp2();
@@ -400,13 +551,18 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
             // run layer 0 of tile t+1 under the output epilogues of tile t.
             const int st_id = tid - (kF3Workers + 2) * 32;                  // 0 .. 32 kF3Stagers - 1
             uint32_t xk = 0;
-            for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+            if (st_id == 0 && a.tile_ctr) { tile_pub(0); tile_pub(1); }
+            for (int it = 0; ; ++it) {
+                const int tile = tile_of(it);
+                if (tile < 0) break;
+                if (st_id == 0 && a.tile_ctr && tile_of(it + 1) >= 0) tile_pub(it + 2);     // the queue ends at its first -1: nobody asks beyond it
                 int local0, nvalid;
                 const float* xa = tile_src(tile, local0, nvalid);
                 {   // pull the rows of the tile after this one towards L2
+                    const int nt = tile_of(it + 1);
                     int l0, nv;
-                    const char* nx = reinterpret_cast<const char*>(tile_src(tile + (int)gridDim.x, l0, nv));
-                    const long nbytes = (tile + (int)gridDim.x < a.n_tiles) ? (long)nv * D * 4 : 0;
+                    const char* nx = reinterpret_cast<const char*>(tile_src(max(nt, 0), l0, nv));
+                    const long nbytes = nt >= 0 ? (long)nv * D * 4 : 0;
                     for (long o = (long)st_id * 128; o < nbytes; o += kF3Stagers * 32 * 128) prefetch_l2(nx + o);
                 }
                 // a chunk is two halves of 512 float4; the loads of the next half are in flight while this one is converted
@@ -589,8 +745,11 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
         // ======================================================================================= workers
         uint32_t xk = 0, yk = 0, gk = 0;
         int tile_iter = 0;
-        for (int tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tile_iter) {
+        for (;; ++tile_iter) {
+            const int tile = tile_of(tile_iter);
+            if (tile < 0) break;
             const uint32_t tp = (uint32_t)(tile_iter & 1);
+            dbg_on = tile_iter >= dbg_skip;
             int local0, nvalid;                                       // local0: row inside its input = the row the noise is drawn for
             const float* xa = tile_src(tile, local0, nvalid);
             // row in the per-jet arrays ([bkg ; OoD], compact); recomputed where it is used instead of living through the tile
@@ -619,7 +778,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                 }
                 s_w[tid] = cr; s_wk[tid] = ck;
             }
-            {   // pull the next tile's rows of X towards L2
+            if constexpr (!SCORE) {   // pull the next tile's rows of X towards L2 (SCORE: the stagers do)
                 int l0, nv;
                 const char* nx = reinterpret_cast<const char*>(tile_src(tile + (int)gridDim.x, l0, nv));
                 const long nbytes = (tile + (int)gridDim.x < a.n_tiles) ? (long)nv * D * 4 : 0;
@@ -689,11 +848,11 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
             auto wait_acc = [&](uint64_t* bar, uint32_t parity) { mbar_wait(bar, parity); tc_fence_after(); };
 
             // chain accumulator -> bias + ReLU -> tile s (pad rows zero)
-            auto epi_act = [&](int s, float bias, bool two) {
+            auto epi_act = [&](int s, float bias, bool two, uint32_t col = T_CH) {
                 const F2Stage& st = P.st[s];
                 if (32 * q >= P.tile_rows[s]) return;
                 float v[16];
-                tmem_ld16(t_lane + T_CH + jc0, v);
+                tmem_ld16(t_lane + col + jc0, v);
                 if (two) {
                     float u[16];
                     tmem_ld16(t_lane + T_L0B + jc0, u);
@@ -743,7 +902,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                 const float bias0 = bias_of(0);
                 wait_acc(&acc[0], tp);
                 stamp();
-                epi_act(0, bias0, D > 16);
+                epi_act(0, bias0, D > 16, T_L0A);
                 publish(&tready[0]);
                 stamp();
             }
@@ -1073,7 +1232,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
         a.dbg[512 + 2 * blockIdx.x] = (long long)dbg_t0; a.dbg[513 + 2 * blockIdx.x] = (long long)t1;
     }
-    if (a.dbg && blockIdx.x == 0 && tid == 0) a.dbg[0] = n_dbg;
+    if (a.dbg && blockIdx.x == 0 && tid == 0) { a.dbg[0] = n_dbg; a.dbg[906] = clock64(); }
     if (a.dbg && blockIdx.x == 0 && warp == kF3Workers && lane == 0) a.dbg[256] = n_dbg2;
     tc_fence_before();
     __syncthreads();

@@ -682,10 +682,15 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
         b.s_mse = o_mse; b.s_mae = o_mae; b.s_kld = o_kld; b.s_jsd = o_jsd; b.s_lat = o_lat; b.s_fin = o_fin; b.s_xhat = o_xhat;
         { const char* e = getenv("OEVAE_SCORE_HEADS_T"); b.heads_t = e ? atoi(e) : 0; }      // 1: heads with the jets on the lanes (A/B timing: +5% with two metrics, -3% with four)
         const int grid2 = std::min(b.n_tiles, n_sm);
+        static int* tile_ctr = nullptr;                                           // dynamic tile counter of the scoring pass
+        if (!tile_ctr) CK(cudaMalloc(&tile_ctr, 256));
+        CK(cudaMemsetAsync(tile_ctr, 0, sizeof(int), s));
+        b.tile_ctr = (getenv("OEVAE_SCORE_STATIC") && atoi(getenv("OEVAE_SCORE_STATIC"))) ? nullptr : tile_ctr;   // 1: round-robin tiles (A/B timing)
         static long long* sdbg = nullptr;
         const bool dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
         if (dbg && !sdbg) { cudaMalloc(&sdbg, 1024 * sizeof(long long)); cudaMemset(sdbg, 0, 1024 * sizeof(long long)); }
         b.dbg = dbg ? sdbg : nullptr;
+        if (dbg) { long long skip = getenv("OEVAE_DBG_SKIP") ? atoll(getenv("OEVAE_DBG_SKIP")) : 0; cudaMemcpy(sdbg + 1000, &skip, sizeof skip, cudaMemcpyHostToDevice); }
         {
             PROF("fused_score", s);
             // workers + issuer + producer + X stagers; the instantiation without the MSE vector keeps 16 more registers for the rest
@@ -698,6 +703,16 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
             long long hbuf[1024]; cudaStreamSynchronize(s); cudaMemcpy(hbuf, sdbg, sizeof hbuf, cudaMemcpyDeviceToHost);
             fprintf(stderr, "[score dbg] grid=%d worker stamps:", grid2);
             for (int i = 2; i <= (int)hbuf[0]; ++i) fprintf(stderr, " %lld", hbuf[i] - hbuf[1]);
+            {
+                std::vector<std::pair<long long, int>> sp;
+                for (int b2 = 0; b2 < grid2 && b2 < 160; ++b2) sp.push_back({hbuf[513 + 2 * b2] - hbuf[512 + 2 * b2], b2});
+                std::sort(sp.begin(), sp.end());
+                fprintf(stderr, "\n[score dbg] CTA spans (ns): min %lld (cta %d) p25 %lld median %lld p75 %lld max %lld (cta %d); slowest:", sp[0].first, sp[0].second,
+                        sp[sp.size() / 4].first, sp[sp.size() / 2].first, sp[3 * sp.size() / 4].first, sp.back().first, sp.back().second);
+                for (size_t i = sp.size() >= 8 ? sp.size() - 8 : 0; i < sp.size(); ++i) fprintf(stderr, " %d:%lld", sp[i].second, sp[i].first);
+                fprintf(stderr, "; cta0 %lld ns = %lld SM cycles (%.0f MHz)", hbuf[513] - hbuf[512], hbuf[906] - hbuf[900],
+                        1e3 * (double)(hbuf[906] - hbuf[900]) / (double)(hbuf[513] - hbuf[512]));
+            }
             fprintf(stderr, "\n[score dbg] issuer stamps:");
             for (int i = 0; i < (int)hbuf[256]; ++i) fprintf(stderr, " %lld", hbuf[257 + i] - hbuf[1]);
             fprintf(stderr, "\n");

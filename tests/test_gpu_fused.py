@@ -171,6 +171,30 @@ def test_fused_score_exact_path(case):
         _close_inf(out[m], ref[m], 1e-3, 1e-4 * scale, m)
 
 
+@pytest.mark.parametrize('env', [{'OEVAE_SCORE_HEADS_T': '1'}, {'OEVAE_SCORE_STATIC': '1'}, {'OEVAE_SCORE_HEADS_T': '1', 'OEVAE_SCORE_STATIC': '1'}])
+def test_fused_score_schedule_variants(monkeypatch, env):
+    """The scoring pass hands tiles out from an atomic counter and keeps the heads with the latent index on the TMEM lanes;
+    the round-robin schedule (OEVAE_SCORE_STATIC=1) and the jets-on-lanes heads (OEVAE_SCORE_HEADS_T=1, M = 64 accumulators)
+    are kept as switches.  Every combination must give the default's scores: bit-equal for the schedule (a tile's arithmetic
+    does not depend on which CTA runs it), and to rounding for the heads (the KLD sum is formed in another order)."""
+    from atlas_vae_b200.engine import DeviceVAE
+    rng = np.random.default_rng(23)
+    FC, D, N = [80, 40, 20, 10], 400, 148 * 64 * 3 + 77
+    X = rng.normal(0, 0.4, (N, D)).astype(np.float32); X[:, 280:] = 0
+    dev = DeviceVAE(FC, D, 'KLD', 'bf16x3', 'fixed', 3); dev.set_params(V.init_params(FC, D, 4))
+    M = ('MSE', 'MAE', 'KLD', 'JSD', 'Latent')
+    ref = {k: v.cpu().numpy() for k, v in dev.score(X, 1, None, metrics=M).items()}
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    out = {k: v.cpu().numpy() for k, v in dev.score(X, 1, None, metrics=M).items()}
+    for m in M:
+        if 'OEVAE_SCORE_HEADS_T' in env:
+            scale = max(np.abs(ref[m]).max(), 1e-6)
+            _close(out[m], ref[m], 1e-3, 1e-4 * scale, m)             # the tolerance the scores are held to against the oracle
+        else:
+            np.testing.assert_array_equal(out[m], ref[m], err_msg=m)
+
+
 def test_fused2_kernel_still_matches(monkeypatch):
     """The non-specialised fused2 kernel (OEVAE_FUSED_V=2) stays available as a cross-check of fused3."""
     monkeypatch.setenv('OEVAE_FUSED_V', '2')
