@@ -9,6 +9,9 @@
 //   warp 17      weight producer (one lane): cp.async.bulk of the pre-swizzled weight ops through a 4-slot ring
 //   warps 18..21 drain warps (one per TMEM lane quarter): dW^T accumulators + bias-gradient parts -> partial-gradient slice.
 //                The slice is 293 KB per tile at cfg-2 and one SM stores ~17 B/clk, so the drains run beside the chain
+// SCORE instantiations (forward only, 640 threads): warps 18..19 are X stagers instead (X chunks of the NEXT tile -> X ring), the
+//   weight ops follow the SCORE schedule (layer 0 of tile t+1 interleaved with the chain of tile t), tiles come from an atomic
+//   counter through a shared-memory queue, decoder tiles alias encoder tiles, layer 0 accumulates in TMEM columns [320, 448).
 // No __syncthreads inside a tile: every hand-off is an mbarrier, so the issuer runs ahead of the epilogues, X staging
 // overlaps the layer-0 MMAs, and the dW^T drains overlap the next stage's MMAs (two dW^T accumulators).
 //
