@@ -120,6 +120,33 @@ def test_fused_score_vs_oracle(N):
         _close(out[m], ref2[m], 1e-3, 1e-4 * scale, m)
 
 
+@pytest.mark.parametrize('FC,D,N', [([80, 40, 10], 80, 64 * 149 + 5), ([33, 7, 5], 23, 1000), ([100, 16], 130, 64 * 300 + 63), ([64, 32, 16], 64, 777),
+                                    ([48, 24, 6], 12, 5000), ([80, 40, 20, 10], 1000, 700)])
+def test_fused_score_shapes(FC, D, N):
+    """Other layouts through the scoring schedule: fewer X chunks than chain stages (nX < 2n), one chunk, D <= 16 (one layer-0
+    accumulator), 16 X chunks, decoder tiles that alias and tile regions too small for the two extra X ring slots; several tiles per
+    CTA so that the tile queue wraps.  Same tolerances as test_fused_score_vs_oracle."""
+    from atlas_vae_b200.engine import DeviceVAE
+    from oracle import scoring as S
+    rng = np.random.default_rng(31)
+    L = FC[-1]
+    flat = V.init_params(FC, D, 6)
+    X = rng.normal(0, 0.4, (N, D)).astype(np.float32); X[:, (3 * D) // 4:] = 0
+    eps = rng.normal(size=(1, N, L)).astype(np.float32)
+    dev = DeviceVAE(FC, D, 'KLD', 'bf16x3', 'external', 0); dev.set_params(flat)
+    out = {k: v.cpu().numpy() for k, v in dev.score(X, 1, eps, metrics=('MSE', 'MAE', 'KLD', 'JSD', 'Latent'), want_xhat=True).items()}
+    n_ref = min(N, 1000)
+    xhat = S.predict(flat, FC, D, X[:n_ref], [eps[0, :n_ref]], np.float64)
+    _close(out['xhat'][:n_ref], xhat, 1e-3, 1e-4, 'xhat')
+    _close(out['Latent'][:n_ref], S.latent_score(flat, FC, D, X[:n_ref], np.float64), 1e-3, 1e-6, 'Latent')
+    ref2 = S.score_metrics(X, out['xhat'], ('MSE', 'MAE', 'KLD', 'JSD'))
+    for m in ('MSE', 'MAE'):
+        _close(out[m], ref2[m], 1e-4, 1e-6, m + ' (device X_hat)')
+    for m in ('KLD', 'JSD'):
+        scale = max(np.abs(ref2[m]).max(), 1e-6)
+        _close(out[m], ref2[m], 1e-3, 1e-4 * scale, m)
+
+
 def _close_inf(a, b, rtol, atol, what):
     """allclose that also wants the same +-inf entries (sums of +-FLT_MAX terms overflow in NumPy's float32 too)."""
     fa, fb = np.isfinite(a), np.isfinite(b)
