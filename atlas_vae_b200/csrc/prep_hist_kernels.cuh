@@ -33,24 +33,48 @@ __global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, 
     const T* src = raw + jet * 4L * n_raw;
     for (int i = lane; i < 4 * n_raw; i += 32) v[i] = to_f32<T>(src[i]);
     __syncwarp();
-    for (int c = lane; c < n_pad; c += 32) {
-        unsigned long long k = 0ull;
-        if (c < n_raw) {
-            float px = v[4 * c + 1], py = v[4 * c + 2];
-            float pt = __fsqrt_rn(__fadd_rn(__fmul_rn(px, px), __fmul_rn(py, py)));
-            k = ((unsigned long long)__float_as_uint(pt) << 32) | (unsigned)(c + 1);
+    // Sort key = (bits of pT) << 32 | (index + 1), descending: argsort(pT)[::-1] of utils.py:564-571 with ties (equal pT) resolved
+    // towards the higher index.  Real jets fill 20-60 of the n_raw slots, the rest is zero padding, and every slot with pT == +0
+    // has the key (0, index + 1): those keys are already ordered among themselves (descending index) and sort below every other
+    // key.  So the slots with pT != 0 are compacted to the front (nv of them), the pT == 0 slots follow in descending index order,
+    // and only the first nvp = 2^ceil(log2 nv) entries go through the bitonic network: the same permutation as the full sort at a
+    // fraction of the passes (nv = 50: 21 passes over 64 keys instead of 36 over 256).
+    auto key_of = [&](int c) -> unsigned long long {
+        const float px = v[4 * c + 1], py = v[4 * c + 2];
+        const float pt = __fsqrt_rn(__fadd_rn(__fmul_rn(px, px), __fmul_rn(py, py)));
+        return ((unsigned long long)__float_as_uint(pt) << 32) | (unsigned)(c + 1);
+    };
+    int nvp = 0;
+    if (!do_sort) {
+        // keep the stored order, e.g. get_4v on already sorted jets
+        for (int c = lane; c < n_pad; c += 32) keys[c] = c < n_raw ? (unsigned long long)(c + 1) : 0ull;
+    } else {
+        const unsigned lt = (1u << lane) - 1u, gt = lane == 31 ? 0u : ~((2u << lane) - 1u);
+        for (int c = n_raw + lane; c < n_pad; c += 32) keys[c] = 0ull;
+        int nv = 0;
+        for (int c0 = 0; c0 < n_raw; c0 += 32) {
+            const int c = c0 + lane;
+            const unsigned long long k = c < n_raw ? key_of(c) : 0ull;
+            const bool nz = (k >> 32) != 0ull;
+            const unsigned m = __ballot_sync(0xffffffffu, nz);
+            if (nz) keys[nv + __popc(m & lt)] = k;
+            nv += __popc(m);
         }
-        keys[c] = k;
+        int zb = nv;
+        for (int c0 = (n_raw - 1) & ~31; c0 >= 0; c0 -= 32) {
+            const int c = c0 + lane;
+            const bool z = c < n_raw && (key_of(c) >> 32) == 0ull;
+            const unsigned m = __ballot_sync(0xffffffffu, z);
+            if (z) keys[zb + __popc(m & gt)] = (unsigned long long)(c + 1);
+            zb += __popc(m);
+        }
+        if (nv > 1) { nvp = 32; while (nvp < nv) nvp <<= 1; }
     }
     __syncwarp();
-    // bitonic sort, descending (do_sort == 0: keep the stored order, e.g. get_4v on already sorted jets)
-    if (!do_sort) {
-        for (int c = lane; c < n_pad; c += 32) keys[c] = c < n_raw ? (unsigned long long)(c + 1) : 0ull;
-        __syncwarp();
-    }
-    for (int k = 2; do_sort && k <= n_pad; k <<= 1) {
+    // bitonic sort of the first nvp keys, descending
+    for (int k = 2; k <= nvp; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = lane; i < n_pad; i += 32) {
+            for (int i = lane; i < nvp; i += 32) {
                 int p = i ^ j;
                 if (p > i) {
                     unsigned long long a = keys[i], b = keys[p];

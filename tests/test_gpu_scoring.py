@@ -135,6 +135,42 @@ def test_preprocess_scalers_and_large():
         np.testing.assert_array_equal(U.apply_scaler(x_ref, 4, scaler)[ok], ref[ok])
 
 
+@pytest.mark.parametrize('n_raw', [200, 50, 32, 7])
+def test_preprocess_partial_sort_cases(n_raw):
+    """K0 compacts the slots with pT != 0, appends the pT == 0 slots in descending index order and sorts only the compacted part.
+    Cases that exercise it against the oracle's argsort(pT)[::-1] (utils.py:564-571), bit-exact: every slot filled, no slot filled,
+    one slot, exact pT ties, pT == 0 slots that still carry E / pz and sit between filled slots, -0.0 momenta, n_raw that is not a
+    multiple of the warp size."""
+    from atlas_vae_b200 import utils as U
+    rng = np.random.default_rng(41 + n_raw)
+    N = 64
+    raw = rng.normal(0, 5, (N, n_raw, 4)).astype(np.float32)
+    raw[1] = 0                                                            # empty jet
+    raw[2, 1:] = 0                                                        # one constituent
+    raw[3, :, 1:3] = raw[3, 0, 1:3]                                       # every pT equal: order by descending index
+    raw[4, ::3, 1:3] = 0                                                  # pT == 0 with E, pz != 0 between filled slots
+    raw[5, ::2, 1] = -0.0; raw[5, ::2, 2] = 0.0
+    for j in range(6, N):                                                 # zero padding of random length, some jets full
+        k = int(rng.integers(0, n_raw + 1)) if j % 4 else n_raw
+        raw[j, k:] = 0
+        if k > 2: raw[j, 1, 1:3] = raw[j, 0, 1:3]                         # one tie per jet
+    raw = raw.reshape(N, 4 * n_raw)
+
+    def sort_ref(r):                                                      # the device's documented tie rule: reverse of a STABLE argsort
+        j = np.float32(r).reshape(len(r), -1, 4)                          # (NumPy's default argsort is not stable; without ties both agree)
+        pt = np.sqrt(j[:, :, 1] ** 2 + j[:, :, 2] ** 2)
+        order = np.argsort(pt, axis=-1, kind='stable')[:, ::-1]
+        return np.take_along_axis(j, order[:, :, None], axis=1).reshape(len(r), -1)
+
+    for n_const in sorted({n_raw, max(1, n_raw // 2), n_raw + 3}):
+        x4 = PP.select_constituents(sort_ref(raw), n_const)
+        pt_ref, m_ref = PP.jet_pt_mass(x4)
+        s = U.preprocess(raw, n_const, 4)
+        np.testing.assert_array_equal(s['constituents'], x4)
+        np.testing.assert_array_equal(s['pt'], pt_ref); np.testing.assert_array_equal(s['m'], m_ref)
+    np.testing.assert_array_equal(U.jets_sorting(raw.astype(np.float16)), sort_ref(raw.astype(np.float16)))
+
+
 def test_hist_and_cuts_bit_exact(golden_dir):
     """K5 vs np.histogram on the reference's get_idx edges; cut masks vs the reference's make_cut selections."""
     from atlas_vae_b200 import cuts as Cc
