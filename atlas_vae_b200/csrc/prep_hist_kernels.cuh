@@ -31,7 +31,25 @@ __global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, 
     long jet = (long)blockIdx.x * warps + wid;
     if (jet >= N) return;
     const T* src = raw + jet * 4L * n_raw;
-    for (int i = lane; i < 4 * n_raw; i += 32) v[i] = to_f32<T>(src[i]);
+    // 16-byte loads when the jet's row is 16-byte aligned (4 n_raw elements: always for fp32 from an aligned base, even n_raw for fp16)
+    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (4 * n_raw * (int)sizeof(T)) % 16 == 0) {
+        constexpr int kPer = 16 / (int)sizeof(T);
+        const int n16 = 4 * n_raw / kPer;
+        const uint4* s16 = reinterpret_cast<const uint4*>(src);
+        for (int i = lane; i < n16; i += 32) {
+            const uint4 q = __ldg(s16 + i);
+            if constexpr (sizeof(T) == 4) {
+                *reinterpret_cast<uint4*>(v + 4 * i) = q;
+            } else {
+                const __half2* h = reinterpret_cast<const __half2*>(&q);
+                const float2 a = __half22float2(h[0]), b = __half22float2(h[1]), c = __half22float2(h[2]), d = __half22float2(h[3]);
+                *reinterpret_cast<float4*>(v + 8 * i) = make_float4(a.x, a.y, b.x, b.y);
+                *reinterpret_cast<float4*>(v + 8 * i + 4) = make_float4(c.x, c.y, d.x, d.y);
+            }
+        }
+    } else {
+        for (int i = lane; i < 4 * n_raw; i += 32) v[i] = to_f32<T>(src[i]);
+    }
     __syncwarp();
     // Sort key = (bits of pT) << 32 | (index + 1), descending: argsort(pT)[::-1] of utils.py:564-571 with ties (equal pT) resolved
     // towards the higher index.  Real jets fill 20-60 of the n_raw slots, the rest is zero padding, and every slot with pT == +0
@@ -72,15 +90,15 @@ __global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, 
     }
     __syncwarp();
     // bitonic sort of the first nvp keys, descending
+    // (one compare-exchange per lane and step: t enumerates the nvp / 2 pairs (i, i | j) of a step, so no lane idles, and the
+    // exchange is two selects instead of a divergent swap)
     for (int k = 2; k <= nvp; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = lane; i < nvp; i += 32) {
-                int p = i ^ j;
-                if (p > i) {
-                    unsigned long long a = keys[i], b = keys[p];
-                    bool desc = (i & k) == 0;
-                    if (desc ? (a < b) : (a > b)) { keys[i] = b; keys[p] = a; }
-                }
+            for (int t = lane; t < (nvp >> 1); t += 32) {
+                const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), p = i | j;
+                const unsigned long long a = keys[i], b = keys[p];
+                const bool sw = ((i & k) == 0) ? (a < b) : (a > b);
+                keys[i] = sw ? b : a; keys[p] = sw ? a : b;
             }
             __syncwarp();
         }
@@ -88,7 +106,9 @@ __global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, 
     const int D = n_dims * n_const, skip = 4 - n_dims;
     float* xo = x_out + jet * (long)D;
     for (int o = lane; o < D; o += 32) {
-        int c = o / n_dims, d = o - c * n_dims + skip;
+        int c, d;
+        if (n_dims == 4) { c = o >> 2; d = o & 3; }                 // (a runtime division costs more than the gather itself)
+        else { c = o / 3; d = o - c * 3 + skip; }
         float val = 0.f;
         if (c < n_raw) {
             unsigned idx = (unsigned)(keys[c] & 0xffffffffull);
@@ -106,7 +126,8 @@ __global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, 
         float s = 0.f;
         if (lane < 4) {
             int nk = min(n_const, n_raw);
-            for (int c = 0; c < nk; ++c) {
+#pragma unroll 8
+            for (int c = 0; c < nk; ++c) {                       // the loads of later terms do not depend on the running sum
                 unsigned idx = (unsigned)(keys[c] & 0xffffffffull);
                 s = __fadd_rn(s, v[4 * (idx - 1) + lane]);
             }
