@@ -944,7 +944,7 @@ int oevae_preprocess(const void* raw, int32_t raw_dtype, int64_t N, int32_t n_ra
     }
     int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
     int n_pad = 32; while (n_pad < n_raw) n_pad <<= 1;
-    size_t per_warp = (size_t)n_pad * 8 + (size_t)n_raw * 16;
+    size_t per_warp = (size_t)n_pad * 8 + (size_t)n_raw * 16 + 16;          // must match preprocess_kernel
     int warps = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)(200 * 1024) / per_warp));
     if (per_warp > 200 * 1024) { g_create_error = "preprocess: n_raw too large"; return OEVAE_EUNSUPPORTED; }
     size_t smem = per_warp * warps;

@@ -25,11 +25,11 @@ __global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, 
     extern __shared__ unsigned char smem_raw[];
     const int warps = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // per warp: n_raw*4 floats + n_pad u64 keys
-    const size_t per_warp = (size_t)n_pad * 8 + (size_t)n_raw * 16;
+    const size_t per_warp = (size_t)n_pad * 8 + (size_t)n_raw * 16 + 16;      // + 16: the warps' regions start on different banks
     unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw + per_warp * wid);
     float* v = reinterpret_cast<float*>(keys + n_pad);
     long jet = (long)blockIdx.x * warps + wid;
-    if (jet >= N) return;
+    if (jet < N) {
     const T* src = raw + jet * 4L * n_raw;
     // 16-byte loads when the jet's row is 16-byte aligned (4 n_raw elements: always for fp32 from an aligned base, even n_raw for fp16)
     if ((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (4 * n_raw * (int)sizeof(T)) % 16 == 0) {
@@ -121,25 +121,36 @@ __global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, 
         }
         xo[o] = val;
     }
+    }                                                            // jet < N
     if (pt_out || m_out) {
-        // sequential sum over the kept constituents, one lane per 4-vector component (np.sum(axis=1) order)
-        float s = 0.f;
-        if (lane < 4) {
-            int nk = min(n_const, n_raw);
-#pragma unroll 8
-            for (int c = 0; c < nk; ++c) {                       // the loads of later terms do not depend on the running sum
-                unsigned idx = (unsigned)(keys[c] & 0xffffffffull);
-                s = __fadd_rn(s, v[4 * (idx - 1) + lane]);
+        // Sequential sum over the kept constituents in np.sum(axis=1) order: one lane per (jet of the block, 4-vector component), so
+        // the block's first warp forms the sums of all its jets at once (a warp per jet kept 28 lanes idle for n_const steps).
+        __syncthreads();
+        if (wid == 0) {
+            const int jl = lane >> 2, comp = lane & 3;
+            const long jj = (long)blockIdx.x * warps + jl;
+            const bool on = jl < warps && jj < N;
+            float s = 0.f;
+            if (on) {
+                const unsigned long long* kj = reinterpret_cast<const unsigned long long*>(smem_raw + per_warp * jl);
+                const float* vj = reinterpret_cast<const float*>(kj + n_pad);
+                const int nk = min(n_const, n_raw);
+#pragma unroll 4
+                for (int c = 0; c < nk; ++c) {
+                    const unsigned idx = (unsigned)(kj[c] & 0xffffffffull);
+                    s = __fadd_rn(s, vj[4 * (idx - 1) + comp]);
+                }
             }
-        }
-        float E = __shfl_sync(0xffffffffu, s, 0), px = __shfl_sync(0xffffffffu, s, 1);
-        float py = __shfl_sync(0xffffffffu, s, 2), pz = __shfl_sync(0xffffffffu, s, 3);
-        if (lane == 0) {
-            float px2 = __fmul_rn(px, px), py2 = __fmul_rn(py, py);
-            if (pt_out) pt_out[jet] = __fsqrt_rn(__fadd_rn(px2, py2));
-            if (m_out) {
-                float m2 = __fsub_rn(__fsub_rn(__fsub_rn(__fmul_rn(E, E), px2), py2), __fmul_rn(pz, pz));
-                m_out[jet] = __fsqrt_rn(fmaxf(0.f, m2));
+            const int l0 = lane & ~3;
+            const float E = __shfl_sync(0xffffffffu, s, l0), px = __shfl_sync(0xffffffffu, s, l0 + 1);
+            const float py = __shfl_sync(0xffffffffu, s, l0 + 2), pz = __shfl_sync(0xffffffffu, s, l0 + 3);
+            if (on && comp == 0) {
+                const float px2 = __fmul_rn(px, px), py2 = __fmul_rn(py, py);
+                if (pt_out) pt_out[jj] = __fsqrt_rn(__fadd_rn(px2, py2));
+                if (m_out) {
+                    const float m2 = __fsub_rn(__fsub_rn(__fsub_rn(__fmul_rn(E, E), px2), py2), __fmul_rn(pz, pz));
+                    m_out[jj] = __fsqrt_rn(fmaxf(0.f, m2));
+                }
             }
         }
     }
