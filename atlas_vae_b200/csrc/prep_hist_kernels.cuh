@@ -18,6 +18,48 @@ template <typename T> __device__ __forceinline__ float to_f32(T v);
 template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
 
+// Bitonic sort (descending) of 32 R keys held R per lane (element e = 32 r + lane) -- the network of the shared-memory loop in
+// preprocess_kernel, unrolled: steps with j >= 32 exchange registers of one lane, steps with j < 32 exchange lanes by shuffle.
+template <int R>
+__device__ __forceinline__ void bitonic_regs_desc(unsigned long long (&x)[R], int lane) {
+#pragma unroll
+    for (int k = 2; k <= 32 * R; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j >= 32) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const int rp = r | (j >> 5);
+                    if (rp != r && rp < R) {
+                        const bool desc = ((r << 5) & k) == 0;
+                        const unsigned long long a = x[r], b = x[rp];
+                        const bool sw = desc ? (a < b) : (a > b);
+                        x[r] = sw ? b : a; x[rp] = sw ? a : b;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, x[r], j);
+                    const bool desc = (((r << 5) | lane) & k) == 0, low = (lane & j) == 0;
+                    const bool keep_max = low == desc;
+                    x[r] = ((x[r] < o) == keep_max) ? o : x[r];          // keys are distinct (the index is part of the key)
+                }
+            }
+        }
+    }
+}
+template <int R>
+__device__ __forceinline__ void bitonic_smem_via_regs(unsigned long long* keys, int lane) {
+    unsigned long long x[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) x[r] = keys[32 * r + lane];
+    bitonic_regs_desc<R>(x, lane);
+#pragma unroll
+    for (int r = 0; r < R; ++r) keys[32 * r + lane] = x[r];
+    __syncwarp();
+}
+
 template <typename T>
 __global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, int n_pad, int n_const, int n_dims,
                                   const double* __restrict__ center, const double* __restrict__ scale, int do_sort,
@@ -70,19 +112,23 @@ __global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, 
         const unsigned lt = (1u << lane) - 1u, gt = lane == 31 ? 0u : ~((2u << lane) - 1u);
         for (int c = n_raw + lane; c < n_pad; c += 32) keys[c] = 0ull;
         int nv = 0;
+        unsigned zmask = 0;                                      // lane b keeps the pT == 0 mask of chunk b (n_raw <= 1024)
         for (int c0 = 0; c0 < n_raw; c0 += 32) {
             const int c = c0 + lane;
             const unsigned long long k = c < n_raw ? key_of(c) : 0ull;
             const bool nz = (k >> 32) != 0ull;
             const unsigned m = __ballot_sync(0xffffffffu, nz);
+            const unsigned mz = __ballot_sync(0xffffffffu, c < n_raw && !nz);
+            if (lane == (c0 >> 5)) zmask = mz;
             if (nz) keys[nv + __popc(m & lt)] = k;
             nv += __popc(m);
         }
         int zb = nv;
         for (int c0 = (n_raw - 1) & ~31; c0 >= 0; c0 -= 32) {
             const int c = c0 + lane;
-            const bool z = c < n_raw && (key_of(c) >> 32) == 0ull;
-            const unsigned m = __ballot_sync(0xffffffffu, z);
+            const unsigned m = n_raw <= 1024 ? __shfl_sync(0xffffffffu, zmask, c0 >> 5)
+                                             : __ballot_sync(0xffffffffu, c < n_raw && (key_of(c) >> 32) == 0ull);
+            const bool z = (m >> lane) & 1u;
             if (z) keys[zb + __popc(m & gt)] = (unsigned long long)(c + 1);
             zb += __popc(m);
         }
@@ -92,6 +138,11 @@ __global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, 
     // bitonic sort of the first nvp keys, descending
     // (one compare-exchange per lane and step: t enumerates the nvp / 2 pairs (i, i | j) of a step, so no lane idles, and the
     // exchange is two selects instead of a divergent swap)
+    // up to 256 keys the network runs in registers (no shared-memory round trips, no warp barriers)
+    if (nvp == 32) { bitonic_smem_via_regs<1>(keys, lane); nvp = 0; }
+    else if (nvp == 64) { bitonic_smem_via_regs<2>(keys, lane); nvp = 0; }
+    else if (nvp == 128) { bitonic_smem_via_regs<4>(keys, lane); nvp = 0; }
+    else if (nvp == 256) { bitonic_smem_via_regs<8>(keys, lane); nvp = 0; }
     for (int k = 2; k <= nvp; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
             for (int t = lane; t < (nvp >> 1); t += 32) {
