@@ -18,32 +18,34 @@ template <typename T> __device__ __forceinline__ float to_f32(T v);
 template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
 
-// Bitonic sort (descending) of 32 R keys held R per lane (element e = 32 r + lane) -- the network of the shared-memory loop in
-// preprocess_kernel, unrolled: steps with j >= 32 exchange registers of one lane, steps with j < 32 exchange lanes by shuffle.
+// Bitonic sort (descending) of 32 R keys held R per lane -- the network of the shared-memory loop in preprocess_kernel, unrolled.
+// Element e = R lane + r (R consecutive keys per lane), so the steps with distance j < R exchange registers of one lane and only
+// the steps with j >= R cross lanes (shuffle by j / R): 15 shuffle steps at every R, against 20 / 25 / 30 with e = 32 r + lane.
 template <int R>
 __device__ __forceinline__ void bitonic_regs_desc(unsigned long long (&x)[R], int lane) {
 #pragma unroll
     for (int k = 2; k <= 32 * R; k <<= 1) {
+        // direction of the element's k-block; for k < R it depends on r only (taken per register below)
+        const bool desc_lane = ((lane * R) & k) == 0;
 #pragma unroll
         for (int j = k >> 1; j > 0; j >>= 1) {
-            if (j >= 32) {
+            if (j < R) {
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    const int rp = r | (j >> 5);
-                    if (rp != r && rp < R) {
-                        const bool desc = ((r << 5) & k) == 0;
+                    const int rp = r | j;
+                    if (rp != r) {
+                        const bool desc = k < R ? ((r & k) == 0) : desc_lane;
                         const unsigned long long a = x[r], b = x[rp];
                         const bool sw = desc ? (a < b) : (a > b);
                         x[r] = sw ? b : a; x[rp] = sw ? a : b;
                     }
                 }
             } else {
+                const bool keep_max = ((lane & (j / R)) == 0) == desc_lane;      // k > j >= R: the direction is the lane's
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, x[r], j);
-                    const bool desc = (((r << 5) | lane) & k) == 0, low = (lane & j) == 0;
-                    const bool keep_max = low == desc;
-                    x[r] = ((x[r] < o) == keep_max) ? o : x[r];          // keys are distinct (the index is part of the key)
+                    const unsigned long long o = __shfl_xor_sync(0xffffffffu, x[r], j / R);
+                    x[r] = ((x[r] < o) == keep_max) ? o : x[r];          // equal keys are the all-zero padding: either is right
                 }
             }
         }
@@ -53,10 +55,10 @@ template <int R>
 __device__ __forceinline__ void bitonic_smem_via_regs(unsigned long long* keys, int lane) {
     unsigned long long x[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) x[r] = keys[32 * r + lane];
+    for (int r = 0; r < R; ++r) x[r] = keys[R * lane + r];
     bitonic_regs_desc<R>(x, lane);
 #pragma unroll
-    for (int r = 0; r < R; ++r) keys[32 * r + lane] = x[r];
+    for (int r = 0; r < R; ++r) keys[R * lane + r] = x[r];
     __syncwarp();
 }
 
