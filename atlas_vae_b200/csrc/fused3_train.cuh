@@ -914,7 +914,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                 const F2Stage& st = P.st[s];
                 float b_mu = 0.f, b_lv = 0.f;
                 if (s != n) b_mu = bias_of(s);
-                else if (!SCORE && lane < L) { b_mu = __ldg(a.theta + st.seg_b[0] + lane); b_lv = __ldg(a.theta + st.seg_b[1] + lane); }
+                else if (!(SCORE && a.heads_t) && lane < L) { b_mu = __ldg(a.theta + st.seg_b[0] + lane); b_lv = __ldg(a.theta + st.seg_b[1] + lane); }
                 if (SCORE && a.heads_t && s == n) {                      // the plan has L <= 16
                     // ---- heads, jets on the lanes (see the issuer): warp (q, h) owns jets 16 q .. 16 q + 15 and latent rows 4 h .. 4 h + 3;
                     // the four partial KLD sums of a jet meet in the per-jet write at the end of the tile

@@ -98,6 +98,7 @@ def test_fused_score_vs_oracle(N):
     rng = np.random.default_rng(5)
     FC, D = [80, 40, 20, 10], 400
     flat = V.init_params(FC, D, 4)
+    flat = (flat + rng.normal(0, 0.03, flat.shape)).astype(np.float32)     # init_params leaves the head / output biases at zero
     X = rng.normal(0, 0.4, (N, D)).astype(np.float32); X[:, 300:] = 0
     eps = rng.normal(size=(1, N, 10)).astype(np.float32)
     dev = DeviceVAE(FC, D, 'KLD', 'bf16x3', 'external', 0); dev.set_params(flat)
@@ -131,6 +132,7 @@ def test_fused_score_shapes(FC, D, N):
     rng = np.random.default_rng(31)
     L = FC[-1]
     flat = V.init_params(FC, D, 6)
+    flat = (flat + rng.normal(0, 0.05, flat.shape)).astype(np.float32)     # init_params leaves the head / output biases at zero
     X = rng.normal(0, 0.4, (N, D)).astype(np.float32); X[:, (3 * D) // 4:] = 0
     eps = rng.normal(size=(1, N, L)).astype(np.float32)
     dev = DeviceVAE(FC, D, 'KLD', 'bf16x3', 'external', 0); dev.set_params(flat)
@@ -208,7 +210,9 @@ def test_fused_score_schedule_variants(monkeypatch, env):
     rng = np.random.default_rng(23)
     FC, D, N = [80, 40, 20, 10], 400, 148 * 64 * 3 + 77
     X = rng.normal(0, 0.4, (N, D)).astype(np.float32); X[:, 280:] = 0
-    dev = DeviceVAE(FC, D, 'KLD', 'bf16x3', 'fixed', 3); dev.set_params(V.init_params(FC, D, 4))
+    flat = V.init_params(FC, D, 4)
+    flat = (flat + rng.normal(0, 0.05, flat.shape)).astype(np.float32)     # non-zero biases in every layer
+    dev = DeviceVAE(FC, D, 'KLD', 'bf16x3', 'fixed', 3); dev.set_params(flat)
     M = ('MSE', 'MAE', 'KLD', 'JSD', 'Latent')
     ref = {k: v.cpu().numpy() for k, v in dev.score(X, 1, None, metrics=M).items()}
     for k, v in env.items():
