@@ -30,11 +30,11 @@ D = N_CONST * N_DIMS
 ALG_BYTES_PER_JET = D * 4 + 4                      # X row + weight (1604 B)
 BETA, LR = 1.0, 1e-3
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed ncu --set full capture of the
-# same workload (profiles/r01_ncu_fused3_train_details.txt: 8,577,536 B read + 4,608 B written; the partial gradients stay in L2)
-NCU_TRAFFIC = {'fused_train': 8577536 + 4608}
-# scoring pass: profiles/r01_ncu_score_fused3_details.txt, fused3_kernel<1,3> over 40,000 jets: 64,552,704 B read + 1,244,416 B
-# written = 1,644.9 B per jet (algorithmic 1,625: X is read from HBM exactly once; the epilogue's second read of x hits L2)
-NCU_SCORE_TRAFFIC_PER_JET = (64552704 + 1244416) / 40000.0
+# same workload (profiles/r01_ncu_fused3_train_details.txt: 8,577,792 B read + 1,024 B written; the partial gradients stay in L2)
+NCU_TRAFFIC = {'fused_train': 8577792 + 1024}
+# scoring pass: profiles/r01_ncu_score_fused3_details.txt, fused3_kernel<1,3> over 40,000 jets: 64,572,160 B read + 1,385,728 B
+# written = 1,648.9 B per jet (algorithmic 1,625: X is read from HBM exactly once; the epilogue's second read of x hits L2)
+NCU_SCORE_TRAFFIC_PER_JET = (64572160 + 1385728) / 40000.0
 METRIC, UNIT = 'train jets/s (fwd+bwd+Adam)', 'jets/s'
 WORKLOAD = 'cfg2: OE-VAE train step, n_constituents=100 x 4-vectors (D=400), FC_layers [80,40,20,10], batch 5000, 1M synthetic QCD jets, beta=1, no OoD term'
 
