@@ -150,6 +150,22 @@ def test_fused_score_shapes(FC, D, N):
         _close(out[m], ref2[m], 1e-3, 1e-4 * scale, m)
 
 
+def test_fused_score_after_training():
+    """Scoring with the parameters two Adam steps leave behind (every bias non-zero, weight image refreshed by the update kernel):
+    MAE / Latent against the oracle evaluated on the DEVICE's parameters, rel 1e-3 -- the sequence __graft_entry__.smoke() runs."""
+    from oracle import scoring as S
+    FC, D, B = [80, 40, 10], 80, 512
+    X, w, eps = _data(FC, D, B, 7)
+    dev = _dev(FC, D); dev.set_params(V.init_params(FC, D, 0))
+    for _ in range(2):
+        dev.train_step(X, w, None, None, eps, 1e-3, 1.0, 0.0, 0.0)
+    th = dev.get_params()
+    out = {k: v.cpu().numpy() for k, v in dev.score(X, 1, eps, metrics=('MAE', 'Latent')).items()}
+    xhat = S.predict(th, FC, D, X, [eps], np.float64)
+    _close(out['MAE'], np.mean(np.abs(X - xhat), 1), 1e-3, 1e-6, 'MAE')
+    _close(out['Latent'], S.latent_score(th, FC, D, X, np.float64), 1e-3, 1e-6, 'Latent')
+
+
 def _close_inf(a, b, rtol, atol, what):
     """allclose that also wants the same +-inf entries (sums of +-FLT_MAX terms overflow in NumPy's float32 too)."""
     fa, fb = np.isfinite(a), np.isfinite(b)
