@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
     __shared__ uint64_t yfull[2], yempty[2], gyfull[kF3MaxChunks], gyempty, dwfull[2], dwempty[2];
     __shared__ uint64_t acc[kF2MaxStages], tready[kF2MaxStages], accB[kF2MaxStages], gready[kF2MaxStages];
     __shared__ uint32_t tmem_base_s;
-    __shared__ int tile_q[8], tile_seq[8];                   // SCORE: dynamic tile queue (iteration i -> slot i & 7), see tile_of
+    __shared__ int tile_q[16], tile_seq[16];                 // SCORE: dynamic tile queue (iteration i -> slot i & 15), see tile_of
     unsigned char* sm = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~(uintptr_t)1023);
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform for the compiler: role branches do not diverge
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
     else if (tid >= 96 && tid < 96 + kF3XSlotsMax) { mbar_init(&xfull[tid - 96], SCORE ? kF3Stagers : kF3Workers); mbar_init(&xempty[tid - 96], 1); }
     else if (tid >= 128 && tid < 130) { mbar_init(&yfull[tid - 128], 1); mbar_init(&yempty[tid - 128], kF3Workers); mbar_init(&dwfull[tid - 128], 1); mbar_init(&dwempty[tid - 128], kF3Drains); }
     else if (tid == 160) mbar_init(&gyempty, 1);
-    if (tid >= 192 && tid < 200) tile_seq[tid - 192] = -1;
+    if (tid >= 192 && tid < 208) tile_seq[tid - 192] = -1;
     mbar_fence_init();
     dbg_c[2] = clock64();
     for (int i = tid * 16; i < P.zero_bytes; i += (int)blockDim.x * 16) *reinterpret_cast<uint4*>(sm + i) = make_uint4(0, 0, 0, 0);
@@ -232,22 +232,22 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
     // SCORE tile schedule.  SMs do not run at the same speed (measured: the slowest CTA of a 100-tile pass needs 8 % longer than the
     // median, single TPCs up to 30 %), so tiles beyond the first are handed out by an atomic counter instead of round-robin.  Lane 0 of
     // the first stager warp (the role that runs furthest ahead) publishes the tile of iteration i + 2 when it starts iteration i; every
-    // role reads the tile of its iteration from the queue (-1 ends the pass).  No role can be more than 3 iterations behind the stagers
-    // (X ring and the acc[0] phase bound them), so 8 slots need no hand-back.
+    // role reads the tile of its iteration from the queue (-1 ends the pass).  No role can be more than 5 iterations behind the stagers
+    // (the X ring holds at most 4 tiles -- one-chunk inputs -- and the acc[0] phase bounds the issuer), so 16 slots need no hand-back.
     auto tile_pub = [&](int it) {
         int id = it == 0 ? (int)blockIdx.x : (int)gridDim.x + atomicAdd(a.tile_ctr, 1);
         if (id >= a.n_tiles) id = -1;
-        tile_q[it & 7] = id;
+        tile_q[it & 15] = id;
         __threadfence_block();
-        *reinterpret_cast<volatile int*>(&tile_seq[it & 7]) = it;
+        *reinterpret_cast<volatile int*>(&tile_seq[it & 15]) = it;
         return id;
     };
     auto tile_of = [&](int it) -> int {
         if (!SCORE || !a.tile_ctr) { const long t_ = (long)blockIdx.x + (long)it * gridDim.x; return t_ < a.n_tiles ? (int)t_ : -1; }
         else {
-            while (*reinterpret_cast<volatile int*>(&tile_seq[it & 7]) != it) __nanosleep(32);
+            while (*reinterpret_cast<volatile int*>(&tile_seq[it & 15]) != it) __nanosleep(32);
             __threadfence_block();
-            return *reinterpret_cast<volatile int*>(&tile_q[it & 7]);
+            return *reinterpret_cast<volatile int*>(&tile_q[it & 15]);
         }
     };
 

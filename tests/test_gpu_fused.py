@@ -121,7 +121,7 @@ def test_fused_score_vs_oracle(N):
         _close(out[m], ref2[m], 1e-3, 1e-4 * scale, m)
 
 
-@pytest.mark.parametrize('FC,D,N', [([80, 40, 10], 80, 64 * 149 + 5), ([33, 7, 5], 23, 1000), ([100, 16], 130, 64 * 300 + 63), ([64, 32, 16], 64, 777),
+@pytest.mark.parametrize('FC,D,N', [([80, 40, 10], 80, 64 * 149 + 5), ([33, 7, 5], 23, 1000), ([100, 16], 130, 64 * 300 + 63), ([64, 32, 16], 64, 777), ([64, 32, 16], 64, 148 * 64 * 12 + 5),
                                     ([48, 24, 6], 12, 5000), ([80, 40, 20, 10], 1000, 700)])
 def test_fused_score_shapes(FC, D, N):
     """Other layouts through the scoring schedule: fewer X chunks than chain stages (nX < 2n), one chunk, D <= 16 (one layer-0
