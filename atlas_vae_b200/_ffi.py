@@ -10,7 +10,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'liboevae.so')
 
 OE_TYPES = {'KLD': 0, 'MSE': 1, 'MAE': 2, 'MSE-margin': 3, 'MAE-margin': 4}
-PRECISIONS = {'fp32': 0, 'bf16x3': 1, 'tf32': 2, 'bf16': 3}
+PRECISIONS = {'fp32': 0, 'bf16x3': 1, 'bf16': 3}
 NOISE_MODES = {'fixed': 0, 'per_step': 1, 'external': 2}
 
 
@@ -27,7 +27,7 @@ class Config(C.Structure):
 _lib = None
 _vp, _i32, _i64, _f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 
-# name -> (restype, argtypes); mirrors include/oevae.h one to one
+# name -> (restype, argtypes); mirrors include/oevae.h one to one (TEST_SIGNATURES: include/oevae_test.h)
 SIGNATURES = {
     'oevae_create': (C.c_int, [C.POINTER(Config), C.POINTER(_vp)]),
     'oevae_destroy': (C.c_int, [_vp]),
@@ -40,6 +40,7 @@ SIGNATURES = {
     'oevae_set_opt_state_host': (C.c_int, [_vp, _vp, _vp, _i64, _i64]),
     'oevae_get_opt_state_host': (C.c_int, [_vp, _vp, _vp, _i64, C.POINTER(_i64)]),
     'oevae_params_device': (_vp, [_vp]),
+    'oevae_reset_opt_state': (C.c_int, [_vp]),
     'oevae_set_noise_offset': (C.c_int, [_vp, C.c_uint64]),
     'oevae_set_oe_type': (C.c_int, [_vp, _i32]),
     'oevae_train_step': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _f32, _f32, _f32, _f32, _vp, _vp, _vp]),
@@ -47,26 +48,30 @@ SIGNATURES = {
     'oevae_apply_update': (C.c_int, [_vp, _vp, _f32, _vp]),
     'oevae_dp_export': (C.c_int, [_vp, _vp]),
     'oevae_dp_connect': (C.c_int, [_vp, _i32, _i32, _vp]),
+    'oevae_dp_last_grad_host': (C.c_int, [_vp, _vp, _i64]),
     'oevae_train_step_dp': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _f32, _f32, _f32, _f32, _vp, _vp, _vp]),
     'oevae_eval_losses': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _f32, _f32, _f32, _vp, _vp, _vp]),
     'oevae_encode': (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp, _vp]),
     'oevae_score': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     'oevae_preprocess': (C.c_int, [_vp, _i32, _i64, _i32, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp]),
     'oevae_affine': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _vp]),
+    'oevae_ingest_f16': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _vp]),
     'oevae_pair_metrics': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp]),
     'oevae_minmax': (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp]),
     'oevae_loss_map': (C.c_int, [_vp, _i64, _i32, _i32, _vp]),
     'oevae_hist': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _i32, _vp, _vp, _i32, _vp]),
-    'oevae_gemm': (C.c_int, [_vp, _i32, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp]),
-    'oevae_probe_mn': (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _i32, _vp]),
-    'oevae_probe_latency': (C.c_int, [_i32, _i32, C.POINTER(_i64), _i32]),
-    'oevae_probe_issue': (C.c_int, [_i32, _i32, _i32, _i32, _i32, C.POINTER(_i64), _i32]),
-    'oevae_probe_bulk': (C.c_int, [_i32, _i32, _i32, _i32, C.POINTER(_i64), _i32]),
     'oevae_host_register': (C.c_int, [_vp, _i64]),
     'oevae_host_unregister': (C.c_int, [_vp]),
     'oevae_launch_count': (_i64, []),
     'oevae_profile_enable': (C.c_int, [_i32]),
     'oevae_profile_report': (C.c_int, [C.c_char_p, _i32]),
+}
+TEST_SIGNATURES = {
+    'oevae_gemm': (C.c_int, [_vp, _i32, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp]),
+    'oevae_probe_mn': (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _i32, _vp]),
+    'oevae_probe_latency': (C.c_int, [_i32, _i32, C.POINTER(_i64), _i32]),
+    'oevae_probe_issue': (C.c_int, [_i32, _i32, _i32, _i32, _i32, C.POINTER(_i64), _i32]),
+    'oevae_probe_bulk': (C.c_int, [_i32, _i32, _i32, _i32, C.POINTER(_i64), _i32]),
 }
 
 
@@ -77,7 +82,7 @@ def lib():
         if not os.path.isfile(LIB_PATH):
             raise OevaeError('%s not found: run ./build.sh (there is no CPU fallback for the OE-VAE hot path)' % LIB_PATH)
         L = C.CDLL(LIB_PATH)
-        for name, (res, args) in SIGNATURES.items():
+        for name, (res, args) in list(SIGNATURES.items()) + list(TEST_SIGNATURES.items()):
             fn = getattr(L, name)            # AttributeError if the library does not export a declared symbol
             fn.restype, fn.argtypes = res, args
         _lib = L

@@ -29,6 +29,7 @@ struct DpArgs {
     float* theta; float* m; float* v; long n;
     float alpha, b1, b2, eps;
     unsigned char* wimg; const int* pos;
+    float* gsum_out;                         // nullable [n]: SUM over ranks before clip_values (parity checks)
 };
 
 __global__ void __launch_bounds__(kDpCols * kDpSlices, 4) dp_adam_kernel(DpArgs a) {
@@ -91,6 +92,7 @@ __global__ void __launch_bounds__(kDpCols * kDpSlices, 4) dp_adam_kernel(DpArgs 
     float gs = 0.f;
 #pragma unroll
     for (int q = 0; q < kDpMaxWorld; ++q) if (q < a.world) gs += (q == a.rank) ? g : tq[q];
+    if (a.gsum_out) a.gsum_out[i] = gs;
     gs = clipv(gs);
     float m = m0, v = v0;
     m += (gs - m) * (1.f - a.b1);

@@ -25,8 +25,21 @@ struct Pass {
     bool encoder_only = false;
 };
 
+// Tuning / debugging switches, read from the environment ONCE when the handle is created (never on the launch path):
+//   OEVAE_FUSED=0          layered path even where the fused kernel applies      OEVAE_FUSED_V=2       fused2 (cross-check) instead of fused3
+//   OEVAE_OE_LAYERED=1     outlier-exposure step on the layered path             OEVAE_SCORE_LAYERED=1 scoring on the layered path
+//   OEVAE_SCORE_STATIC=1   round-robin tiles in the scoring pass                 OEVAE_SCORE_HEADS_T=1 scoring heads with the jets on the lanes
+//   OEVAE_FUSED_DBG=1      phase stamps of CTA 0 to stderr (synchronises)        OEVAE_DBG_SKIP=k      stamps from the k-th tile of CTA 0 on
+struct Knobs {
+    bool fused = true, oe_layered = false, score_layered = false, score_static = false, fused_dbg = false;
+    int fused_v = 3, score_heads_t = 0;
+    long long dbg_skip = 0;
+    void read_env();
+};
+
 struct Engine {
     oevae_config cfg{};
+    Knobs knobs;
     std::string err;
     int D = 0, L = 0, n = 0, maxH = 0, n_sm = 0;
     std::vector<int> hid;
@@ -49,6 +62,7 @@ struct Engine {
     // data-parallel exchange over NVLink peer memory (dp_kernels.cuh): [2][Ppad] reduced gradients + [8][dp_nblk] flags
     float* dp_buf = nullptr; void* dp_peer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     int dp_rank = -1, dp_world = 0, dp_nblk = 0; unsigned int dp_seq = 0;
+    float* dp_gsum = nullptr;     // [P] SUM over ranks of the last step's gradient, before clip_values (parity checks: oevae_dp_last_grad_host)
 
     ~Engine();
     int fail(int code, const char* fmt, ...);
@@ -69,6 +83,8 @@ struct Engine {
     int losses(const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood, const float* eps, int n_eps,
                long B, float beta, float lamb, float margin, float* per_jet, double* sums, bool want_grad, cudaStream_t s);
     int fused_init();
+    int refresh_images(cudaStream_t s);
+    long long* dbg_buffer();
     int fused_losses(const float* x, const float* w, const float* eps, long B, float beta, float* per_jet, double* sums,
                      bool want_grad, cudaStream_t s);
     int fused_oe(const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood, const float* eps, long B,
@@ -76,7 +92,8 @@ struct Engine {
     int reduce_and_update(float* grad_out, const float* grad_in, bool apply, float lr, cudaStream_t s);
     int dp_export(void* handle_out64);
     int dp_connect(int rank, int world, const void* handles);
-    int dp_update(float lr, cudaStream_t s);
+    int dp_update(float lr, bool have_grad, cudaStream_t s);
+    int reset_opt();
     int score(const float* x, long N, int n_iter, const float* eps, float* o_mse, float* o_mae, float* o_kld, float* o_jsd,
               float* o_lat, unsigned char* o_fin, float* o_xhat, cudaStream_t s);
     int encode(const float* x, long N, const float* eps, float* o_mu, float* o_lv, float* o_z, cudaStream_t s);

@@ -1,5 +1,5 @@
 // liboevae.so: C ABI (include/oevae.h) over the sm_100a kernels.  Host orchestration only; no torch types.
-#include "../../include/oevae.h"
+#include "../../include/oevae_test.h"
 #include "common.cuh"
 #include "ref_kernels.cuh"
 #include "prep_hist_kernels.cuh"
@@ -7,7 +7,7 @@
 #include "umma_probe.cuh"
 #include "engine.h"
 #include "prof.h"
-#include "fused_host.cuh"
+#include "adam_kernels.cuh"
 #include "fused2_train.cuh"
 #include "fused3_train.cuh"
 #include "dp_kernels.cuh"
@@ -51,13 +51,25 @@ int Engine::cuda_check(cudaError_t e, const char* what) {
 #define CKL() do { LAUNCHED(); int _r = cuda_check(cudaGetLastError(), "kernel launch"); if (_r) return _r; } while (0)
 #define TRY(call) do { int _r = (call); if (_r) return _r; } while (0)
 
+void Knobs::read_env() {
+    auto geti = [](const char* k, long long dflt) { const char* e = getenv(k); return e ? atoll(e) : dflt; };
+    fused = geti("OEVAE_FUSED", 1) != 0;
+    fused_v = (int)geti("OEVAE_FUSED_V", 3);
+    oe_layered = geti("OEVAE_OE_LAYERED", 0) != 0;
+    score_layered = geti("OEVAE_SCORE_LAYERED", 0) != 0;
+    score_static = geti("OEVAE_SCORE_STATIC", 0) != 0;
+    score_heads_t = (int)geti("OEVAE_SCORE_HEADS_T", 0);
+    fused_dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
+    dbg_skip = geti("OEVAE_DBG_SKIP", 0);
+}
+
 int Engine::init(const oevae_config& c) {
     cfg = c;
+    knobs.read_env();
     if (c.input_dim <= 0 || c.latent_dim <= 0 || c.n_hidden < 0 || c.n_hidden > 8) return fail(OEVAE_EINVAL, "bad layer configuration");
     if (c.oe_type < 0 || c.oe_type > 4) return fail(OEVAE_EINVAL, "bad oe_type %d", c.oe_type);
     if (c.noise_mode < 0 || c.noise_mode > 2) return fail(OEVAE_EINVAL, "bad noise_mode %d", c.noise_mode);
-    if (c.precision < 0 || c.precision > 3) return fail(OEVAE_EINVAL, "bad precision %d", c.precision);
-    if (c.precision == OEVAE_PREC_TF32) return fail(OEVAE_EUNSUPPORTED, "precision tf32 is not implemented yet (use fp32, bf16x3 or bf16)");
+    if (c.precision != OEVAE_PREC_FP32 && c.precision != OEVAE_PREC_BF16X3 && c.precision != OEVAE_PREC_BF16) return fail(OEVAE_EINVAL, "bad precision %d", c.precision);
     D = c.input_dim; L = c.latent_dim; n = c.n_hidden;
     for (int k = 0; k < n; ++k) { if (c.hidden[k] <= 0) return fail(OEVAE_EINVAL, "bad hidden width"); hid.push_back(c.hidden[k]); }
     // Keras trainable_weights order (models.py:22-28,43-48)
@@ -88,14 +100,15 @@ int Engine::init(const oevae_config& c) {
 
 namespace oevae {
 struct FusedState {
-    FPlan plan{};
-    F2Plan plan2{};                                         // feature-major kernel (default); plan = jet-major v1 (OEVAE_FUSED=1)
-    bool v2 = false, v3 = true;                             // v3: warp-specialised fused3_kernel on the same plan (OEVAE_FUSED_V=2 selects fused2)
+    F2Plan plan2{};                                         // feature-major fused kernels (fused2_train.cuh / fused3_train.cuh)
+    bool v3 = true;                                         // warp-specialised fused3_kernel (OEVAE_FUSED_V=2 selects fused2, the cross-check)
     unsigned char* wimg = nullptr; int* pos = nullptr; float* parts = nullptr;
     uint32_t img_bytes = 0;
     bool img_dirty = true, last_fused = false;
     int last_grid = 0;
     float* oe_pj = nullptr; float* oe_c = nullptr; long oe_cap = 0;   // fused outlier-exposure step: raw [4][2B] losses, [2][2B] coefficients
+    int* tile_ctr = nullptr;                                // dynamic tile counter of this handle's scoring passes (on cfg.device)
+    long long* dbg_buf = nullptr;                           // phase stamps (OEVAE_FUSED_DBG), allocated on demand
 };
 }
 
@@ -104,7 +117,12 @@ Engine::~Engine() {
     if (dp_buf) cudaFree(dp_buf);
     if (theta) cudaFree(theta);
     if (arena) cudaFree(arena);
-    if (fz) { if (fz->wimg) cudaFree(fz->wimg); if (fz->pos) cudaFree(fz->pos); if (fz->parts) cudaFree(fz->parts); if (fz->oe_pj) cudaFree(fz->oe_pj); if (fz->oe_c) cudaFree(fz->oe_c); delete fz; }
+    if (dp_gsum) cudaFree(dp_gsum);
+    if (fz) {
+        if (fz->wimg) cudaFree(fz->wimg); if (fz->pos) cudaFree(fz->pos); if (fz->parts) cudaFree(fz->parts); if (fz->oe_pj) cudaFree(fz->oe_pj);
+        if (fz->oe_c) cudaFree(fz->oe_c); if (fz->tile_ctr) cudaFree(fz->tile_ctr); if (fz->dbg_buf) cudaFree(fz->dbg_buf);
+        delete fz;
+    }
 }
 
 // launch with the programmatic-stream-serialization attribute (PDL): the kernel may start while its predecessor in the
@@ -121,128 +139,96 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
 }
 
-// fused kernel set-up: only for bf16x3 and nets that fit one CTA (see build_fused_plan); otherwise layered path
+// fused kernel set-up: only for bf16x3 and nets that fit one CTA (see build_fused2_plan); otherwise layered path
 int Engine::fused_init() {
-    if (cfg.precision != OEVAE_PREC_BF16X3) return 0;
-    const char* env = getenv("OEVAE_FUSED");
-    if (env && atoi(env) == 0) return 0;
-    const char* ert = getenv("OEVAE_FUSED_RT");
+    if (cfg.precision != OEVAE_PREC_BF16X3 || !knobs.fused) return 0;
     FusedState* f = new FusedState();
     std::vector<int> pos;
-    bool ok = false;
-    if (!(env && atoi(env) == 1)) {
-        uint32_t img_bytes = 0;
-        if (build_fused2_plan(*this, f->plan2, pos, img_bytes)) {
-            f->v2 = true; f->img_bytes = img_bytes;
-            CK(cudaMalloc(&f->wimg, f->img_bytes));
-            CK(cudaMemset(f->wimg, 0, f->img_bytes));
-            CK(cudaMalloc(&f->pos, pos.size() * sizeof(int)));
-            CK(cudaMemcpy(f->pos, pos.data(), pos.size() * sizeof(int), cudaMemcpyHostToDevice));
-            CK(cudaMalloc(&f->parts, ((size_t)n_sm * Ppad + 64) * sizeof(float)));
-            CK(cudaFuncSetAttribute(fused2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
-            CK(cudaFuncSetAttribute(fused2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
-            CK(cudaFuncSetAttribute(fused3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
-            CK(cudaFuncSetAttribute(fused3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
-            CK(cudaFuncSetAttribute(fused3_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
-            CK(cudaFuncSetAttribute(fused3_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
-            CK(cudaFuncSetAttribute(fused3_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
-            { const char* ev = getenv("OEVAE_FUSED_V"); f->v3 = !(ev && atoi(ev) == 2); }   // 3: warp-specialised kernel (default), 2: fused2
-            fz = f;
-            return 0;
-        }
-    }
-    const int cand[4] = {64, 48, 32, 16};
-    for (int i = 0; i < 4 && !ok; ++i) {
-        if (ert && atoi(ert) != cand[i]) continue;
-        ok = build_fused_plan(*this, cand[i], f->plan, pos);
-    }
-    if (!ok) { delete f; return 0; }
-    const FPlan& P_ = f->plan;
-    f->img_bytes = P_.wop_off[P_.n_wop - 1] + P_.wop_bytes[P_.n_wop - 1];
+    uint32_t img_bytes = 0;
+    if (!build_fused2_plan(*this, f->plan2, pos, img_bytes)) { delete f; return 0; }
+    fz = f;                                                 // owned by the handle from here on (freed by ~Engine on a failed init too)
+    f->img_bytes = img_bytes;
     CK(cudaMalloc(&f->wimg, f->img_bytes));
     CK(cudaMemset(f->wimg, 0, f->img_bytes));
     CK(cudaMalloc(&f->pos, pos.size() * sizeof(int)));
     CK(cudaMemcpy(f->pos, pos.data(), pos.size() * sizeof(int), cudaMemcpyHostToDevice));
-    CK(cudaMalloc(&f->parts, (size_t)n_sm * Ppad * sizeof(float)));
-    CK(cudaFuncSetAttribute(fused_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, P_.smem_bytes));
-    fz = f;
+    CK(cudaMalloc(&f->parts, ((size_t)n_sm * Ppad + 64) * sizeof(float)));
+    CK(cudaMalloc(&f->tile_ctr, 256));
+    CK(cudaFuncSetAttribute(fused2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+    CK(cudaFuncSetAttribute(fused2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+    CK(cudaFuncSetAttribute(fused3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+    CK(cudaFuncSetAttribute(fused3_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+    CK(cudaFuncSetAttribute(fused3_kernel<true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+    CK(cudaFuncSetAttribute(fused3_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+    CK(cudaFuncSetAttribute(fused3_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
+    f->v3 = knobs.fused_v != 2;
     return 0;
+}
+
+// weights were set from the host: rebuild the bf16 images
+int Engine::refresh_images(cudaStream_t s) {
+    FusedState& f = *fz;
+    if (!f.img_dirty) return 0;
+    AdamImgArgs ai{};
+    ai.theta = theta; ai.n = P; ai.wimg = f.wimg; ai.pos = f.pos;
+    { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, kAdamCols), kAdamCols * kAdamSlices, 0, s>>>(ai); }
+    CKL();
+    f.img_dirty = false;
+    return 0;
+}
+
+long long* Engine::dbg_buffer() {
+    if (!knobs.fused_dbg) return nullptr;
+    FusedState& f = *fz;
+    if (!f.dbg_buf) { cudaMalloc(&f.dbg_buf, 1024 * sizeof(long long)); cudaMemset(f.dbg_buf, 0, 1024 * sizeof(long long)); }
+    return f.dbg_buf;
 }
 
 int Engine::fused_losses(const float* x, const float* w, const float* eps, long B, float beta, float* per_jet, double* sums,
                          bool want_grad, cudaStream_t s) {
     FusedState& f = *fz;
-    const FPlan& P_ = f.plan;
-    if (f.img_dirty) {                                      // weights were set from the host: rebuild the bf16 images
-        AdamImgArgs ai{};
-        ai.theta = theta; ai.n = P; ai.wimg = f.wimg; ai.pos = f.pos;
-        { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, kAdamCols), kAdamCols * kAdamSlices, 0, s>>>(ai); }
-        CKL();
-        f.img_dirty = false;
-    }
-    static long long* dbg_buf = nullptr;
-    const bool dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
-    if (dbg && !dbg_buf) { cudaMalloc(&dbg_buf, 1024 * sizeof(long long)); cudaMemset(dbg_buf, 0, 1024 * sizeof(long long)); }
-    if (f.v2) {
-        F2Args b{};
-        b.x = x; b.w = w; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = f.parts + (getenv("OEVAE_PART_SHIFT") ? atoi(getenv("OEVAE_PART_SHIFT")) : 0);
-        b.per_jet = per_jet; b.sums = sums;
-        b.B = B; b.n_tiles = (int)((B + kF2Jets - 1) / kF2Jets); b.train = want_grad; b.mse = mse_type();
-        b.beta = beta; b.seed = cfg.seed; b.row_offset = row_offset;
-        b.step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
-        ++calls;
-        b.dbg = dbg ? dbg_buf : nullptr;
-        const int grid2 = std::min(b.n_tiles, n_sm);
-        {
-            PROF(want_grad ? "fused_train" : "fused_eval", s);
-            if (f.v3) CK(launch_pdl(fused3_kernel<false>, dim3(grid2), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b));
-            else fused2_kernel<false><<<grid2, kF2Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
-        }
-        CKL();
-        if (want_grad) { f.last_fused = true; f.last_grid = grid2; }
-        if (dbg) {
-            long long hbuf[1024]; cudaStreamSynchronize(s); cudaMemcpy(hbuf, dbg_buf, sizeof hbuf, cudaMemcpyDeviceToHost);
-            fprintf(stderr, "[fused%d dbg] grid=%d stamps(cycles since start):", f.v3 ? 3 : 2, grid2);
-            for (int i = 2; i <= (int)hbuf[0]; ++i) fprintf(stderr, " %lld", hbuf[i] - hbuf[1]);
-            fprintf(stderr, "\n");
-            if (f.v3) {
-                long long t0min = 1ll << 62, t1max = 0, dmax = 0, dmin = 1ll << 62; int imax = 0;
-                for (int b2 = 0; b2 < grid2 && b2 < 160; ++b2) {
-                    const long long t0 = hbuf[512 + 2 * b2], t1 = hbuf[513 + 2 * b2];
-                    t0min = std::min(t0min, t0); t1max = std::max(t1max, t1);
-                    if (t1 - t0 > dmax) { dmax = t1 - t0; imax = b2; }
-                    dmin = std::min(dmin, t1 - t0);
-                }
-                fprintf(stderr, "[fused3 dbg] set-up cycles (tid 0): prefetch %lld, barrier init %lld, zero %lld, tmem alloc %lld, sync %lld; first stamp at +%lld\n",
-                        hbuf[901] - hbuf[900], hbuf[902] - hbuf[901], hbuf[903] - hbuf[902], hbuf[904] - hbuf[903], hbuf[905] - hbuf[904], hbuf[1] - hbuf[900]);
-                fprintf(stderr, "[fused3 dbg] CTA spans (ns): first entry -> last exit %lld, per-CTA min %lld max %lld (cta %d), cta0 %lld, entry skew %lld\n",
-                        t1max - t0min, dmin, dmax, imax, hbuf[513] - hbuf[512], hbuf[512 + 2 * (grid2 - 1)] - t0min);
-            }
-            if (f.v3 && hbuf[256] > 0) {
-                fprintf(stderr, "[fused3 dbg] issuer stamps:");
-                for (int i = 0; i < (int)hbuf[256]; ++i) fprintf(stderr, " %lld", hbuf[257 + i] - hbuf[1]);
-                fprintf(stderr, "\n");
-            }
-        }
-        return 0;
-    }
-    FusedArgs a{};
-    a.x = x; a.w = w; a.eps = eps; a.wimg = f.wimg; a.parts = f.parts;
-    a.per_jet = per_jet; a.sums = sums; a.kld_out = nullptr;
-    a.B = B; a.n_tiles = (int)((B + P_.Rt - 1) / P_.Rt); a.train = want_grad; a.mse = mse_type();
-    a.beta = beta; a.seed = cfg.seed; a.row_offset = row_offset;
-    a.step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
+    TRY(refresh_images(s));
+    long long* dbg_buf = dbg_buffer();
+    const bool dbg = dbg_buf != nullptr;
+    F2Args b{};
+    b.x = x; b.w = w; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = f.parts;
+    b.per_jet = per_jet; b.sums = sums;
+    b.B = B; b.n_tiles = (int)((B + kF2Jets - 1) / kF2Jets); b.train = want_grad; b.mse = mse_type();
+    b.beta = beta; b.seed = cfg.seed; b.row_offset = row_offset;
+    b.step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
     ++calls;
-    const int grid = std::min(a.n_tiles, n_sm);
-    a.dbg = dbg ? dbg_buf : nullptr;
-    { PROF(want_grad ? "fused_train" : "fused_eval", s); fused_train_kernel<<<grid, 256, P_.smem_bytes, s>>>(P_, a); }
+    b.dbg = dbg_buf;
+    const int grid2 = std::min(b.n_tiles, n_sm);
+    {
+        PROF(want_grad ? "fused_train" : "fused_eval", s);
+        if (f.v3) CK(launch_pdl(fused3_kernel<false>, dim3(grid2), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b));
+        else fused2_kernel<false><<<grid2, kF2Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
+    }
     CKL();
-    if (want_grad) { f.last_fused = true; f.last_grid = grid; }
+    if (want_grad) { f.last_fused = true; f.last_grid = grid2; }
     if (dbg) {
-        long long h[256]; cudaStreamSynchronize(s); cudaMemcpy(h, dbg_buf, sizeof h, cudaMemcpyDeviceToHost);
-        fprintf(stderr, "[fused dbg] grid=%d Rt=%d stamps(cycles since start):", grid, P_.Rt);
-        for (int i = 2; i <= (int)h[0]; ++i) fprintf(stderr, " %lld", h[i] - h[1]);
+        long long hbuf[1024]; cudaStreamSynchronize(s); cudaMemcpy(hbuf, dbg_buf, sizeof hbuf, cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[fused%d dbg] grid=%d stamps(cycles since start):", f.v3 ? 3 : 2, grid2);
+        for (int i = 2; i <= (int)hbuf[0]; ++i) fprintf(stderr, " %lld", hbuf[i] - hbuf[1]);
         fprintf(stderr, "\n");
+        if (f.v3) {
+            long long t0min = 1ll << 62, t1max = 0, dmax = 0, dmin = 1ll << 62; int imax = 0;
+            for (int b2 = 0; b2 < grid2 && b2 < 160; ++b2) {
+                const long long t0 = hbuf[512 + 2 * b2], t1 = hbuf[513 + 2 * b2];
+                t0min = std::min(t0min, t0); t1max = std::max(t1max, t1);
+                if (t1 - t0 > dmax) { dmax = t1 - t0; imax = b2; }
+                dmin = std::min(dmin, t1 - t0);
+            }
+            fprintf(stderr, "[fused3 dbg] set-up cycles (tid 0): prefetch %lld, barrier init %lld, zero %lld, tmem alloc %lld, sync %lld; first stamp at +%lld\n",
+                    hbuf[901] - hbuf[900], hbuf[902] - hbuf[901], hbuf[903] - hbuf[902], hbuf[904] - hbuf[903], hbuf[905] - hbuf[904], hbuf[1] - hbuf[900]);
+            fprintf(stderr, "[fused3 dbg] CTA spans (ns): first entry -> last exit %lld, per-CTA min %lld max %lld (cta %d), cta0 %lld, entry skew %lld\n",
+                    t1max - t0min, dmin, dmax, imax, hbuf[513] - hbuf[512], hbuf[512 + 2 * (grid2 - 1)] - t0min);
+        }
+        if (f.v3 && hbuf[256] > 0) {
+            fprintf(stderr, "[fused3 dbg] issuer stamps:");
+            for (int i = 0; i < (int)hbuf[256]; ++i) fprintf(stderr, " %lld", hbuf[257 + i] - hbuf[1]);
+            fprintf(stderr, "\n");
+        }
     }
     return 0;
 }
@@ -483,7 +469,7 @@ int Engine::losses(const float* x_bkg, const float* w_bkg, const float* x_ood, c
         return fused_losses(x_bkg, w_bkg, eps, B, beta, per_jet, sums, want_grad, s);
     }
     const bool same_eps = cfg.noise_mode == OEVAE_NOISE_FIXED || (cfg.noise_mode == OEVAE_NOISE_EXTERNAL && n_eps == 1);
-    if (fz && fz->v2 && fz->v3 && x_ood && B > 0 && x_bkg && same_eps && !getenv("OEVAE_OE_LAYERED")) {
+    if (fz && fz->v3 && x_ood && B > 0 && x_bkg && same_eps && !knobs.oe_layered) {
         if (cfg.noise_mode == OEVAE_NOISE_EXTERNAL) {
             if (!eps) return fail(OEVAE_EINVAL, "noise_mode EXTERNAL needs eps");
         } else if (eps) return fail(OEVAE_EINVAL, "eps given but noise_mode is not EXTERNAL");
@@ -513,13 +499,7 @@ int Engine::losses(const float* x_bkg, const float* w_bkg, const float* x_ood, c
 int Engine::fused_oe(const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood, const float* eps, long B,
                      float beta, float lamb, float margin, float* per_jet, double* sums, bool want_grad, cudaStream_t s) {
     FusedState& f = *fz;
-    if (f.img_dirty) {
-        AdamImgArgs ai{};
-        ai.theta = theta; ai.n = P; ai.wimg = f.wimg; ai.pos = f.pos;
-        { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, kAdamCols), kAdamCols * kAdamSlices, 0, s>>>(ai); }
-        CKL();
-        f.img_dirty = false;
-    }
+    TRY(refresh_images(s));
     if (cfg.oe_type == OEVAE_OE_KLD) {
         // paired tiles: the hinge on KLD(bkg) - KLD(OoD) and its derivative are formed inside the kernel -> one launch
         F2Args b{};
@@ -583,7 +563,7 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
     if (fz) {                                               // same update + refresh of the bf16 weight images
         AdamImgArgs ai{};
         if (grad_in) ai.grad_in = grad_in;
-        else if (fz->last_fused) { ai.parts = fz->parts + (getenv("OEVAE_PART_SHIFT") ? atoi(getenv("OEVAE_PART_SHIFT")) : 0); ai.n_parts = fz->last_grid; ai.part_stride = Ppad; ai.grad_out = grad_out; }
+        else if (fz->last_fused) { ai.parts = fz->parts; ai.n_parts = fz->last_grid; ai.part_stride = Ppad; ai.grad_out = grad_out; }
         else { ai.parts = parts; ai.n_parts = n_slots_used; ai.part_stride = Ppad; ai.grad_out = grad_out; }
         ai.theta = theta; ai.m = m; ai.v = v; ai.n = P;
         ai.alpha = a.alpha; ai.b1 = a.b1; ai.b2 = a.b2; ai.eps = a.eps; ai.apply = apply;
@@ -625,16 +605,20 @@ int Engine::dp_connect(int rank, int world, const void* handles) {
         if (q == rank) { dp_peer[q] = dp_buf; continue; }
         CK(cudaIpcOpenMemHandle(&dp_peer[q], hs[q], cudaIpcMemLazyEnablePeerAccess));
     }
+    if (!dp_gsum) CK(cudaMalloc(&dp_gsum, Ppad * sizeof(float)));
     dp_rank = rank; dp_world = world; dp_seq = 0;
     return 0;
 }
 
 // after a gradient pass: local sum of the partial slices + exchange with the peers + clip_values + Adam, one kernel
-int Engine::dp_update(float lr, cudaStream_t s) {
+// have_grad false: this rank's shard of the batch was empty (it still takes part in the exchange, with a zero gradient)
+int Engine::dp_update(float lr, bool have_grad, cudaStream_t s) {
     if (dp_world < 2) return fail(OEVAE_EINVAL, "dp_update: not connected");
     DpArgs a{};
-    if (fz && fz->last_fused) { a.parts = fz->parts; a.n_parts = fz->last_grid; }
+    if (!have_grad) { a.parts = fz ? fz->parts : parts; a.n_parts = 0; }
+    else if (fz && fz->last_fused) { a.parts = fz->parts; a.n_parts = fz->last_grid; }
     else { a.parts = parts; a.n_parts = n_slots_used; }
+    a.gsum_out = dp_gsum;
     a.part_stride = Ppad;
     ++step; ++dp_seq;
     const int b = (int)(dp_seq & 1u);
@@ -657,6 +641,13 @@ int Engine::dp_update(float lr, cudaStream_t s) {
     return 0;
 }
 
+// fresh optimiser: tf.keras.optimizers.Adam(lr) is constructed anew by every train_model call (models.py:138)
+int Engine::reset_opt() {
+    CK(cudaMemset(m, 0, 2 * P * sizeof(float)));
+    step = 0;
+    return 0;
+}
+
 int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o_mse, float* o_mae, float* o_kld, float* o_jsd,
                   float* o_lat, unsigned char* o_fin, float* o_xhat, cudaStream_t s) {
     if (N < 0 || n_iter < 1) return fail(OEVAE_EINVAL, "bad N / n_iter");
@@ -664,15 +655,9 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
     if (N == 0) return 0;
     // single sampling pass: the whole pass is one launch of the fused forward kernel in its
     // SCORE instantiation (X read once, nothing but the [N] score vectors written)
-    if (fz && fz->v2 && n_iter == 1 && !getenv("OEVAE_SCORE_LAYERED")) {
+    if (fz && n_iter == 1 && !knobs.score_layered) {
         FusedState& f = *fz;
-        if (f.img_dirty) {
-            AdamImgArgs ai{};
-            ai.theta = theta; ai.n = P; ai.wimg = f.wimg; ai.pos = f.pos;
-            { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, kAdamCols), kAdamCols * kAdamSlices, 0, s>>>(ai); }
-            CKL();
-            f.img_dirty = false;
-        }
+        TRY(refresh_images(s));
         F2Args b{};
         b.x = x; b.w = nullptr; b.eps = eps; b.theta = theta; b.wimg = f.wimg; b.parts = nullptr;
         b.B = N; b.n_tiles = (int)((N + kF2Jets - 1) / kF2Jets); b.train = 0; b.mse = 0; b.beta = 0.f;
@@ -680,17 +665,16 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
         b.step = (cfg.noise_mode == OEVAE_NOISE_PER_STEP) ? (unsigned)(4 * calls) : 0u;
         ++calls;
         b.s_mse = o_mse; b.s_mae = o_mae; b.s_kld = o_kld; b.s_jsd = o_jsd; b.s_lat = o_lat; b.s_fin = o_fin; b.s_xhat = o_xhat;
-        { const char* e = getenv("OEVAE_SCORE_HEADS_T"); b.heads_t = e ? atoi(e) : 0; }      // 1: heads with the jets on the lanes (A/B timing: +5% with two metrics, -3% with four)
+        b.heads_t = knobs.score_heads_t;                     // 1: heads with the jets on the lanes (A/B timing: +5% with two metrics, -3% with four)
         const int grid2 = std::min(b.n_tiles, n_sm);
-        static int* tile_ctr = nullptr;                                           // dynamic tile counter of the scoring pass
-        if (!tile_ctr) CK(cudaMalloc(&tile_ctr, 256));
-        CK(cudaMemsetAsync(tile_ctr, 0, sizeof(int), s));
-        b.tile_ctr = (getenv("OEVAE_SCORE_STATIC") && atoi(getenv("OEVAE_SCORE_STATIC"))) ? nullptr : tile_ctr;   // 1: round-robin tiles (A/B timing)
-        static long long* sdbg = nullptr;
-        const bool dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
-        if (dbg && !sdbg) { cudaMalloc(&sdbg, 1024 * sizeof(long long)); cudaMemset(sdbg, 0, 1024 * sizeof(long long)); }
-        b.dbg = dbg ? sdbg : nullptr;
-        if (dbg) { long long skip = getenv("OEVAE_DBG_SKIP") ? atoll(getenv("OEVAE_DBG_SKIP")) : 0; cudaMemcpy(sdbg + 1000, &skip, sizeof skip, cudaMemcpyHostToDevice); }
+        // dynamic tile counter of the pass: per handle, on the handle's device, zeroed in stream order (passes of one handle are
+        // serialised by its stream; a handle is not thread-safe, oevae.h)
+        CK(cudaMemsetAsync(f.tile_ctr, 0, sizeof(int), s));
+        b.tile_ctr = knobs.score_static ? nullptr : f.tile_ctr;   // OEVAE_SCORE_STATIC=1: round-robin tiles (A/B timing, bit-identical scores)
+        long long* sdbg = dbg_buffer();
+        const bool dbg = sdbg != nullptr;
+        b.dbg = sdbg;
+        if (dbg) { long long skip = knobs.dbg_skip; cudaMemcpy(sdbg + 1000, &skip, sizeof skip, cudaMemcpyHostToDevice); }
         {
             PROF("fused_score", s);
             // workers + issuer + producer + X stagers; the instantiation without the MSE vector keeps 16 more registers for the rest
@@ -877,6 +861,15 @@ int oevae_train_step(oevae_t h, const float* x_bkg, const float* w_bkg, const fl
     return e->reduce_and_update(nullptr, nullptr, true, lr, s);
 }
 
+int oevae_dp_last_grad_host(oevae_t h, float* grad_host, int64_t nn) {
+    H(h);
+    if (!grad_host || nn != e->P) return e->fail(OEVAE_EINVAL, "dp_last_grad: expected %ld floats", e->P);
+    if (!e->dp_gsum) return e->fail(OEVAE_EINVAL, "dp_last_grad: not connected");
+    return e->cuda_check(cudaMemcpy(grad_host, e->dp_gsum, nn * 4, cudaMemcpyDeviceToHost), "dp_last_grad");
+}
+
+int oevae_reset_opt_state(oevae_t h) { H(h); return e->reset_opt(); }
+
 int oevae_dp_export(oevae_t h, void* handle_out64) { H(h); return e->dp_export(handle_out64); }
 int oevae_dp_connect(oevae_t h, int32_t rank, int32_t world, const void* handles) { H(h); return e->dp_connect(rank, world, handles); }
 int oevae_train_step_dp(oevae_t h, const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood,
@@ -885,9 +878,12 @@ int oevae_train_step_dp(oevae_t h, const float* x_bkg, const float* w_bkg, const
     H(h);
     cudaStream_t s = (cudaStream_t)stream;
     if (e->dp_world < 2) return e->fail(OEVAE_EINVAL, "train_step_dp: call oevae_dp_export / oevae_dp_connect first");
-    int rc = e->losses(x_bkg, w_bkg, x_ood, w_ood, eps, n_eps, B, beta, lamb, margin, per_jet_out, sums_acc, true, s);
-    if (rc) return rc;
-    return e->dp_update(lr, s);
+    // B == 0: a rank whose shard of the (short, last) global batch is empty still exchanges -- a zero gradient
+    if (B > 0) {
+        int rc = e->losses(x_bkg, w_bkg, x_ood, w_ood, eps, n_eps, B, beta, lamb, margin, per_jet_out, sums_acc, true, s);
+        if (rc) return rc;
+    } else if (B < 0) return e->fail(OEVAE_EINVAL, "negative batch");
+    return e->dp_update(lr, B > 0, s);
 }
 
 int oevae_loss_and_grad(oevae_t h, const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood,
@@ -896,6 +892,7 @@ int oevae_loss_and_grad(oevae_t h, const float* x_bkg, const float* w_bkg, const
     H(h);
     if (!grad_out) return e->fail(OEVAE_EINVAL, "grad_out is null");
     cudaStream_t s = (cudaStream_t)stream;
+    if (B == 0) return e->cuda_check(cudaMemsetAsync(grad_out, 0, e->P * sizeof(float), s), "zero gradient of an empty shard");
     int rc = e->losses(x_bkg, w_bkg, x_ood, w_ood, eps, n_eps, B, beta, lamb, margin, per_jet_out, sums_acc, true, s);
     if (rc) return rc;
     return e->reduce_and_update(grad_out, nullptr, false, 0.f, s);
@@ -968,6 +965,16 @@ int oevae_affine(const float* x, float* y, int64_t N, int32_t D, const double* c
     affine_kernel<<<cdiv(N * D, 256), 256, 0, (cudaStream_t)stream>>>(x, y, N, D, center, scale);
     LAUNCHED();
     return free_fail(cudaGetLastError(), "affine launch");
+}
+
+int oevae_ingest_f16(const void* raw_f16, float* x, int64_t N, int32_t D, const double* center, const double* scale, int32_t device, void* stream) {
+    if (N == 0) return 0;
+    if (!raw_f16 || !x || N < 0 || D <= 0 || (center && !scale)) { g_create_error = "ingest_f16: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    const long n = (long)N * D;
+    { PROF("ingest_f16", (cudaStream_t)stream); ingest_f16_kernel<<<cdiv((n + 7) / 8, 256), 256, 0, (cudaStream_t)stream>>>((const __half*)raw_f16, x, n, D, center, scale); }
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "ingest_f16 launch");
 }
 
 int oevae_pair_metrics(const float* P, const float* Q, int64_t N, int32_t D, float* mse, float* mae, float* mare, float* kld,

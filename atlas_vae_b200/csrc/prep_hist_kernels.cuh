@@ -210,6 +210,46 @@ __global__ void preprocess_kernel(const T* __restrict__ raw, long N, int n_raw, 
 }
 
 // ------------------------------------------------------------------------------------------------
+// fp16 ingest: the reference's files hold the constituents as float16 (tools/merging.py:31,51-53), load_data widens them to float32
+// (utils.py:89-97: jets_sorting returns np.float32) and apply_scaling transforms them (utils.py:406-417).  A host that keeps the
+// sorted / truncated fp16 rows uploads half the bytes; this kernel is float32(raw) followed by the same fp64-evaluated affine map
+// as preprocess_kernel / affine_kernel, eight elements per thread (one 16-byte load, two 16-byte stores).
+// ------------------------------------------------------------------------------------------------
+__global__ void ingest_f16_kernel(const __half* __restrict__ raw, float* __restrict__ x, long n_elems, int D,
+                                  const double* __restrict__ center, const double* __restrict__ scale) {
+    const long i8 = ((long)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+    if (i8 >= n_elems) return;
+    float v[8];
+    const bool vec = i8 + 8 <= n_elems && ((reinterpret_cast<uintptr_t>(raw + i8) & 15) == 0) && ((reinterpret_cast<uintptr_t>(x + i8) & 15) == 0);
+    if (vec) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4*>(raw + i8));
+        const __half2* h = reinterpret_cast<const __half2*>(&q);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { const float2 f = __half22float2(h[k]); v[2 * k] = f.x; v[2 * k + 1] = f.y; }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = i8 + k < n_elems ? __half2float(raw[i8 + k]) : 0.f;
+    }
+    if (scale) {
+        int c = (int)(i8 % D);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            double t = (double)v[k];
+            if (center) t = (double)(float)(t - center[c]);
+            v[k] = (float)(t / scale[c]);
+            if (++c == D) c = 0;
+        }
+    }
+    if (vec) {
+        *reinterpret_cast<float4*>(x + i8) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(x + i8 + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) if (i8 + k < n_elems) x[i8 + k] = v[k];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // loss_mapping (plots.py:15-20): global min/max (decides the branch) and the elementwise map.
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void atomic_min_double(double* addr, double val) {

@@ -52,7 +52,7 @@ def parse_args(argv=None):
     p.add_argument('--HLVs', default='OFF')
     p.add_argument('--patience', default=3, type=int)                             # hard-coded 3 in models.py:222
     p.add_argument('--n_gpus', default=1, type=int)
-    p.add_argument('--precision', default='bf16x3', choices=['fp32', 'bf16x3', 'tf32', 'bf16'])
+    p.add_argument('--precision', default='bf16x3', choices=['fp32', 'bf16x3', 'bf16'])
     p.add_argument('--seed', default=1234, type=int)
     a = p.parse_args(argv)
     for key in ['n_train', 'n_valid', 'n_OoD', 'n_sig', 'batch_size']:           # vae.py:50

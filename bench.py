@@ -355,7 +355,7 @@ def main():
     ap.add_argument('--steps', type=int, default=200)
     ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--precision', default='bf16x3', choices=['fp32', 'bf16x3', 'tf32', 'bf16'])
+    ap.add_argument('--precision', default='bf16x3', choices=['fp32', 'bf16x3', 'bf16'])
     ap.add_argument('--cpu-steps', type=int, default=300)
     ap.add_argument('--no-cpu', action='store_true')
     ap.add_argument('--no-extra', action='store_true', help='skip the cfg-3 (OE) and cfg-5 (wide) legs')

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define OEVAE_VERSION 100
+#define OEVAE_VERSION 200
 #if defined(__GNUC__)
 #define OEVAE_API __attribute__((visibility("default")))
 #else
@@ -36,10 +36,10 @@ enum { OEVAE_OK = 0, OEVAE_EINVAL = -1, OEVAE_ECUDA = -2, OEVAE_ENOMEM = -3, OEV
 /* OE_type of models.py:72-105 */
 enum { OEVAE_OE_KLD = 0, OEVAE_OE_MSE = 1, OEVAE_OE_MAE = 2, OEVAE_OE_MSE_MARGIN = 3, OEVAE_OE_MAE_MARGIN = 4 };
 
-/* arithmetic of the Dense contractions */
+/* arithmetic of the Dense contractions (value 2 is unassigned: a kind::tf32 mode was planned and dropped -- bf16x3 reaches
+ * fp32-grade accuracy at the same MMA cost per product) */
 enum { OEVAE_PREC_FP32 = 0,      /* CUDA-core fp32 FMA: the reference-dtype mode and parity anchor   */
        OEVAE_PREC_BF16X3 = 1,    /* tcgen05 kind::f16, operands split hi+lo bf16, 3 MMAs, fp32 accum */
-       OEVAE_PREC_TF32 = 2,      /* tcgen05 kind::tf32, fp32 accumulate                              */
        OEVAE_PREC_BF16 = 3 };    /* tcgen05 kind::f16 on bf16-rounded operands, fp32 accumulate      */
 
 /* where the reparameterisation noise comes from (models.py:9-15) */
@@ -79,6 +79,8 @@ OEVAE_API int oevae_set_params_host(oevae_t h, const float* flat_host, int64_t n
 OEVAE_API int oevae_get_params_host(oevae_t h, float* flat_host, int64_t n);
 OEVAE_API int oevae_set_opt_state_host(oevae_t h, const float* m_host, const float* v_host, int64_t n, int64_t step);
 OEVAE_API int oevae_get_opt_state_host(oevae_t h, float* m_host, float* v_host, int64_t n, int64_t* step);
+/* fresh optimiser (m = v = 0, step = 0): the reference builds a new tf.keras.optimizers.Adam in every train_model call (models.py:138) */
+OEVAE_API int oevae_reset_opt_state(oevae_t h);
 OEVAE_API float* oevae_params_device(oevae_t h);              /* device address of the flat parameters (read-only for callers) */
 /* Philox row counter of row 0 of the next calls: a data-parallel rank passes its offset inside the global
  * batch so that the noise of a jet does not depend on how the batch is sharded. */
@@ -112,7 +114,8 @@ OEVAE_API int oevae_loss_and_grad(oevae_t h, const float* x_bkg, const float* w_
  * its 64-byte cudaIpcMemHandle_t; the caller gathers the handles of all ranks (any transport) and passes the
  * world x 64 bytes to oevae_dp_connect.  oevae_train_step_dp is oevae_train_step for one rank's slice of the global
  * batch: its update kernel sums this rank's partial gradients, exchanges the result with the peers through P2P loads /
- * stores and applies clip + Adam to the SUM over ranks (models.py:183), identically on every rank.
+ * stores and applies clip + Adam to the SUM over ranks (models.py:183), identically on every rank.  B == 0 is allowed there:
+ * a rank whose shard of a short last batch is empty still joins the exchange, with a zero gradient.
  * OEVAE_EUNSUPPORTED from oevae_dp_connect (network too large for a co-resident launch): use oevae_loss_and_grad +
  * all-reduce + oevae_apply_update. */
 OEVAE_API int oevae_dp_export(oevae_t h, void* handle_out64);
@@ -122,6 +125,10 @@ OEVAE_API int oevae_train_step_dp(oevae_t h, const float* x_bkg, const float* w_
                         const float* eps, int32_t n_eps, int64_t B,
                         float lr, float beta, float lamb, float margin,
                         float* per_jet_out, double* sums_acc, void* stream);
+
+/* the SUM over ranks of the last oevae_train_step_dp's gradient, before clip_values (host copy; synchronises): lets a
+ * data-parallel caller check the exchanged gradient against oevae_loss_and_grad of the global batch */
+OEVAE_API int oevae_dp_last_grad_host(oevae_t h, float* grad_host, int64_t n);
 
 /* clip_values(grad) + Adam with the given (possibly all-reduced) gradient; increments the step. */
 OEVAE_API int oevae_apply_update(oevae_t h, const float* grad, float lr, void* stream);
@@ -155,6 +162,13 @@ OEVAE_API int oevae_preprocess(const void* raw, int32_t raw_dtype, int64_t N, in
                      int32_t n_dims, const double* center, const double* scale, int32_t sort,
                      float* x_out, float* pt_out, float* m_out, int32_t device, void* stream);
 
+/* fp16 ingest: the reference's files store the constituents as float16 (tools/merging.py:31,51-53); load_data widens them to
+ * float32 (utils.py:89-97) and apply_scaling transforms them (utils.py:406-417).  raw_f16 [N,D] (already sorted / sliced) ->
+ * x [N,D] = fp32(fp32(fp32(raw) - center) / scale), center / scale nullable as in oevae_preprocess.  Bit-identical to
+ * oevae_affine on the widened array, at half the upload bytes. */
+OEVAE_API int oevae_ingest_f16(const void* raw_f16, float* x, int64_t N, int32_t D, const double* center, const double* scale,
+                     int32_t device, void* stream);
+
 /* apply_scaling for affine scalers (utils.py:406-417) on an already sliced [N,D] array; y may alias x */
 OEVAE_API int oevae_affine(const float* x, float* y, int64_t N, int32_t D, const double* center, const double* scale,
                  int32_t device, void* stream);
@@ -177,29 +191,6 @@ OEVAE_API int oevae_loss_map(float* v, int64_t N, int32_t branch, int32_t device
 OEVAE_API int oevae_hist(const float* var, const float* w, const float* jzw, const float* score, const uint8_t* keep,
                int64_t N, float cut, const double* edges, int32_t n_edges,
                int64_t* counts, double* wsums, int32_t device, void* stream);
-
-/* The layered Dense contraction on its own (kernel-level tests): C[R,Cn] = sum_t A[r*sAr+t*sAt] * B[t*sBt+c*sBc]
- * (+bias[c], ReLU) in the handle's precision.  kind 0: forward (sAt==1, sBc==1), 1: dX (sAt==1, sBt==1),
- * 2: dW (sAr==1, sBc==1) -- the three operand orientations of models.py:31-34 and its tape gradient. */
-OEVAE_API int oevae_gemm(oevae_t h, int32_t kind, const float* A, int64_t sAr, int64_t sAt, const float* B, int64_t sBt, int64_t sBc,
-               float* C, int32_t ldc, int32_t R, int32_t Cn, int32_t T, const float* bias, int32_t relu, void* stream);
-
-/* Hardware-layout probe (tests): C = A^T B through MN-major SWIZZLE_128B descriptors, A [K,M], B [K,N]; dumps the
- * raw TMEM accumulator [128 lanes, N] so that the M=64 / M=128 lane mapping can be asserted. */
-OEVAE_API int oevae_probe_mn(const float* A, const float* B, int32_t K, int32_t M, int32_t N, float* raw_out, int32_t device, void* stream);
-
-/* Tuning probe: cycles from issuing nm = {1,3,6,12,18,36} dependent tcgen05.mma (M x N x 16, bf16) to the mbarrier
- * wake-up after tcgen05.commit; out_host6 is a HOST array of 6 int64. */
-OEVAE_API int oevae_probe_latency(int32_t M, int32_t N, int64_t* out_host6, int32_t device);
-
-/* Tuning probe: cycles for nw warps to each issue nm tcgen05.mma (mode 0: descriptors rebuilt, 1: hoisted) and see
- * their commit; out_host1 is a HOST int64. */
-OEVAE_API int oevae_probe_issue(int32_t M, int32_t N, int32_t nw, int32_t nm, int32_t mode, int64_t* out_host1, int32_t device);
-
-/* Tuning probe: cycles for `depth` cp.async.bulk global->shared copies of `bytes` each, issued back to back by one
- * thread of each of n_cta CTAs (same_src: every CTA reads the same bytes, as the weight images are read);
- * out_host2 = {best of 5, first (cold)} of CTA 0. */
-OEVAE_API int oevae_probe_bulk(int32_t bytes, int32_t depth, int32_t n_cta, int32_t same_src, int64_t* out_host2, int32_t device);
 
 /* _BatchStager (host loads -> device batches, replacing the implicit per-step H2D of models.py:180): page-lock a
  * host array in place.  Returns 0 when newly registered (release it with oevae_host_unregister), 1 when the range

@@ -1,5 +1,5 @@
-"""CPU-side checks of the boundary: the shared library loads, exports every symbol include/oevae.h declares,
-and the ctypes table mirrors the header.  No compute calls (there is no GPU on the CPU test box)."""
+"""CPU-side checks of the boundary: the shared library loads, exports every symbol include/oevae.h (the drop-in boundary) and
+include/oevae_test.h (kernel-level test / tuning entry points) declare, and the ctypes tables mirror the headers.  No compute calls (there is no GPU on the CPU test box)."""
 import os
 import re
 import subprocess
@@ -8,8 +8,8 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _declared():
-    src = open(os.path.join(ROOT, 'include', 'oevae.h')).read()
+def _declared(header='oevae.h'):
+    src = open(os.path.join(ROOT, 'include', header)).read()
     return sorted(set(re.findall(r'OEVAE_API[^;]*?\b(oevae_\w+)\s*\(', src)))
 
 
@@ -21,23 +21,25 @@ def test_library_builds_and_exports_header_symbols():
     exported = sorted(set(re.findall(r'\b(oevae_\w+)\b', out)))
     declared = _declared()
     assert len(declared) >= 25
-    assert exported == declared
+    assert not any(d.startswith('oevae_probe') or d == 'oevae_gemm' for d in declared)   # test hooks stay out of the public header
+    assert exported == sorted(declared + _declared('oevae_test.h'))
 
 
 def test_ctypes_table_matches_header():
     from atlas_vae_b200 import _ffi
     assert sorted(_ffi.SIGNATURES) == _declared()
+    assert sorted(_ffi.TEST_SIGNATURES) == _declared('oevae_test.h')
     L = _ffi.lib()                              # dlopen + resolve every symbol
-    assert L.oevae_version() == 100
+    assert L.oevae_version() == 200
     assert _ffi.launch_count() == 0
 
 
 def test_argument_counts_match_header():
     """Each ctypes argtypes list has as many entries as the C prototype has parameters."""
     from atlas_vae_b200 import _ffi
-    src = open(os.path.join(ROOT, 'include', 'oevae.h')).read()
+    src = open(os.path.join(ROOT, 'include', 'oevae.h')).read() + open(os.path.join(ROOT, 'include', 'oevae_test.h')).read()
     src = re.sub(r'/\*.*?\*/', '', src, flags=re.S)
-    for name, (_, argtypes) in _ffi.SIGNATURES.items():
+    for name, (_, argtypes) in list(_ffi.SIGNATURES.items()) + list(_ffi.TEST_SIGNATURES.items()):
         m = re.search(r'\b%s\s*\(([^)]*)\)' % name, src)
         assert m, name
         params = m.group(1).strip()
