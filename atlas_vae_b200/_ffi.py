@@ -24,6 +24,20 @@ class Config(C.Structure):
                 ('noise_mode', C.c_int32), ('device', C.c_int32), ('seed', C.c_uint64), ('max_batch', C.c_int64)]
 
 
+class HostLoad(C.Structure):
+    """oevae_host_load (include/oevae.h)"""
+    _fields_ = [('x_host', C.c_void_p), ('w_host', C.c_void_p), ('xo_host', C.c_void_p), ('wo_host', C.c_void_p),
+                ('x_dtype', C.c_int32), ('update', C.c_int32),
+                ('n_rows', C.c_int64), ('batch_size', C.c_int64), ('first_batch', C.c_int64), ('n_batches', C.c_int64),
+                ('rank', C.c_int32), ('world', C.c_int32), ('noise_row0', C.c_int64),
+                ('center', C.c_void_p), ('scale', C.c_void_p),
+                ('x_resident', C.c_void_p), ('w_resident', C.c_void_p), ('xo_resident', C.c_void_p), ('wo_resident', C.c_void_p),
+                ('resident_stride', C.c_int64),
+                ('lr', C.c_float), ('beta', C.c_float), ('lamb', C.c_float), ('margin', C.c_float),
+                ('sums_acc', C.c_void_p), ('sums_trace_host', C.c_void_p),
+                ('h2d_bytes', C.c_int64)]
+
+
 _lib = None
 _vp, _i32, _i64, _f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 
@@ -46,6 +60,7 @@ SIGNATURES = {
     'oevae_train_step': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _f32, _f32, _f32, _f32, _vp, _vp, _vp]),
     'oevae_loss_and_grad': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _i64, _f32, _f32, _f32, _vp, _vp, _vp, _vp]),
     'oevae_apply_update': (C.c_int, [_vp, _vp, _f32, _vp]),
+    'oevae_train_batches_host': (C.c_int, [_vp, C.POINTER(HostLoad), _vp]),
     'oevae_dp_export': (C.c_int, [_vp, _vp]),
     'oevae_dp_connect': (C.c_int, [_vp, _i32, _i32, _vp]),
     'oevae_dp_last_grad_host': (C.c_int, [_vp, _vp, _i64]),

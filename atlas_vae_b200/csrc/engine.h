@@ -64,6 +64,12 @@ struct Engine {
     int dp_rank = -1, dp_world = 0, dp_nblk = 0; unsigned int dp_seq = 0;
     float* dp_gsum = nullptr;     // [P] SUM over ranks of the last step's gradient, before clip_values (parity checks: oevae_dp_last_grad_host)
 
+    // host-load loop (oevae_train_batches_host): copy stream, per-slot events, staging ring (3 slots)
+    cudaStream_t hl_copy = nullptr; cudaEvent_t hl_ready[3] = {nullptr, nullptr, nullptr}, hl_freed[3] = {nullptr, nullptr, nullptr};
+    unsigned char* hl_ring = nullptr; size_t hl_ring_bytes = 0;
+    bool hl_used[3] = {false, false, false};
+    const void* hl_src = nullptr; long hl_copied_upto = 0;   // batches [.., hl_copied_upto) of the load at hl_src have their copies issued
+
     ~Engine();
     int fail(int code, const char* fmt, ...);
     int cuda_check(cudaError_t e, const char* what);
@@ -94,6 +100,7 @@ struct Engine {
     int dp_connect(int rank, int world, const void* handles);
     int dp_update(float lr, bool have_grad, cudaStream_t s);
     int reset_opt();
+    int train_batches_host(oevae_host_load& a, cudaStream_t s);
     int score(const float* x, long N, int n_iter, const float* eps, float* o_mse, float* o_mae, float* o_kld, float* o_jsd,
               float* o_lat, unsigned char* o_fin, float* o_xhat, cudaStream_t s);
     int encode(const float* x, long N, const float* eps, float* o_mu, float* o_lv, float* o_z, cudaStream_t s);

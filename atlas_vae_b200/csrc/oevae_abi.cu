@@ -118,6 +118,9 @@ Engine::~Engine() {
     if (theta) cudaFree(theta);
     if (arena) cudaFree(arena);
     if (dp_gsum) cudaFree(dp_gsum);
+    if (hl_ring) cudaFree(hl_ring);
+    for (int k = 0; k < 3; ++k) { if (hl_ready[k]) cudaEventDestroy(hl_ready[k]); if (hl_freed[k]) cudaEventDestroy(hl_freed[k]); }
+    if (hl_copy) cudaStreamDestroy(hl_copy);
     if (fz) {
         if (fz->wimg) cudaFree(fz->wimg); if (fz->pos) cudaFree(fz->pos); if (fz->parts) cudaFree(fz->parts); if (fz->oe_pj) cudaFree(fz->oe_pj);
         if (fz->oe_c) cudaFree(fz->oe_c); if (fz->tile_ctr) cudaFree(fz->tile_ctr); if (fz->dbg_buf) cudaFree(fz->dbg_buf);
@@ -641,6 +644,117 @@ int Engine::dp_update(float lr, bool have_grad, cudaStream_t s) {
     return 0;
 }
 
+// train_model's batch loop over a host-resident load (models.py:172-190): see oevae.h.  Slot k of the ring (or row b * stride of
+// the resident buffers) is filled on the copy stream and consumed on the caller's stream; ready[k] / freed[k] order the two.
+int Engine::train_batches_host(oevae_host_load& a, cudaStream_t s) {
+    if (!a.x_host || !a.w_host || a.n_rows <= 0 || a.batch_size <= 0 || a.first_batch < 0 || a.n_batches < 0) return fail(OEVAE_EINVAL, "train_batches_host: bad arguments");
+    if ((a.xo_host == nullptr) != (a.wo_host == nullptr)) return fail(OEVAE_EINVAL, "train_batches_host: xo_host and wo_host must be given together");
+    if (a.x_dtype != 0 && a.x_dtype != 1) return fail(OEVAE_EINVAL, "train_batches_host: x_dtype must be 0 (float32) or 1 (float16)");
+    if (a.world < 1 || a.rank < 0 || a.rank >= a.world) return fail(OEVAE_EINVAL, "train_batches_host: bad rank / world");
+    if (a.update == 1 && dp_world < 2) return fail(OEVAE_EINVAL, "train_batches_host: update 1 needs oevae_dp_connect");
+    if (a.update != 0 && a.update != 1) return fail(OEVAE_EINVAL, "train_batches_host: bad update mode");
+    if (a.center && !a.scale) return fail(OEVAE_EINVAL, "train_batches_host: center without scale");
+    if (cfg.noise_mode == OEVAE_NOISE_EXTERNAL) return fail(OEVAE_EINVAL, "train_batches_host: noise_mode EXTERNAL has no eps source here");
+    const bool ood = a.xo_host != nullptr, f16 = a.x_dtype == 1, resident = a.x_resident != nullptr;
+    if (resident && (!a.w_resident || (ood && (!a.xo_resident || !a.wo_resident)))) return fail(OEVAE_EINVAL, "train_batches_host: incomplete resident buffers");
+    const long cap = (a.batch_size + a.world - 1) / a.world + 1;                 // largest shard of a global batch
+    if (resident && a.resident_stride < cap - 1) return fail(OEVAE_EINVAL, "train_batches_host: resident_stride too small");
+    if (!hl_copy) {
+        CK(cudaStreamCreateWithFlags(&hl_copy, cudaStreamNonBlocking));
+        for (int k = 0; k < 3; ++k) { CK(cudaEventCreateWithFlags(&hl_ready[k], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&hl_freed[k], cudaEventDisableTiming)); }
+    }
+    // ring slot: [x fp32][xo fp32][w][wo][x f16][xo f16]; with resident buffers only the f16 staging part is used
+    const size_t xb = (size_t)cap * D * 4, wb = ((size_t)cap * 4 + 255) / 256 * 256, hb = ((size_t)cap * D * 2 + 255) / 256 * 256;
+    const size_t slot_bytes = 2 * xb + 2 * wb + 2 * hb;
+    if (hl_ring_bytes < 3 * slot_bytes) {
+        CK(cudaStreamSynchronize(s)); CK(cudaStreamSynchronize(hl_copy));
+        if (hl_ring) cudaFree(hl_ring);
+        hl_ring = nullptr; hl_ring_bytes = 0;
+        CK(cudaMalloc(&hl_ring, 3 * slot_bytes));
+        hl_ring_bytes = 3 * slot_bytes;
+        for (int k = 0; k < 3; ++k) hl_used[k] = false;
+    }
+    const size_t esz = f16 ? 2 : 4;
+    const long nb_total = (a.n_rows + a.batch_size - 1) / a.batch_size;
+    const long b_end = std::min<long>(a.first_batch + a.n_batches, nb_total);
+    struct Shard { long lo, n, off; };
+    auto shard = [&](long b) {
+        const long g0 = b * a.batch_size, g1 = std::min<long>(g0 + a.batch_size, a.n_rows), n = g1 - g0;
+        const long s0 = (n * a.rank) / a.world, s1 = (n * (a.rank + 1)) / a.world;
+        return Shard{g0 + s0, s1 - s0, s0};
+    };
+    struct Bufs { float *x, *xo, *w, *wo; unsigned char *hx, *hxo; };
+    auto bufs = [&](long b) {
+        unsigned char* base = hl_ring + (size_t)(b % 3) * slot_bytes;
+        Bufs r;
+        r.x = reinterpret_cast<float*>(base); r.xo = reinterpret_cast<float*>(base + xb);
+        r.w = reinterpret_cast<float*>(base + 2 * xb); r.wo = reinterpret_cast<float*>(base + 2 * xb + wb);
+        r.hx = base + 2 * xb + 2 * wb; r.hxo = r.hx + hb;
+        if (resident) {
+            r.x = a.x_resident + (size_t)b * a.resident_stride * D; r.w = a.w_resident + (size_t)b * a.resident_stride;
+            if (ood) { r.xo = a.xo_resident + (size_t)b * a.resident_stride * D; r.wo = a.wo_resident + (size_t)b * a.resident_stride; }
+        }
+        return r;
+    };
+    auto issue_copy = [&](long b) -> int {
+        const int k = (int)(b % 3);
+        const Shard sh = shard(b);
+        const Bufs d = bufs(b);
+        if (hl_used[k]) CK(cudaStreamWaitEvent(hl_copy, hl_freed[k], 0));          // the step that read slot k's previous content is done
+        if (sh.n > 0) {
+            const size_t xbytes = (size_t)sh.n * D * esz;
+            CK(cudaMemcpyAsync(f16 ? (void*)d.hx : (void*)d.x, (const unsigned char*)a.x_host + (size_t)sh.lo * D * esz, xbytes, cudaMemcpyHostToDevice, hl_copy));
+            CK(cudaMemcpyAsync(d.w, a.w_host + sh.lo, (size_t)sh.n * 4, cudaMemcpyHostToDevice, hl_copy));
+            a.h2d_bytes += (int64_t)(xbytes + (size_t)sh.n * 4);
+            if (ood) {
+                CK(cudaMemcpyAsync(f16 ? (void*)d.hxo : (void*)d.xo, (const unsigned char*)a.xo_host + (size_t)sh.lo * D * esz, xbytes, cudaMemcpyHostToDevice, hl_copy));
+                CK(cudaMemcpyAsync(d.wo, a.wo_host + sh.lo, (size_t)sh.n * 4, cudaMemcpyHostToDevice, hl_copy));
+                a.h2d_bytes += (int64_t)(xbytes + (size_t)sh.n * 4);
+            }
+        }
+        CK(cudaEventRecord(hl_ready[k], hl_copy));
+        return 0;
+    };
+    a.h2d_bytes = 0;
+    const unsigned long long save_off = row_offset;
+    // copies run two batches ahead of the steps, also across calls: a caller that walks a load in groups (train_model reads the
+    // running means every 10 batches, models.py:191) finds the first batches of the next group already in flight
+    if (hl_src != a.x_host || hl_copied_upto < a.first_batch || hl_copied_upto > a.first_batch + 2) { hl_src = a.x_host; hl_copied_upto = a.first_batch; }
+    auto copy_upto = [&](long upto) -> int {                                       // issue the copies of batches [hl_copied_upto, upto)
+        for (; hl_copied_upto < std::min<long>(upto, nb_total); ++hl_copied_upto) TRY(issue_copy(hl_copied_upto));
+        return 0;
+    };
+    TRY(copy_upto(a.first_batch + 2));
+    for (long b = a.first_batch; b < b_end; ++b) {
+        const int k = (int)(b % 3);
+        const Shard sh = shard(b);
+        const Bufs d = bufs(b);
+        CK(cudaStreamWaitEvent(s, hl_ready[k], 0));
+        if (sh.n > 0) {
+            const long ne = sh.n * D;
+            if (f16) {
+                { PROF("ingest_f16", s); ingest_f16_kernel<<<cdiv((ne + 7) / 8, 256), 256, 0, s>>>(reinterpret_cast<const __half*>(d.hx), d.x, ne, D, a.center, a.scale); } CKL();
+                if (ood) { { PROF("ingest_f16", s); ingest_f16_kernel<<<cdiv((ne + 7) / 8, 256), 256, 0, s>>>(reinterpret_cast<const __half*>(d.hxo), d.xo, ne, D, a.center, a.scale); } CKL(); }
+            } else if (a.scale) {
+                { PROF("affine", s); affine_kernel<<<cdiv(ne, 256), 256, 0, s>>>(d.x, d.x, sh.n, D, a.center, a.scale); } CKL();
+                if (ood) { { PROF("affine", s); affine_kernel<<<cdiv(ne, 256), 256, 0, s>>>(d.xo, d.xo, sh.n, D, a.center, a.scale); } CKL(); }
+            }
+        }
+        row_offset = save_off + (unsigned long long)(a.noise_row0 + sh.off);        // noise of a jet does not depend on the sharding
+        int rc = 0;
+        if (sh.n > 0) rc = losses(d.x, d.w, ood ? d.xo : nullptr, ood ? d.wo : nullptr, nullptr, 0, sh.n, a.beta, a.lamb, a.margin, nullptr, a.sums_acc, true, s);
+        if (!rc) rc = a.update == 1 ? dp_update(a.lr, sh.n > 0, s) : (sh.n > 0 ? reduce_and_update(nullptr, nullptr, true, a.lr, s) : 0);
+        row_offset = save_off;
+        if (rc) return rc;
+        CK(cudaEventRecord(hl_freed[k], s)); hl_used[k] = true;
+        if (a.sums_trace_host && a.sums_acc)
+            CK(cudaMemcpyAsync(a.sums_trace_host + 4 * (b - a.first_batch), a.sums_acc, 4 * sizeof(double), cudaMemcpyDeviceToHost, s));
+        TRY(copy_upto(b + 3));
+    }
+    if (b_end >= nb_total) hl_src = nullptr;                                       // load finished: the next call starts afresh
+    return 0;
+}
+
 // fresh optimiser: tf.keras.optimizers.Adam(lr) is constructed anew by every train_model call (models.py:138)
 int Engine::reset_opt() {
     CK(cudaMemset(m, 0, 2 * P * sizeof(float)));
@@ -896,6 +1010,12 @@ int oevae_loss_and_grad(oevae_t h, const float* x_bkg, const float* w_bkg, const
     int rc = e->losses(x_bkg, w_bkg, x_ood, w_ood, eps, n_eps, B, beta, lamb, margin, per_jet_out, sums_acc, true, s);
     if (rc) return rc;
     return e->reduce_and_update(grad_out, nullptr, false, 0.f, s);
+}
+
+int oevae_train_batches_host(oevae_t h, oevae_host_load* load, void* stream) {
+    H(h);
+    if (!load) return e->fail(OEVAE_EINVAL, "train_batches_host: null load");
+    return e->train_batches_host(*load, (cudaStream_t)stream);
 }
 
 int oevae_apply_update(oevae_t h, const float* grad, float lr, void* stream) {

@@ -53,3 +53,27 @@ def shard_bounds(n, rank, world):
 def barrier():
     if td.is_available() and td.is_initialized() and td.get_world_size() > 1:
         td.barrier()
+
+
+def bind_to_gpu_numa(local_rank):
+    """Pin this process to the CPUs of the NUMA node its GPU hangs off (sysfs), BEFORE it allocates host buffers, so that the
+    page-locked batches a rank uploads are first-touched on the node next to its GPU.  Returns a short description (for bench
+    records); does nothing when the topology is not exposed."""
+    try:
+        out = __import__('subprocess').run(['nvidia-smi', '--query-gpu=pci.bus_id', '--format=csv,noheader', '-i', str(local_rank)],
+                                           capture_output=True, text=True, timeout=20).stdout.strip().lower()
+        bus = out[-12:] if len(out) >= 12 else out                 # 00000000:1b:00.0 -> 0000:1b:00.0
+        base = '/sys/bus/pci/devices/' + bus
+        node = int(open(base + '/numa_node').read().strip())
+        cl = open(base + '/local_cpulist').read().strip()
+        cpus = set()
+        for part in cl.split(','):
+            a, _, b = part.partition('-')
+            cpus |= set(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if node < 0 or not cpus:
+            return 'gpu %s: no NUMA affinity exposed' % bus
+        os.sched_setaffinity(0, cpus)
+        return 'gpu %s -> NUMA node %d (%d cpus)' % (bus, node, len(cpus))
+    except Exception as e:                                          # noqa: BLE001 -- diagnostics only
+        return 'not bound (%s)' % type(e).__name__

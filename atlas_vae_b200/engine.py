@@ -91,6 +91,16 @@ class DeviceVAE:
         check(self.lib.oevae_get_opt_state_host(self.h, ptr(m), ptr(v), m.size, C.byref(st)), self.h)
         return m, v, int(st.value)
 
+    def reset_opt(self):
+        """Fresh Adam (m = v = 0, step = 0): what `tf.keras.optimizers.Adam(lr)` at models.py:138 gives every train_model call."""
+        check(self.lib.oevae_reset_opt_state(self.h), self.h)
+
+    def dp_last_grad(self):
+        """SUM over ranks of the last train_step_dp's gradient, before clip_values (host array)."""
+        g = np.empty(self.n_params, np.float32)
+        check(self.lib.oevae_dp_last_grad_host(self.h, ptr(g), g.size), self.h)
+        return g
+
     def set_noise_offset(self, row_offset):
         check(self.lib.oevae_set_noise_offset(self.h, int(row_offset)), self.h)
 
@@ -152,6 +162,11 @@ class DeviceVAE:
         eps, n_eps = self._eps(eps, B)
         check(self.lib.oevae_train_step_dp(self.h, ptr(x), ptr(w), ptr(x_ood), ptr(w_ood), ptr(eps), n_eps, B,
                                            lr, beta, lamb, margin, ptr(per_jet), ptr(sums), _stream()), self.h)
+
+    def train_batches_host(self, load):
+        """oevae_train_batches_host: `load` is an _ffi.HostLoad; returns the host->device bytes the call copied."""
+        check(self.lib.oevae_train_batches_host(self.h, C.byref(load), _stream()), self.h)
+        return int(load.h2d_bytes)
 
     def loss_and_grad(self, x, w, x_ood=None, w_ood=None, eps=None, beta=0., lamb=0., margin=0.,
                       per_jet=None, sums=None, grad=None):

@@ -190,28 +190,90 @@ def get_losses(vae, data, OE_type, beta, lamb, margin, eps=None):
 
 
 # ------------------------------------------------------------------------------------------------ staging
-class _BatchStager:
-    """Host (NumPy) load -> device batches.  The arrays of a load are page-locked in place once
-    (cudaHostRegister) and every batch is copied host->device on a side stream, two batches ahead of the
-    compute stream, so the training loop never waits on PCIe unless PCIe is the bottleneck."""
+_PINNED = {}                                                  # (address, bytes) -> [array, refcount]: arrays page-locked in place
 
-    def __init__(self, arrays, batch_size, device, shard=(0, 1)):
-        self.device = device
-        self.arrays = [np.ascontiguousarray(a, np.float32) for a in arrays]
+
+def _pin(a):
+    """cudaHostRegister the array's memory once (a load is stepped through every epoch); _unpin releases it."""
+    if a is None or a.nbytes == 0:
+        return
+    key = (a.ctypes.data, a.nbytes)
+    if key in _PINNED:
+        _PINNED[key][1] += 1
+    elif _ffi.lib().oevae_host_register(a.ctypes.data, a.nbytes) == 0:
+        _PINNED[key] = [a, 1]
+
+
+def _unpin(a):
+    if a is None:
+        return
+    key = (a.ctypes.data, a.nbytes)
+    ent = _PINNED.get(key)
+    if ent is None:
+        return
+    ent[1] -= 1
+    if ent[1] <= 0:
+        _ffi.lib().oevae_host_unregister(a.ctypes.data)
+        del _PINNED[key]
+
+
+def _host_x(a):
+    """Constituent rows as the device path takes them: float16 stays float16 (the reference's on-disk dtype, tools/merging.py:31 --
+    half the upload; widened on the device), everything else becomes contiguous float32 (Keras casts inputs to float32)."""
+    a = np.asarray(a)
+    return np.ascontiguousarray(a) if a.dtype == np.float16 else np.ascontiguousarray(a, np.float32)
+
+
+def _scaler_dev(scaler, D, device):
+    """(center, scale) device float64 tensors of an affine scaler (utils.py:406-417), (None, None) without a scaler."""
+    if scaler is None:
+        return None, None
+    from .utils import _scaler_affine
+    aff = _scaler_affine(scaler, D)
+    if aff is None:
+        raise NotImplementedError('train_model(scaler=...) takes affine scalers (MaxAbs / Robust); apply %s with utils.apply_scaler first' % type(scaler).__name__)
+    c, sc = aff
+    if len(sc) != D or (c is not None and len(c) != D):
+        raise ValueError('scaler was fitted on %d columns, the model input has %d' % (len(sc), D))
+    return (None if c is None else torch.as_tensor(c).to(device)), torch.as_tensor(sc).to(device)
+
+
+def _upload(dev, a, center=None, scale=None, stream=None):
+    """One host block -> float32 device tensor, widening float16 / applying the affine scaler on the device."""
+    t = torch.from_numpy(a).to(dev.device, non_blocking=True)
+    if a.dtype == np.float16 or (scale is not None and a.ndim == 2):
+        out = torch.empty(t.shape, dtype=torch.float32, device=dev.device)
+        if t.numel():
+            lib, st = _ffi.lib(), torch.cuda.current_stream().cuda_stream
+            if a.dtype == np.float16:
+                _ffi.check(lib.oevae_ingest_f16(_ffi.ptr(t), _ffi.ptr(out), t.shape[0], t.shape[1], _ffi.ptr(center), _ffi.ptr(scale), dev.device_index, st))
+            else:
+                _ffi.check(lib.oevae_affine(_ffi.ptr(t), _ffi.ptr(out), t.shape[0], t.shape[1], _ffi.ptr(center), _ffi.ptr(scale), dev.device_index, st))
+        return out
+    return t
+
+
+class _BatchStager:
+    """Host (NumPy) load -> device batches for the paths that step from Python (validation chunks; training on the all-reduce
+    fallback).  The arrays of a load are page-locked in place once and every batch is copied host->device on a side stream, two
+    batches ahead of the compute stream; float16 rows are widened (and an affine scaler applied) on the device."""
+
+    def __init__(self, arrays, batch_size, dev, shard=(0, 1), center=None, scale=None):
+        self.dev = dev
+        self.device = dev.device
+        self.arrays = [None if a is None else (_host_x(a) if np.ndim(a) == 2 else np.ascontiguousarray(a, np.float32)) for a in arrays]
         self.n = len(self.arrays[0])
         self.batch_size = int(batch_size)
         self.n_batches = int(np.ceil(self.n / self.batch_size))
         self.rank, self.world = shard
-        self.copy_stream = torch.cuda.Stream(device=device)
-        self._registered = []
-        for a in self.arrays:
-            if a.nbytes and _ffi.lib().oevae_host_register(a.ctypes.data, a.nbytes) == 0:
-                self._registered.append(a)
+        self.center, self.scale = center, scale
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        for a in self.arrays: _pin(a)
         self.h2d_bytes = 0
 
     def bounds(self, b):
         lo, hi = b * self.batch_size, min((b + 1) * self.batch_size, self.n)
-        if self.world > 1:                      # contiguous shard of the global batch (SURVEY 8(e))
+        if self.world > 1:                      # contiguous shard of the global batch (SURVEY 8(e)); may be empty in a short last batch
             n = hi - lo
             s0, s1 = lo + (n * self.rank) // self.world, lo + (n * (self.rank + 1)) // self.world
             return s0, s1, lo
@@ -222,11 +284,9 @@ class _BatchStager:
         out = []
         with torch.cuda.stream(self.copy_stream):
             for a in self.arrays:
-                src = torch.from_numpy(a[lo:hi])
-                dst = torch.empty(src.shape, dtype=torch.float32, device=self.device)
-                dst.copy_(src, non_blocking=True)
-                self.h2d_bytes += src.numel() * 4
-                out.append(dst)
+                if a is None: out.append(None); continue
+                out.append(_upload(self.dev, a[lo:hi], self.center, self.scale))
+                self.h2d_bytes += a[lo:hi].nbytes
             ev = torch.cuda.Event(); ev.record(self.copy_stream)
         return out, ev
 
@@ -238,26 +298,118 @@ class _BatchStager:
                 pending.append(self._issue(b + 2))
             torch.cuda.current_stream().wait_event(ev)
             for t in tensors:
-                t.record_stream(torch.cuda.current_stream())
+                if t is not None: t.record_stream(torch.cuda.current_stream())
             yield b, tensors
 
     def close(self):
         torch.cuda.synchronize(self.device)
-        for a in self._registered:
-            _ffi.lib().oevae_host_unregister(a.ctypes.data)
-        self._registered = []
+        for a in self.arrays: _unpin(a)
+        self.arrays = []
+
+
+class _TrainLoad:
+    """One (bkg, OoD) load of train_model on the native batch loop (oevae_train_batches_host): page-locked host arrays, optional
+    device-resident float32 copy that later epochs step on without another upload (generator OFF: the reference also loads once,
+    models.py:139-148)."""
+
+    def __init__(self, dev, bkg, ood, batch_size, shard, center, scale, keep_resident, noise_row0=0):
+        self.dev = dev
+        self.noise_row0 = int(noise_row0)
+        self.X, self.w = _host_x(_pick_X(bkg)), np.ascontiguousarray(bkg['weights'], np.float32)
+        self.Xo = self.wo = None
+        if ood is not None:
+            self.Xo, self.wo = _host_x(_pick_X(ood)), np.ascontiguousarray(ood['weights'], np.float32)
+            if self.Xo.dtype != self.X.dtype: self.Xo = self.Xo.astype(self.X.dtype)
+            if len(self.Xo) != len(self.X): raise ValueError('OoD sample is not row-aligned with the background sample (utils.py:227)')
+        self.n = len(self.X)
+        self.batch_size = int(batch_size)
+        self.n_batches = int(np.ceil(self.n / self.batch_size))
+        self.rank, self.world = shard
+        self.center, self.scale = center, scale
+        for a in (self.X, self.w, self.Xo, self.wo): _pin(a)
+        self.res = None
+        D = self.X.shape[1]
+        self.stride = -(-self.batch_size // self.world) + 1
+        if keep_resident:
+            rows = self.stride * self.n_batches
+            need = rows * (D + 1) * 4 * (2 if ood is not None else 1)
+            free, _ = torch.cuda.mem_get_info(dev.device)
+            if need < 0.6 * free:
+                mk = lambda *sh: torch.empty(sh, dtype=torch.float32, device=dev.device)
+                self.res = [mk(rows, D), mk(rows), mk(rows, D) if ood is not None else None, mk(rows) if ood is not None else None]
+        self.filled = False                                  # resident copy complete (after the first pass over the load)
+        self.h2d_bytes = 0
+
+    def shard_rows(self, b):
+        lo, hi = b * self.batch_size, min((b + 1) * self.batch_size, self.n)
+        n = hi - lo
+        return (n * self.rank) // self.world, (n * (self.rank + 1)) // self.world
+
+    def run(self, first, count, lr, beta, lamb, margin, sums, peer, trace=None):
+        """Steps batches [first, first + count): native host loop (first epoch) or the resident device batches (later epochs)."""
+        dev = self.dev
+        if self.filled:
+            for b in range(first, first + count):
+                s0, s1 = self.shard_rows(b)
+                o = b * self.stride
+                x, w = self.res[0][o:o + s1 - s0], self.res[1][o:o + s1 - s0]
+                xo = wo = None
+                if self.res[2] is not None: xo, wo = self.res[2][o:o + s1 - s0], self.res[3][o:o + s1 - s0]
+                dev.set_noise_offset(self.noise_row0 + s0)
+                if peer:
+                    dev.train_step_dp(x, w, xo, wo, None, lr, beta, lamb, margin, None, sums)
+                else:
+                    dev.train_step(x, w, xo, wo, None, lr, beta, lamb, margin, None, sums)
+                if trace is not None: trace[b - first].copy_(sums, non_blocking=True)
+            dev.set_noise_offset(0)
+            return
+        L = _ffi.HostLoad()
+        L.x_host, L.w_host = self.X.ctypes.data, self.w.ctypes.data
+        L.xo_host = None if self.Xo is None else self.Xo.ctypes.data
+        L.wo_host = None if self.wo is None else self.wo.ctypes.data
+        L.x_dtype = 1 if self.X.dtype == np.float16 else 0
+        L.update = 1 if peer else 0
+        L.n_rows, L.batch_size, L.first_batch, L.n_batches = self.n, self.batch_size, first, count
+        L.rank, L.world, L.noise_row0 = self.rank, self.world, self.noise_row0
+        L.center, L.scale = _ffi.ptr(self.center), _ffi.ptr(self.scale)
+        if self.res is not None:
+            L.x_resident, L.w_resident = _ffi.ptr(self.res[0]), _ffi.ptr(self.res[1])
+            L.xo_resident, L.wo_resident = _ffi.ptr(self.res[2]), _ffi.ptr(self.res[3])
+            L.resident_stride = self.stride
+        L.lr, L.beta, L.lamb, L.margin = lr, beta, lamb, margin
+        L.sums_acc = _ffi.ptr(sums)
+        L.sums_trace_host = None if trace is None else trace.data_ptr()
+        self.h2d_bytes += dev.train_batches_host(L)
+        if self.res is not None and first + count >= self.n_batches: self.filled = True
+
+    def close(self):
+        torch.cuda.synchronize(self.dev.device)
+        for a in (self.X, self.w, self.Xo, self.wo): _unpin(a)
+        self.res = None
 
 
 # ------------------------------------------------------------------------------------------------ train_model
 def train_model(vae, train_sample, valid_sample, OE_type='KLD', n_epochs=1, batch_size=5000,
                 beta=0, lamb=0, margin=0, lr=1e-3, hist_file=None, model_in=None, model_out=None,
-                patience=3, verbose=True):
-    """models.py:135-219.  Same control flow, history schema, print cadence and LR-patience logic; the batch
-    body (get_losses + tape.gradient + clip + Adam + metric updates, models.py:180-190) is one C-ABI call.
-    Under torchrun (WORLD_SIZE>1) every global batch is split contiguously across ranks and the flat
-    gradient is all-reduced with SUM before the update."""
+                patience=3, verbose=True, *, scaler=None, metrics_every=10, stats=None, sharded_input=False):
+    """models.py:135-219.  Same control flow, history schema, print cadence and LR-patience logic; the batch loop
+    (get_losses + tape.gradient + clip + Adam + metric updates, models.py:177-190) runs inside the library: one C-ABI call
+    per group of `metrics_every` batches copies the group's batches host->device two ahead of the compute stream and steps them.
+    Differences from the reference that do not change results:
+      * lamb == 0: the OoD arrays are neither uploaded nor evaluated (the reference multiplies their loss by 0, models.py:130);
+      * generator OFF (one load): the load is uploaded once and later epochs step on the device-resident copy;
+      * `scaler` (keyword, affine sklearn scaler): the samples are given UNSCALED -- float16 as the reference's files store them
+        (tools/merging.py:31) or float32 -- and apply_scaler (utils.py:406-430) runs on the device per batch, bit-identical to the
+        host transform and half the upload for float16;
+      * `metrics_every` (keyword, default the reference's 10): cadence of the running-mean read-back / print (models.py:191).
+    Under torchrun (WORLD_SIZE>1) every global batch is split contiguously across ranks and the gradients are SUMMED before the
+    update: inside the update kernel over NVLink peer memory, else by an all-reduce of the flat gradient.
+    `sharded_input` (keyword): under torchrun every rank passes ITS OWN part of the sample (equal sizes on all ranks) instead of
+    the whole sample: a global batch is then `world x batch_size` jets, `batch_size` from each rank's host (jet-ID's
+    `batch_size * n_gpus`, classifier.py:137).  `stats` (keyword): optional dict that receives {'h2d_bytes', 'steps'}."""
     dev = vae.dev
     dev.set_oe_type(OE_type)
+    dev.reset_opt()                                           # models.py:138: a new Adam (m = v = 0, t = 0) per train_model call
     rank, world = _dist.rank_world()
     out = sys.stdout if (verbose and rank == 0) else open(os.devnull, 'w')
     optimizer = Adam(learning_rate=lr)
@@ -281,73 +433,135 @@ def train_model(vae, train_sample, valid_sample, OE_type='KLD', n_epochs=1, batc
     # n_gpus > 1: the update kernel exchanges the per-rank gradient sums over NVLink peer memory (one node, NCCL backend);
     # otherwise (gloo test boxes, nets too large for a co-resident launch) SUM all-reduce of the flat gradient
     peer = world > 1 and torch.distributed.get_backend() == 'nccl' and (getattr(dev, 'dp', False) or dev.dp_connect())
-    total_batches = 0; count = 0
+    native = (world == 1 or peer) and dev.noise != 'external'
+    own = bool(sharded_input) and world > 1                   # every rank steps through its own rows; sums / counts are global
+    shard = (0, 1) if own else (rank, world)
+    gmul = world if own else 1
+    use_ood = lamb != 0
+    center, scale = _scaler_dev(scaler, vae.input_dim, dev.device)
+    metrics_every = max(1, int(metrics_every))
+    trace = torch.zeros((metrics_every, 4), dtype=torch.float64).pin_memory()   # per-step copy of the running sums (models.py:187-190)
+    total_batches = 0; count = 0; n_steps = 0; h2d = 0
     beta, lamb, margin = float(beta), float(lamb), float(margin)
-    for epoch in range(n_epochs):
-        sum_batches = 0; n_seen = 0; start_time = time.time()
-        print('\nEpoch %d/%d:' % (epoch + 1, n_epochs), file=out)
-        sums.zero_(); vsum.zero_()
-        losses = {}
-        for train_idx in range(len(train_sample)):
-            bkg, ood = train_sample[train_idx]
-            stager = _BatchStager([_pick_X(bkg), bkg['weights'], _pick_X(ood), ood['weights']], batch_size, dev.device, (rank, world))
-            if epoch == 0: total_batches += stager.n_batches
-            try:
-                for batch_idx, (x, w, xo, wo) in stager:
-                    sum_batches += 1
-                    lo, hi, glo = stager.bounds(batch_idx)
-                    if world == 1:
-                        dev.train_step(x, w, xo, wo, None, optimizer.learning_rate, beta, lamb, margin, None, sums)
-                    elif peer:
-                        dev.set_noise_offset(lo - glo)
-                        dev.train_step_dp(x, w, xo, wo, None, optimizer.learning_rate, beta, lamb, margin, None, sums)
-                    else:
-                        dev.set_noise_offset(lo - glo)
-                        dev.loss_and_grad(x, w, xo, wo, None, beta, lamb, margin, None, sums, grad)
-                        _dist.all_reduce_sum(grad)
-                        dev.apply_update(grad, optimizer.learning_rate)
-                    n_seen += min((batch_idx + 1) * stager.batch_size, stager.n) - batch_idx * stager.batch_size
-                    last = batch_idx + 1 == stager.n_batches
-                    if sum_batches % 10 == 0 or last:                    # models.py:191-200
-                        s = sums.clone()
-                        if world > 1: _dist.all_reduce_sum(s)
-                        mean = (s / n_seen).cpu().numpy()
-                        losses = {'MSE': mean[0]}
-                        if beta != 0: losses['KLD'] = mean[1]
-                        if lamb != 0: losses['OE'] = mean[2]
-                        losses['Train loss'] = mean[3]
-                        print('Batch %4d/%d: mean losses' % (sum_batches, total_batches), end='  -->  ', flush=True, file=out)
-                        for key, val in losses.items():
-                            cond = train_idx + 1 != train_len or not last
-                            end = '\r' if cond and key == 'Train loss' else '  '
-                            print(key + ' = ' + format(val, '4.3e'), end=end, flush=True, file=out)
-            finally:
-                stager.close()
-        n_valid = 0
-        for valid_data in valid_sample:                                      # models.py:201-211
-            bkg, ood = valid_data
-            stager = _BatchStager([_pick_X(bkg), bkg['weights'], _pick_X(ood), ood['weights']], int(1e6), dev.device, (rank, world))
-            try:
-                for batch_idx, (x, w, xo, wo) in stager:
-                    lo, hi, glo = stager.bounds(batch_idx)
-                    dev.set_noise_offset(lo - glo)
+    loads = {}                                                # generator OFF: the load (and its resident copy) lives across epochs
+    vcache = {}
+    try:
+        for epoch in range(n_epochs):
+            sum_batches = 0; n_seen = 0; start_time = time.time()
+            print('\nEpoch %d/%d:' % (epoch + 1, n_epochs), file=out)
+            sums.zero_(); vsum.zero_()
+            losses = {}
+
+            def report(last_of_load, last_load, trace_row=None):
+                if trace_row is not None and world == 1:                   # the step's sums already came back (per-step device->host copy)
+                    torch.cuda.current_stream().synchronize()
+                    mean = trace_row.numpy() / max(n_seen, 1)
+                else:
+                    s = sums.clone()
+                    if world > 1: _dist.all_reduce_sum(s)
+                    mean = (s / max(n_seen, 1)).cpu().numpy()
+                losses.clear(); losses['MSE'] = mean[0]
+                if beta != 0: losses['KLD'] = mean[1]
+                if lamb != 0: losses['OE'] = mean[2]
+                losses['Train loss'] = mean[3]
+                print('Batch %4d/%d: mean losses' % (sum_batches, total_batches), end='  -->  ', flush=True, file=out)
+                for key, val in losses.items():
+                    cond = (not last_load) or not last_of_load
+                    end = '\r' if cond and key == 'Train loss' else '  '
+                    print(key + ' = ' + format(val, '4.3e'), end=end, flush=True, file=out)
+
+            for train_idx in range(len(train_sample)):
+                last_load = train_idx + 1 == train_len
+                if native:
+                    ld = loads.get(train_idx)
+                    if ld is None:
+                        bkg, ood = train_sample[train_idx]
+                        ld = _TrainLoad(dev, bkg, ood if use_ood else None, batch_size, shard, center, scale,
+                                        keep_resident=(train_len == 1 and n_epochs > 1), noise_row0=rank * int(batch_size) if own else 0)
+                        if train_len == 1: loads[train_idx] = ld
+                    if epoch == 0: total_batches += ld.n_batches
+                    try:
+                        b = 0
+                        while b < ld.n_batches:
+                            cnt = min(metrics_every - sum_batches % metrics_every, ld.n_batches - b)
+                            ld.run(b, cnt, optimizer.learning_rate, beta, lamb, margin, sums, peer, trace)
+                            b += cnt; sum_batches += cnt; n_steps += cnt
+                            n_seen += gmul * (min(b * ld.batch_size, ld.n) - (b - cnt) * ld.batch_size)
+                            last = b == ld.n_batches
+                            if sum_batches % metrics_every == 0 or last:             # models.py:191-200
+                                report(last, last_load, trace[cnt - 1])
+                    finally:
+                        if train_len != 1: h2d += ld.h2d_bytes; ld.close()
+                    continue
+                # ---- stepping from Python: all-reduce fallback (gloo / nets too large for the peer-memory update) and EXTERNAL noise
+                bkg, ood = train_sample[train_idx]
+                arrays = [_pick_X(bkg), bkg['weights']] + ([_pick_X(ood), ood['weights']] if use_ood else [None, None])
+                stager = _BatchStager(arrays, batch_size, dev, shard, center, scale)
+                if epoch == 0: total_batches += stager.n_batches
+                try:
+                    for batch_idx, (x, w, xo, wo) in stager:
+                        sum_batches += 1; n_steps += 1
+                        lo, hi, glo = stager.bounds(batch_idx)
+                        dev.set_noise_offset(lo - glo + (rank * int(batch_size) if own else 0))
+                        if world == 1:
+                            dev.train_step(x, w, xo, wo, None, optimizer.learning_rate, beta, lamb, margin, None, sums)
+                        elif peer:
+                            dev.train_step_dp(x, w, xo, wo, None, optimizer.learning_rate, beta, lamb, margin, None, sums)
+                        else:
+                            dev.loss_and_grad(x, w, xo, wo, None, beta, lamb, margin, None, sums, grad)   # empty shard: zero gradient
+                            _dist.all_reduce_sum(grad)
+                            dev.apply_update(grad, optimizer.learning_rate)
+                        n_seen += gmul * (min((batch_idx + 1) * stager.batch_size, stager.n) - batch_idx * stager.batch_size)
+                        last = batch_idx + 1 == stager.n_batches
+                        if sum_batches % metrics_every == 0 or last:                 # models.py:191-200
+                            report(last, last_load)
+                finally:
+                    h2d += stager.h2d_bytes
+                    stager.close()
+            n_valid = 0
+            for vidx, valid_data in enumerate(valid_sample):                         # models.py:201-211
+                chunks = vcache.get(vidx)
+                if chunks is None:
+                    bkg, ood = valid_data
+                    arrays = [_pick_X(bkg), bkg['weights']] + ([_pick_X(ood), ood['weights']] if use_ood else [None, None])
+                    stager = _BatchStager(arrays, int(1e6), dev, shard, center, scale)
+                    chunks = []
+                    try:
+                        for batch_idx, ts in stager:
+                            lo, hi, glo = stager.bounds(batch_idx)
+                            chunks.append((lo - glo, ts))
+                        nv = stager.n
+                    finally:
+                        h2d += stager.h2d_bytes
+                        stager.close()
+                    chunks = (nv, chunks)
+                    free, _ = torch.cuda.mem_get_info(dev.device)
+                    if valid_len == 1 and n_epochs > 1 and free > (8 << 30): vcache[vidx] = chunks
+                nv, parts = chunks
+                for off, (x, w, xo, wo) in parts:
+                    if x.shape[0] == 0: continue
+                    dev.set_noise_offset(off)
                     pj = torch.empty((4, x.shape[0]), dtype=torch.float32, device=dev.device)
                     dev.eval_losses(x, w, xo, wo, None, beta, lamb, margin, pj, vsum)
-                n_valid += stager.n
-            finally:
-                stager.close()
-        dev.set_noise_offset(0)
-        if world > 1: _dist.all_reduce_sum(vsum)
-        losses['Valid loss'] = float(vsum[3].item() / max(n_valid, 1))
-        print('Valid loss = ' + format(losses['Valid loss'], '4.3e'), end='  ', flush=True, file=out)
-        print('(', '\b' + format(time.time() - start_time, '.1f'), '\b' + 's)', file=out)
-        for key in history: history[key] += [float(losses[key]) if key in losses else 0]
-        if hist_file is not None and rank == 0: pickle.dump(history, open(hist_file, 'wb'))
-        if epoch > 0:
-            optimizer, count = model_checkpoint(vae, optimizer, history, model_out, count, patience=patience, _out=out, _save=(rank == 0))
-            if count is None: break
-        elif n_epochs == 1 and model_out and rank == 0:
-            vae.save_weights(model_out)                                      # reference never saves here
+                n_valid += gmul * nv
+            dev.set_noise_offset(0)
+            if world > 1: _dist.all_reduce_sum(vsum)
+            losses['Valid loss'] = float(vsum[3].item() / max(n_valid, 1))
+            print('Valid loss = ' + format(losses['Valid loss'], '4.3e'), end='  ', flush=True, file=out)
+            print('(', '\b' + format(time.time() - start_time, '.1f'), '\b' + 's)', file=out)
+            for key in history: history[key] += [float(losses[key]) if key in losses else 0]
+            if hist_file is not None and rank == 0: pickle.dump(history, open(hist_file, 'wb'))
+            if epoch > 0:
+                optimizer, count = model_checkpoint(vae, optimizer, history, model_out, count, patience=patience, _out=out, _save=(rank == 0))
+                if count is None: break
+            elif n_epochs == 1 and model_out and rank == 0:
+                vae.save_weights(model_out)                                      # reference never saves here
+    finally:
+        for ld in loads.values():
+            h2d += ld.h2d_bytes
+            ld.close()
+        if stats is not None:
+            stats['h2d_bytes'] = h2d; stats['steps'] = n_steps
     return history
 
 

@@ -192,6 +192,36 @@ OEVAE_API int oevae_hist(const float* var, const float* w, const float* jzw, con
                int64_t N, float cut, const double* edges, int32_t n_edges,
                int64_t* counts, double* wsums, int32_t device, void* stream);
 
+/* ---- train_model's batch loop over one HOST-resident load (models.py:172-190), one call per group of batches ----------------
+ * Replaces the implicit per-step host->device copies of models.py:180-182: batches [first_batch, first_batch + n_batches) of
+ * `batch_size` rows are copied host->device on an internal copy stream, two batches ahead of the compute stream, and stepped with
+ * oevae_train_step (update 0) or oevae_train_step_dp (update 1; this rank's contiguous shard [n rank / world, n (rank+1) / world)
+ * of every global batch, an empty shard joins the exchange).  Host arrays should be page-locked (oevae_host_register).
+ *   x_dtype 1: x_host / xo_host hold float16 rows as the reference's files do (tools/merging.py:31); they are widened and scaled on
+ *              the device (oevae_ingest_f16).  x_dtype 0 with a scaler: oevae_affine on the device.  center / scale: DEVICE double[D].
+ *   x_resident (+ w_resident, xo_resident, wo_resident): nullable DEVICE buffers that receive the float32 batches, batch b at row
+ *              b * resident_stride (stride >= the largest shard): the load then stays on the device and later epochs step on it
+ *              without another copy.  Null: a three-slot ring inside the handle.
+ *   sums_acc   DEVICE double[4] (as oevae_train_step); sums_trace_host: nullable page-locked double[n_batches][4] that receives
+ *              sums_acc after every step (device->host copy in stream order): the per-step metric read of models.py:187-190. */
+typedef struct {
+    const void*  x_host;  const float* w_host;
+    const void*  xo_host; const float* wo_host;       /* OoD arrays: both null => no OE term */
+    int32_t      x_dtype;                             /* 0 float32, 1 float16 */
+    int32_t      update;                              /* 0 single rank, 1 peer-memory data parallel */
+    int64_t      n_rows, batch_size, first_batch, n_batches;
+    int32_t      rank, world;                         /* row shard of every batch: [n rank / world, n (rank+1) / world); world 1 = all rows */
+    int64_t      noise_row0;                          /* added to the Philox row counter (a rank that feeds its own pre-sharded load
+                                                         passes rank * batch_size so that ranks do not share noise) */
+    const double* center; const double* scale;
+    float*       x_resident; float* w_resident; float* xo_resident; float* wo_resident;
+    int64_t      resident_stride;
+    float        lr, beta, lamb, margin;
+    double*      sums_acc; double* sums_trace_host;
+    int64_t      h2d_bytes;                           /* out: bytes copied host->device by this call */
+} oevae_host_load;
+OEVAE_API int oevae_train_batches_host(oevae_t h, oevae_host_load* load, void* stream);
+
 /* _BatchStager (host loads -> device batches, replacing the implicit per-step H2D of models.py:180): page-lock a
  * host array in place.  Returns 0 when newly registered (release it with oevae_host_unregister), 1 when the range
  * was already page-locked (nothing to release), OEVAE_ECUDA otherwise; never leaves a CUDA error pending. */

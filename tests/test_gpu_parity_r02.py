@@ -1,0 +1,202 @@
+"""Parity of the paths bench.py times, at the shapes BASELINE.json names (round-2 gates):
+  * clip_values paths (models.py:243-246) through the FUSED bf16x3 training kernels (plain, paired OE-KLD, two-pass OE-MSE)
+  * 200-step loss curves at the cfg-2 and cfg-3 shapes (B = 5000, D = 400, FC [80,40,20,10]) against the float64 oracle, rel 1e-3
+  * KLD / JSD anomaly scores against the float64 oracle END TO END, next to the float32 oracle's own error (the reference computes
+    them in float32 and has the same cancellation): gate on device error <= 4 x float32-oracle error
+  * cfg-5's exact layer list [1024, 512, 256, 64] (layered tcgen05 path, split-K dW over 16 slots): losses and gradient
+Every comparison lands in gpurun_out/r02_parity.jsonl through conftest.record_parity."""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip('torch')
+pytestmark = pytest.mark.gpu
+
+from conftest import record_parity
+from oracle import vae_numpy as V, scoring as S
+from test_gpu_tensorcore import _close, _close_grad, _close_losses
+
+
+def _dev(FC, D, oe='KLD', precision='bf16x3', noise='external', seed=0):
+    from atlas_vae_b200.engine import DeviceVAE
+    return DeviceVAE(FC, D, oe, precision, noise, seed)
+
+
+def _kernel_names(fn):
+    from atlas_vae_b200 import _ffi
+    _ffi.profile(True)
+    fn()
+    torch.cuda.synchronize()
+    names = [r[0] for r in _ffi.profile_report()]
+    _ffi.profile(False)
+    return names
+
+
+# ------------------------------------------------------------------------------------------------ (a) clip paths, fused kernels
+def _clip_fixture(FC, D, B, seed=0):
+    flat = V.init_params(FC, D, seed).astype(np.float32)
+    lay, _ = V.param_layout(FC, D)
+    off = {n: (o, s) for n, s, o in lay}
+    L = FC[-1]
+    lvb = off['log_var.bias'][0]
+    flat[lvb:lvb + 4] = [200., -200., 30., 0.]                 # exp overflow (-> non-finite -> 0) / underflow / beyond the clip / regular
+    ob = off['out.bias'][0]
+    flat[ob] = 3e6; flat[ob + 1] = -2.5e6                       # reconstructions beyond +-1e6: clipped forward, zero gradient
+    rng = np.random.default_rng(seed)
+    X = rng.normal(size=(B, D)).astype(np.float32); Xo = rng.normal(0.2, 1.1, (B, D)).astype(np.float32)
+    w = rng.uniform(0.5, 1.5, B).astype(np.float32); wo = rng.uniform(0.5, 1.5, B).astype(np.float32)
+    eps = rng.normal(size=(B, L)).astype(np.float32)
+    return flat, X, Xo, w, wo, eps
+
+
+@pytest.mark.parametrize('oe,ood,kernel', [('KLD', False, 'fused_train'), ('MSE', False, 'fused_train'), ('KLD', True, 'fused_oe_pair_train'),
+                                           ('MSE', True, 'fused_oe_train'), ('MAE-margin', True, 'fused_oe_train')])
+@pytest.mark.parametrize('FC,D,B', [([8, 4], 6, 16), ([80, 40, 20, 10], 400, 333)])
+def test_fused_clip_paths(FC, D, B, oe, ood, kernel):
+    """lv = +-200, |y_raw| > 1e6: forward clip and the zero-gradient masks of SURVEY appendix A on the bench path (fused3_kernel<0,0>,
+    <0,1>, <0,2>), against the float32 oracle (in float64 exp(100) is finite, the reference computes in float32)."""
+    flat, X, Xo, w, wo, eps = _clip_fixture(FC, D, B)
+    dev = _dev(FC, D, oe); dev.set_params(flat)
+    pj = torch.empty((4, B), device='cuda')
+    a = (X, w, Xo, wo) if ood else (X, w, None, None)
+    beta, lamb, margin = 1.0, (1.3 if ood else 0.0), (0.5 if ood else 0.0)
+    holder = {}
+    names = _kernel_names(lambda: holder.setdefault('g', dev.loss_and_grad(a[0], a[1], a[2], a[3], eps, beta, lamb, margin, pj)))
+    assert kernel in names and not any(n.startswith('gemm') for n in names), names          # the fused kernel ran, not the layered path
+    out, gref = V.losses_and_grad(flat, FC, D, X, w, Xo if ood else None, wo if ood else None, eps, OE_type=oe, beta=beta, lamb=lamb, margin=margin, dtype=np.float32)
+    got = pj.cpu().numpy()
+    assert np.isfinite(got).all()
+    _close_losses(got, np.stack(out), 1e-3, 1e-5, 'clip-path losses (%s%s)' % (oe, ', OoD' if ood else ''))
+    _close_grad(holder['g'].cpu().numpy(), gref, 1e-3, 1e-4, 'clip-path gradient (%s%s)' % (oe, ', OoD' if ood else ''), outliers=5e-3)
+    # rows the masks must zero: the output-bias entries whose reconstruction is clipped for every jet
+    lay, _ = V.param_layout(FC, D)
+    ob = {n: o for n, s, o in lay}['out.bias']
+    g = holder['g'].cpu().numpy()
+    assert g[ob] == 0 and g[ob + 1] == 0 and gref[ob] == 0
+
+
+def test_fused_update_sanitises_gradient():
+    """NaN / inf / |g| > 1e6 gradient entries through the fused path's update kernel (adam_img_kernel): models.py:185."""
+    FC, D = [80, 40, 20, 10], 400
+    flat = V.init_params(FC, D, 0)
+    dev = _dev(FC, D); dev.set_params(flat)
+    gbad = torch.zeros(dev.n_params, device='cuda'); gbad[0] = float('nan'); gbad[1] = float('inf'); gbad[2] = 5e6; gbad[3] = -2.; gbad[4] = float('-inf')
+    dev.apply_update(gbad, 1e-3)
+    th = dev.get_params()
+    th_ref, _, _ = V.adam_step(flat.astype(np.float64), np.zeros(len(flat)), np.zeros(len(flat)), gbad.cpu().numpy().astype(np.float64), 1, 1e-3)
+    _close(th, th_ref, 1e-6, 1e-7, 'fused adam on sanitised gradient')
+    assert th[0] == flat[0] and th[1] == flat[1] and th[4] == flat[4]
+    # and the refreshed bf16 image is the one the next forward uses: losses after the update follow the oracle's updated parameters
+    rng = np.random.default_rng(1)
+    X = rng.normal(0, 0.5, (200, D)).astype(np.float32); w = np.ones(200, np.float32); eps = rng.normal(size=(200, 10)).astype(np.float32)
+    pj = dev.eval_losses(X, w, None, None, eps, 1.0, 0., 0.)
+    out, _ = V.losses_and_grad(th_ref.astype(np.float32), FC, D, X, w, None, None, eps, OE_type='KLD', beta=1.0, want_grad=False)
+    _close(pj.cpu().numpy(), np.stack(out), 1e-3, 1e-6, 'losses after the sanitised update')
+
+
+# ------------------------------------------------------------------------------------------------ (b) 200-step loss curves
+def _jets_like(rng, B, D):
+    X = rng.normal(0, 0.25, (B, D)).astype(np.float32)
+    n_live = rng.integers(20, 70, B)
+    X *= (np.arange(D)[None, :] < 4 * n_live[:, None])                      # zero-padded constituents
+    return X
+
+
+@pytest.mark.parametrize('cfg', ['cfg2', 'cfg3'])
+def test_200_step_loss_curve(cfg):
+    """200-step loss curve at the cfg-2 shape (FC [80,40,20,10], D = 400, B = 5000, fixed eps) within rel 1e-3 of the
+    float64 oracle's; cfg3 = the same with the paired OoD batch (OE_type KLD, beta, lambda, margin != 0)."""
+    FC, D, B, steps = [80, 40, 20, 10], 400, 5000, 200
+    rng = np.random.default_rng(2024)
+    flat = V.init_params(FC, D, 0)
+    X, Xo = _jets_like(rng, B, D), (_jets_like(rng, B, D) * 1.3).astype(np.float32)
+    w = np.ones(B, np.float32); wo = rng.uniform(0.5, 1.5, B).astype(np.float32)
+    eps = rng.normal(size=(B, FC[-1])).astype(np.float32)
+    ood = cfg == 'cfg3'
+    beta, lamb, margin = 1.0, (2.0 if ood else 0.0), (0.5 if ood else 0.0)
+    dev = _dev(FC, D); dev.set_params(flat)
+    tr = V.Trainer(flat, FC, D, 'KLD')
+    d = lambda t: None if t is None else torch.as_tensor(t).cuda()
+    Xd, wd, Xod, wod, ed = d(X), d(w), d(Xo if ood else None), d(wo if ood else None), d(eps)
+    curve, ref = [], []
+    sums = torch.zeros(4, dtype=torch.float64, device='cuda')
+    for s in range(steps):
+        sums.zero_()
+        dev.train_step(Xd, wd, Xod, wod, ed, 1e-3, beta, lamb, margin, None, sums)
+        curve.append((sums / B).cpu().numpy())
+        o = tr.step(X, w, Xo if ood else None, wo if ood else None, eps, lr=1e-3, beta=beta, lamb=lamb, margin=margin)
+        ref.append([float(np.mean(q)) for q in o])
+    curve, ref = np.array(curve), np.array(ref)
+    assert ref[-1, 3] < 0.9 * ref[0, 3]                                      # the curve actually moves
+    scale = np.abs(ref[:, 3]).max()
+    for col, nme in enumerate(('rec', 'kld', 'oe', 'total')):
+        if col == 2 and not ood: continue
+        # the OE column is a hinge of a difference of two KLDs: its floor scales with the losses that are subtracted
+        _close(curve[:, col], ref[:, col], 1e-3, 1e-6 + (1e-3 * scale if col == 2 else 0), '200-step %s curve (%s)' % (nme, cfg))
+    th = dev.get_params()
+    moved = np.abs(tr.theta - flat.astype(np.float64))
+    err = np.abs(th - tr.theta)
+    frac = float(np.mean(err > 1e-3 * np.abs(tr.theta) + 0.02 * moved + 1e-6))
+    record_parity('theta after 200 Adam steps (%s): fraction outside rel 1e-3 + 2%% of the movement' % cfg, frac, 5e-3,
+                  {'median_err_over_movement': float(np.median(err / np.maximum(moved, 1e-12)))})
+    assert frac < 5e-3
+
+
+# ------------------------------------------------------------------------------------------------ (c) KLD / JSD end to end
+def test_kld_jsd_scores_end_to_end():
+    """Device KLD / JSD scores (utils.py:346-375 on the device's own forward pass) against the float64 oracle end to end, with the
+    float32 oracle's own error beside it: sum_d p log2(p/q) cancels, so the float32 reference is itself only ~1e-4-accurate; the
+    device must be within 4x of that (median and 99th percentile)."""
+    from atlas_vae_b200.engine import DeviceVAE
+    rng = np.random.default_rng(17)
+    FC, D, N = [80, 40, 20, 10], 400, 3000
+    flat = V.init_params(FC, D, 4)
+    flat = (flat + rng.normal(0, 0.01, flat.shape)).astype(np.float32)
+    X = np.abs(rng.normal(0, 0.3, (N, D))).astype(np.float32) + 0.02          # positive inputs: KLD / JSD of distributions
+    X[:, 300:] = 0
+    eps = rng.normal(size=(1, N, 10)).astype(np.float32)
+    dev = DeviceVAE(FC, D, 'KLD', 'bf16x3', 'external', 0); dev.set_params(flat)
+    out = {k: v.cpu().numpy().astype(np.float64) for k, v in dev.score(X, 1, eps, metrics=('MSE', 'MAE', 'KLD', 'JSD', 'Latent')).items() if k != 'finite'}
+    x64 = S.predict(flat, FC, D, X, [eps[0]], np.float64).astype(np.float64)
+    r64 = S.score_metrics(X.astype(np.float64), x64, ('MSE', 'MAE', 'KLD', 'JSD'))
+    x32 = S.predict(flat, FC, D, X, [eps[0]], np.float32)
+    r32 = S.score_metrics(X, x32, ('MSE', 'MAE', 'KLD', 'JSD'))
+    for m in ('MSE', 'MAE'):
+        _close(out[m], r64[m], 1e-3, 1e-6, m + ' end to end')
+    for m in ('KLD', 'JSD'):
+        scale = np.abs(r64[m]).mean()
+        e_dev = np.abs(out[m] - r64[m]) / scale
+        e_f32 = np.abs(r32[m].astype(np.float64) - r64[m]) / scale
+        med_d, med_r, p99_d, p99_r = np.median(e_dev), np.median(e_f32), np.percentile(e_dev, 99), np.percentile(e_f32, 99)
+        rel_jet = np.abs(out[m] - r64[m]) / np.maximum(np.abs(r64[m]), 1e-30)
+        record_parity(m + ' end to end vs float64 oracle (error / mean |score|): device median', med_d, 4 * med_r + 1e-6,
+                      {'device_p99': float(p99_d), 'device_max': float(e_dev.max()), 'f32_oracle_median': float(med_r), 'f32_oracle_p99': float(p99_r),
+                       'f32_oracle_max': float(e_f32.max()), 'device_per_jet_rel_median': float(np.median(rel_jet)), 'device_per_jet_rel_max': float(rel_jet.max())})
+        print('%s: device err median %.2e p99 %.2e max %.2e | float32 oracle median %.2e p99 %.2e max %.2e (units of mean |score| = %.3e)'
+              % (m, med_d, p99_d, e_dev.max(), med_r, p99_r, e_f32.max(), scale))
+        assert med_d <= 4 * med_r + 1e-6 and p99_d <= 4 * p99_r + 1e-5, m
+        assert np.median(rel_jet) <= 1e-3, m                                   # north_star: per-jet scores within rel 1e-3 (typical jet)
+
+
+# ------------------------------------------------------------------------------------------------ (d) cfg-5 exact shape
+@pytest.mark.parametrize('precision', ['bf16x3'])
+def test_cfg5_shape_losses_and_gradient(precision):
+    """BASELINE config 5's layer list [1024, 512, 256, 64] at D = 400 (B = 4096): multi-tile N, split-K dW over 16 slots."""
+    FC, D, B = [1024, 512, 256, 64], 400, 4096
+    rng = np.random.default_rng(55)
+    flat = V.init_params(FC, D, 2)
+    X = _jets_like(rng, B, D); w = rng.uniform(0.5, 1.5, B).astype(np.float32)
+    eps = rng.normal(size=(B, FC[-1])).astype(np.float32)
+    dev = _dev(FC, D, 'KLD', precision); dev.set_params(flat)
+    pj = torch.empty((4, B), device='cuda')
+    grad = dev.loss_and_grad(X, w, None, None, eps, 0.7, 0., 0., pj)
+    out, gref = V.losses_and_grad(flat, FC, D, X, w, None, None, eps, OE_type='KLD', beta=0.7)
+    _close(pj.cpu().numpy(), np.stack(out), 1e-3, 1e-6, 'cfg-5 per-jet losses')
+    _close_grad(grad.cpu().numpy(), gref, 1e-3, 1e-4, 'cfg-5 flat gradient')
+    # one Adam step on that gradient
+    dev.apply_update(grad, 1e-3)
+    th_ref, _, _ = V.adam_step(flat.astype(np.float64), np.zeros(len(flat)), np.zeros(len(flat)), gref, 1, 1e-3)
+    th = dev.get_params()
+    # Adam's first step is lr * sign(g) wherever |g| >> eps: entries whose gradient is ~0 may differ by up to lr
+    bad = np.abs(th - th_ref) > 1e-6 + 1e-4 * np.abs(th_ref)
+    record_parity('cfg-5 theta after one Adam step: fraction outside 1e-4', float(bad.mean()), 2e-2)
+    assert bad.mean() < 2e-2 and np.abs(th - th_ref).max() <= 2.1e-3

@@ -11,10 +11,7 @@ pytestmark = pytest.mark.gpu
 from oracle import vae_numpy as V, scoring as S, preprocess as PP
 
 
-def _close(a, b, rtol, atol, what=''):
-    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
-    err = np.abs(a - b) - (atol + rtol * np.abs(b))
-    assert err.max() <= 0, '%s: max abs err %.3e' % (what, np.abs(a - b).max())
+from test_gpu_tensorcore import _close          # records the achieved error in gpurun_out/r02_parity.jsonl
 
 
 def test_pair_metrics_match_reference(golden_dir):

@@ -25,8 +25,13 @@ def _dev(FC, D, oe, precision):
 
 
 def _close(a, b, rtol, atol, what=''):
+    from conftest import record_parity
     a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
     err = np.abs(a - b) - (atol + rtol * np.abs(b))
+    # achieved: the smallest rtol at which the check would still pass with this atol
+    with np.errstate(all='ignore'):
+        ach = np.nan_to_num(np.maximum(np.abs(a - b) - atol, 0) / np.maximum(np.abs(b), 1e-300), nan=0.0, posinf=1e300)
+    record_parity(what, float(ach.max()) if a.size else 0.0, rtol, {'atol': float(atol)})
     assert err.max() <= 0, '%s: max abs err %.3e (rel %.3e)' % (what, np.abs(a - b).max(), (np.abs(a - b) / (np.abs(b) + 1e-30)).max())
 
 
@@ -41,6 +46,8 @@ def _close_grad(g, gref, rtol, atol_frac, what='grad', outliers=2e-3):
     scale = max(np.abs(gref).max(), 1e-3)
     bad = np.abs(g - gref) > rtol * np.abs(gref) + atol_frac * scale
     l2 = np.linalg.norm(g - gref) / max(np.linalg.norm(gref), 1e-30)
+    from conftest import record_parity
+    record_parity(what + ' (rel L2)', l2, 20 * rtol, {'outlier_frac': float(bad.mean()), 'outlier_bound': float(outliers)})
     assert bad.mean() <= outliers and l2 <= 20 * rtol, '%s: %.2e of entries out of tolerance, rel L2 err %.2e, max abs err %.3e (scale %.3e)' % (
         what, bad.mean(), l2, np.abs(g - gref).max(), scale)
 

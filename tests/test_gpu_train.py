@@ -19,10 +19,7 @@ def _dev(FC, D, oe='KLD', noise='external', precision='fp32', seed=0):
     return DeviceVAE(FC, D, oe, precision, noise, seed)
 
 
-def _close(a, b, rtol, atol, what=''):
-    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
-    err = np.abs(a - b) - (atol + rtol * np.abs(b))
-    assert err.max() <= 0, '%s: max abs err %.3e (rel %.3e)' % (what, np.abs(a - b).max(), (np.abs(a - b) / (np.abs(b) + 1e-30)).max())
+from test_gpu_tensorcore import _close          # records the achieved error in gpurun_out/r02_parity.jsonl
 
 
 @pytest.mark.parametrize('oe', V.OE_TYPES)
