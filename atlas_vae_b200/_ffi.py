@@ -71,10 +71,16 @@ SIGNATURES = {
     'oevae_preprocess': (C.c_int, [_vp, _i32, _i64, _i32, _i32, _i32, _vp, _vp, _i32, _vp, _vp, _vp, _i32, _vp]),
     'oevae_affine': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _vp]),
     'oevae_ingest_f16': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _i32, _vp]),
+    'oevae_quantile_normal': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _i32, C.c_double, C.c_double, _i32, _vp]),
+    'oevae_power_yj': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp, _i32, _vp]),
     'oevae_pair_metrics': (C.c_int, [_vp, _vp, _i64, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp]),
     'oevae_minmax': (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp]),
     'oevae_loss_map': (C.c_int, [_vp, _i64, _i32, _i32, _vp]),
-    'oevae_hist': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _i32, _vp, _vp, _i32, _vp]),
+    'oevae_hist': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _i32, _f32, _i32, _vp, _vp, _i32, _vp]),
+    'oevae_wsum': (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp]),
+    'oevae_roc': (C.c_int, [_vp, _vp, _i32, _vp, _i64, _vp, _vp, _vp, C.POINTER(_i64), _i32, _vp]),
+    'oevae_roc_cuts': (C.c_int, [_vp, _vp, _vp, _i64, _vp, _i32, C.c_double, _vp, _i32, _vp]),
+    'oevae_roc_searchsorted': (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _vp, _i32, _vp]),
     'oevae_host_register': (C.c_int, [_vp, _i64]),
     'oevae_host_unregister': (C.c_int, [_vp]),
     'oevae_launch_count': (_i64, []),

@@ -64,10 +64,13 @@ struct Engine {
     int dp_rank = -1, dp_world = 0, dp_nblk = 0; unsigned int dp_seq = 0;
     float* dp_gsum = nullptr;     // [P] SUM over ranks of the last step's gradient, before clip_values (parity checks: oevae_dp_last_grad_host)
 
-    // host-load loop (oevae_train_batches_host): copy stream, per-slot events, staging ring (3 slots)
-    cudaStream_t hl_copy = nullptr; cudaEvent_t hl_ready[3] = {nullptr, nullptr, nullptr}, hl_freed[3] = {nullptr, nullptr, nullptr};
+    // host-load loop (oevae_train_batches_host): copy stream, per-slot events, staging ring of kHlSlots batches; the copies run
+    // kHlSlots - 1 batches ahead of the steps, so the copy engine stays busy while the host reads the running means (a sync every
+    // 10 batches, models.py:191)
+    static constexpr int kHlSlots = 6;
+    cudaStream_t hl_copy = nullptr; cudaEvent_t hl_ready[kHlSlots] = {}, hl_freed[kHlSlots] = {};
     unsigned char* hl_ring = nullptr; size_t hl_ring_bytes = 0;
-    bool hl_used[3] = {false, false, false};
+    bool hl_used[kHlSlots] = {};
     const void* hl_src = nullptr; long hl_copied_upto = 0;   // batches [.., hl_copied_upto) of the load at hl_src have their copies issued
 
     ~Engine();

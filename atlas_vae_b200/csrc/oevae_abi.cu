@@ -3,6 +3,8 @@
 #include "common.cuh"
 #include "ref_kernels.cuh"
 #include "prep_hist_kernels.cuh"
+#include "roc_kernels.cuh"
+#include "scaler_kernels.cuh"
 #include "umma_gemm.cuh"
 #include "umma_probe.cuh"
 #include "engine.h"
@@ -119,7 +121,7 @@ Engine::~Engine() {
     if (arena) cudaFree(arena);
     if (dp_gsum) cudaFree(dp_gsum);
     if (hl_ring) cudaFree(hl_ring);
-    for (int k = 0; k < 3; ++k) { if (hl_ready[k]) cudaEventDestroy(hl_ready[k]); if (hl_freed[k]) cudaEventDestroy(hl_freed[k]); }
+    for (int k = 0; k < kHlSlots; ++k) { if (hl_ready[k]) cudaEventDestroy(hl_ready[k]); if (hl_freed[k]) cudaEventDestroy(hl_freed[k]); }
     if (hl_copy) cudaStreamDestroy(hl_copy);
     if (fz) {
         if (fz->wimg) cudaFree(fz->wimg); if (fz->pos) cudaFree(fz->pos); if (fz->parts) cudaFree(fz->parts); if (fz->oe_pj) cudaFree(fz->oe_pj);
@@ -661,18 +663,19 @@ int Engine::train_batches_host(oevae_host_load& a, cudaStream_t s) {
     if (resident && a.resident_stride < cap - 1) return fail(OEVAE_EINVAL, "train_batches_host: resident_stride too small");
     if (!hl_copy) {
         CK(cudaStreamCreateWithFlags(&hl_copy, cudaStreamNonBlocking));
-        for (int k = 0; k < 3; ++k) { CK(cudaEventCreateWithFlags(&hl_ready[k], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&hl_freed[k], cudaEventDisableTiming)); }
+        for (int k = 0; k < kHlSlots; ++k) { CK(cudaEventCreateWithFlags(&hl_ready[k], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&hl_freed[k], cudaEventDisableTiming)); }
     }
     // ring slot: [x fp32][xo fp32][w][wo][x f16][xo f16]; with resident buffers only the f16 staging part is used
     const size_t xb = (size_t)cap * D * 4, wb = ((size_t)cap * 4 + 255) / 256 * 256, hb = ((size_t)cap * D * 2 + 255) / 256 * 256;
     const size_t slot_bytes = 2 * xb + 2 * wb + 2 * hb;
-    if (hl_ring_bytes < 3 * slot_bytes) {
+    constexpr int NS = kHlSlots, AHEAD = kHlSlots - 1;
+    if (hl_ring_bytes < NS * slot_bytes) {
         CK(cudaStreamSynchronize(s)); CK(cudaStreamSynchronize(hl_copy));
         if (hl_ring) cudaFree(hl_ring);
         hl_ring = nullptr; hl_ring_bytes = 0;
-        CK(cudaMalloc(&hl_ring, 3 * slot_bytes));
-        hl_ring_bytes = 3 * slot_bytes;
-        for (int k = 0; k < 3; ++k) hl_used[k] = false;
+        CK(cudaMalloc(&hl_ring, NS * slot_bytes));
+        hl_ring_bytes = NS * slot_bytes;
+        for (int k = 0; k < NS; ++k) hl_used[k] = false;
     }
     const size_t esz = f16 ? 2 : 4;
     const long nb_total = (a.n_rows + a.batch_size - 1) / a.batch_size;
@@ -685,7 +688,7 @@ int Engine::train_batches_host(oevae_host_load& a, cudaStream_t s) {
     };
     struct Bufs { float *x, *xo, *w, *wo; unsigned char *hx, *hxo; };
     auto bufs = [&](long b) {
-        unsigned char* base = hl_ring + (size_t)(b % 3) * slot_bytes;
+        unsigned char* base = hl_ring + (size_t)(b % NS) * slot_bytes;
         Bufs r;
         r.x = reinterpret_cast<float*>(base); r.xo = reinterpret_cast<float*>(base + xb);
         r.w = reinterpret_cast<float*>(base + 2 * xb); r.wo = reinterpret_cast<float*>(base + 2 * xb + wb);
@@ -697,7 +700,7 @@ int Engine::train_batches_host(oevae_host_load& a, cudaStream_t s) {
         return r;
     };
     auto issue_copy = [&](long b) -> int {
-        const int k = (int)(b % 3);
+        const int k = (int)(b % NS);
         const Shard sh = shard(b);
         const Bufs d = bufs(b);
         if (hl_used[k]) CK(cudaStreamWaitEvent(hl_copy, hl_freed[k], 0));          // the step that read slot k's previous content is done
@@ -717,16 +720,16 @@ int Engine::train_batches_host(oevae_host_load& a, cudaStream_t s) {
     };
     a.h2d_bytes = 0;
     const unsigned long long save_off = row_offset;
-    // copies run two batches ahead of the steps, also across calls: a caller that walks a load in groups (train_model reads the
+    // copies run AHEAD batches ahead of the steps, also across calls: a caller that walks a load in groups (train_model reads the
     // running means every 10 batches, models.py:191) finds the first batches of the next group already in flight
-    if (hl_src != a.x_host || hl_copied_upto < a.first_batch || hl_copied_upto > a.first_batch + 2) { hl_src = a.x_host; hl_copied_upto = a.first_batch; }
+    if (hl_src != a.x_host || hl_copied_upto < a.first_batch || hl_copied_upto > a.first_batch + AHEAD) { hl_src = a.x_host; hl_copied_upto = a.first_batch; }
     auto copy_upto = [&](long upto) -> int {                                       // issue the copies of batches [hl_copied_upto, upto)
         for (; hl_copied_upto < std::min<long>(upto, nb_total); ++hl_copied_upto) TRY(issue_copy(hl_copied_upto));
         return 0;
     };
-    TRY(copy_upto(a.first_batch + 2));
+    TRY(copy_upto(a.first_batch + AHEAD));
     for (long b = a.first_batch; b < b_end; ++b) {
-        const int k = (int)(b % 3);
+        const int k = (int)(b % NS);
         const Shard sh = shard(b);
         const Bufs d = bufs(b);
         CK(cudaStreamWaitEvent(s, hl_ready[k], 0));
@@ -749,7 +752,7 @@ int Engine::train_batches_host(oevae_host_load& a, cudaStream_t s) {
         CK(cudaEventRecord(hl_freed[k], s)); hl_used[k] = true;
         if (a.sums_trace_host && a.sums_acc)
             CK(cudaMemcpyAsync(a.sums_trace_host + 4 * (b - a.first_batch), a.sums_acc, 4 * sizeof(double), cudaMemcpyDeviceToHost, s));
-        TRY(copy_upto(b + 3));
+        TRY(copy_upto(b + 1 + AHEAD));
     }
     if (b_end >= nb_total) hl_src = nullptr;                                       // load finished: the next call starts afresh
     return 0;
@@ -885,6 +888,23 @@ int Engine::forward_encoder(const Pass& p, cudaStream_t s) {
     ++calls;
     return 0;
 }
+
+// ---- weighted ROC + cut thresholds (roc_kernels.cuh)
+namespace {
+struct RocWs {
+    unsigned char* base = nullptr; size_t off = 0, cap = 0;
+    template <typename T> T* take(size_t n) { off = (off + 255) / 256 * 256; T* p = reinterpret_cast<T*>(base + off); off += n * sizeof(T); return p; }
+};
+// exclusive scan of in[n] -> out[n] (may alias), total -> *total_dev; tiles: scratch of cdiv(n, kTile) + 1 entries
+int roc_scan(const uint32_t* in, uint32_t* out, long n, uint32_t* tiles, uint32_t* total_dev, cudaStream_t s) {
+    using namespace roc;
+    const unsigned nt = cdiv(n, kTile);
+    scan_tiles_kernel<<<nt, kThreads, 0, s>>>(in, n, tiles); LAUNCHED();
+    scan_block_kernel<<<1, 1024, 0, s>>>(tiles, nt, total_dev); LAUNCHED();
+    scan_apply_kernel<<<nt, kThreads, 0, s>>>(in, n, tiles, out); LAUNCHED();
+    return 0;
+}
+}  // namespace
 
 // ================================================================================================ C ABI
 #define H(h) if (!(h)) return OEVAE_EINVAL; Engine* e = reinterpret_cast<Engine*>(h); cudaSetDevice(e->cfg.device)
@@ -1097,6 +1117,27 @@ int oevae_ingest_f16(const void* raw_f16, float* x, int64_t N, int32_t D, const 
     return free_fail(cudaGetLastError(), "ingest_f16 launch");
 }
 
+int oevae_quantile_normal(const float* x, float* y, int64_t N, int32_t D, const double* quantiles_t, const double* references, int32_t n_q,
+                          double clip_min, double clip_max, int32_t device, void* stream) {
+    if (N == 0) return 0;
+    if (!x || !y || N < 0 || D <= 0 || !quantiles_t || !references || n_q < 2) { g_create_error = "quantile_normal: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    const long n = (long)N * D;
+    { PROF("quantile_normal", (cudaStream_t)stream); scal::quantile_normal_kernel<<<cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(x, y, n, D, quantiles_t, references, n_q, clip_min, clip_max); }
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "quantile_normal launch");
+}
+
+int oevae_power_yj(const float* x, float* y, int64_t N, int32_t D, const float* lambdas, const float* mean, const float* scale, int32_t device, void* stream) {
+    if (N == 0) return 0;
+    if (!x || !y || N < 0 || D <= 0 || !lambdas) { g_create_error = "power_yj: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    const long n = (long)N * D;
+    { PROF("power_yj", (cudaStream_t)stream); scal::power_yj_kernel<<<cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(x, y, n, D, lambdas, mean, scale); }
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "power_yj launch");
+}
+
 int oevae_pair_metrics(const float* P, const float* Q, int64_t N, int32_t D, float* mse, float* mae, float* mare, float* kld,
                        float* jsd, float* xs, int32_t device, void* stream) {
     if (N == 0) return 0;
@@ -1129,7 +1170,7 @@ int oevae_loss_map(float* v, int64_t N, int32_t branch, int32_t device, void* st
 }
 
 int oevae_hist(const float* var, const float* w, const float* jzw, const float* score, const uint8_t* keep, int64_t N, float cut,
-               const double* edges, int32_t n_edges, int64_t* counts, double* wsums, int32_t device, void* stream) {
+               const double* edges, int32_t n_edges, float wscale, int32_t density, int64_t* counts, double* wsums, int32_t device, void* stream) {
     if (n_edges < 2 || !edges || !counts || (w && !wsums) || (N > 0 && (!var || !jzw))) { g_create_error = "hist: bad arguments"; return OEVAE_EINVAL; }
     int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
     if (N <= 0) return 0;
@@ -1137,10 +1178,19 @@ int oevae_hist(const float* var, const float* w, const float* jzw, const float* 
     if (smem > 200 * 1024) { g_create_error = "hist: too many bins"; return OEVAE_EUNSUPPORTED; }
     if (smem > 48 * 1024) { rc = free_fail(cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "smem attr"); if (rc) return rc; }
     unsigned grid = std::min<unsigned>(cdiv(N, 256 * 8), 148 * 4);
-    { PROF("hist", (cudaStream_t)stream); hist_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(var, w, jzw, score, keep, N, cut, edges, n_edges,
+    { PROF("hist", (cudaStream_t)stream); hist_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(var, w, jzw, score, keep, N, cut, edges, n_edges, wscale, density,
                                                            reinterpret_cast<unsigned long long*>(counts), wsums); }
     LAUNCHED();
     return free_fail(cudaGetLastError(), "hist launch");
+}
+
+int oevae_wsum(const float* w, const uint8_t* keep, int64_t N, double* sum_acc, int32_t device, void* stream) {
+    if (!sum_acc || (N > 0 && !w)) { g_create_error = "wsum: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    if (N <= 0) return 0;
+    wsum_kernel<<<std::min<unsigned>(cdiv(N, 1024), 148 * 4), 256, 0, (cudaStream_t)stream>>>(w, keep, N, sum_acc);
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "wsum launch");
 }
 
 // Layered-GEMM building block exposed for kernel-level tests: C[R,Cn] = sum_t A[r*sAr + t*sAt] * B[t*sBt + c*sBc]
@@ -1207,6 +1257,119 @@ int oevae_probe_bulk(int32_t bytes, int32_t depth, int32_t n_cta, int32_t same_s
     rc = free_fail(cudaMemcpy(out_host2, d, 2 * sizeof(long long), cudaMemcpyDeviceToHost), "probe_bulk");
     cudaFree(d); cudaFree(src);
     return rc;
+}
+
+// ---- weighted ROC + cut thresholds (roc_kernels.cuh)
+
+int oevae_roc(const float* score, const uint8_t* y_true, int32_t pos_label, const float* w, int64_t N,
+              double* fpr, double* tpr, double* thr, int64_t* n_points_host, int32_t device, void* stream) {
+    using namespace roc;
+    if (!score || !y_true || !fpr || !tpr || !thr || !n_points_host || N <= 0 || N >= (1ll << 31)) { g_create_error = "roc: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const long n = N;
+    const unsigned nt = cdiv(n, kTile);
+    RocWs ws;
+    ws.cap = (size_t)n * (4 * 4 + 2 * 4 + 2 * 8 + 4 + 3 * 8) + (size_t)256 * nt * 4 + (size_t)nt * 24 + (1 << 16);
+    rc = free_fail(cudaMalloc(&ws.base, ws.cap), "roc workspace"); if (rc) return rc;
+    uint32_t* keys0 = ws.take<uint32_t>(n); uint32_t* keys1 = ws.take<uint32_t>(n);
+    uint32_t* vals0 = ws.take<uint32_t>(n); uint32_t* vals1 = ws.take<uint32_t>(n);
+    uint32_t* flags = ws.take<uint32_t>(n); uint32_t* pos = ws.take<uint32_t>(n);
+    double* a = ws.take<double>(n); double* b = ws.take<double>(n);
+    float* ss = ws.take<float>(n);
+    double* tps = ws.take<double>(n); double* fps = ws.take<double>(n); double* th = ws.take<double>(n);
+    uint32_t* hist = ws.take<uint32_t>((size_t)256 * nt);
+    uint32_t* tiles = ws.take<uint32_t>(nt + 64);
+    double* dta = ws.take<double>(nt + 1); double* dtb = ws.take<double>(nt + 1);
+    uint32_t* total = ws.take<uint32_t>(4);
+    int* bad = reinterpret_cast<int*>(ws.take<uint32_t>(4));
+    auto done = [&](int code, const char* msg) { cudaStreamSynchronize(s); cudaFree(ws.base); if (code) g_create_error = msg; return code; };
+    auto fetch = [&](const void* dptr, void* hptr, size_t bytes) { return cudaMemcpyAsync(hptr, dptr, bytes, cudaMemcpyDeviceToHost, s) == cudaSuccess && cudaStreamSynchronize(s) == cudaSuccess; };
+    const unsigned g256 = cdiv(n, 256);
+    cudaMemsetAsync(bad, 0, sizeof(int), s);
+    // 1. drop zero-weight samples (order-preserving), 2. keys = descending-score order image, payload = sample index
+    long m = n;
+    if (w) {
+        nonzero_flag_kernel<<<g256, 256, 0, s>>>(w, n, flags); LAUNCHED();
+        roc_scan(flags, pos, n, tiles, total, s);
+        uint32_t h = 0; if (!fetch(total, &h, 4)) return done(OEVAE_ECUDA, "roc: scan failed");
+        m = h;
+        if (m == 0) return done(OEVAE_EINVAL, "roc: every sample has zero weight");
+    }
+    build_keys_kernel<<<g256, 256, 0, s>>>(score, n, w ? flags : nullptr, w ? pos : nullptr, keys0, vals0, bad); LAUNCHED();
+    const unsigned mt = cdiv(m, kTile);
+    uint32_t *kin = keys0, *kout = keys1, *vin = vals0, *vout = vals1;
+    for (int shift = 0; shift < 32; shift += 8) {
+        rs_hist_kernel<<<mt, kThreads, 0, s>>>(kin, m, shift, hist, (int)mt); LAUNCHED();
+        roc_scan(hist, hist, 256L * mt, tiles, nullptr, s);
+        rs_scatter_kernel<<<mt, kThreads, 0, s>>>(kin, vin, kout, vout, m, shift, hist, (int)mt); LAUNCHED();
+        std::swap(kin, kout); std::swap(vin, vout);
+    }
+    // 3. class-wise weighted cumulative sums in np.cumsum's order
+    gather_sorted_kernel<<<cdiv(m, 256), 256, 0, s>>>(vin, m, score, y_true, pos_label, w, a, b, ss, bad); LAUNCHED();
+    int hbad = 0; if (!fetch(bad, &hbad, sizeof(int))) return done(OEVAE_ECUDA, "roc: gather failed");
+    if (hbad & 1) return done(OEVAE_EINVAL, "roc: non-finite score (sklearn's roc_curve rejects NaN / inf; apply utils.filtering first)");
+    const char* force = getenv("OEVAE_ROC_CUMSUM");                               // "seq" / "par": tests compare the two paths
+    const bool seq = force ? (force[0] == 's') : (hbad & 2) != 0;
+    if (seq) { seq_cumsum2_kernel<<<1, kThreads, 0, s>>>(a, b, m); LAUNCHED(); }
+    else {
+        dscan_tiles_kernel<<<mt, kThreads, 0, s>>>(a, b, m, dta, dtb); LAUNCHED();
+        dscan_block_kernel<<<1, 32, 0, s>>>(dta, dtb, mt); LAUNCHED();
+        dscan_apply_kernel<<<mt, kThreads, 0, s>>>(a, b, m, dta, dtb); LAUNCHED();
+    }
+    // 4. one point per distinct score
+    distinct_flag_kernel<<<cdiv(m, 256), 256, 0, s>>>(ss, m, flags); LAUNCHED();
+    roc_scan(flags, pos, m, tiles, total, s);
+    uint32_t m1u = 0; if (!fetch(total, &m1u, 4)) return done(OEVAE_ECUDA, "roc: distinct scan failed");
+    const long m1 = m1u;
+    take_points_kernel<<<cdiv(m, 256), 256, 0, s>>>(flags, pos, m, a, b, ss, tps, fps, th); LAUNCHED();
+    // 5. drop_intermediate, 6. normalise
+    long m2 = m1;
+    if (m1 > 2) {
+        corner_flag_kernel<<<cdiv(m1, 256), 256, 0, s>>>(fps, tps, m1, flags); LAUNCHED();
+        roc_scan(flags, pos, m1, tiles, total, s);
+        uint32_t h = 0; if (!fetch(total, &h, 4)) return done(OEVAE_ECUDA, "roc: corner scan failed");
+        m2 = h;
+        finish_kernel<<<cdiv(m1, 256), 256, 0, s>>>(flags, pos, m1, fps, tps, th, fpr, tpr, thr); LAUNCHED();
+    } else {
+        finish_kernel<<<cdiv(m1, 256), 256, 0, s>>>(nullptr, nullptr, m1, fps, tps, th, fpr, tpr, thr); LAUNCHED();
+    }
+    *n_points_host = m2 + 1;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return done(OEVAE_ECUDA, cudaGetErrorString(e));
+    return done(0, "");
+}
+
+int oevae_roc_cuts(const double* fpr, const double* tpr, const double* thr, int64_t n_points, const double* eff_host, int32_t n_eff,
+                   double min_tpr, double* out_host, int32_t device, void* stream) {
+    if (!fpr || !tpr || !thr || n_points <= 0 || n_eff < 0 || n_eff > 64 || (n_eff && !eff_host) || !out_host) { g_create_error = "roc_cuts: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    double* d = nullptr;
+    rc = free_fail(cudaMalloc(&d, (size_t)(n_eff + 4 * (n_eff + 1)) * sizeof(double) + 64), "roc_cuts workspace"); if (rc) return rc;
+    double* out = d + n_eff;
+    if (n_eff) cudaMemcpyAsync(d, eff_host, n_eff * sizeof(double), cudaMemcpyHostToDevice, s);
+    roc::roc_cuts_kernel<<<n_eff + 1, 1024, 0, s>>>(fpr, tpr, thr, n_points, d, n_eff, min_tpr, out); LAUNCHED();
+    cudaMemcpyAsync(out_host, out, (size_t)4 * (n_eff + 1) * sizeof(double), cudaMemcpyDeviceToHost, s);
+    cudaError_t e = cudaStreamSynchronize(s);
+    cudaFree(d);
+    return free_fail(e, "roc_cuts");
+}
+
+int oevae_roc_searchsorted(const double* fpr, const double* thr, int64_t n_points, const double* eff_host, int32_t n_q,
+                           double* thr_out_host, double* eff_out_host, int32_t device, void* stream) {
+    if (!fpr || !thr || n_points <= 0 || n_q <= 0 || n_q > 65536 || !eff_host || !thr_out_host) { g_create_error = "roc_searchsorted: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    double* d = nullptr;
+    rc = free_fail(cudaMalloc(&d, (size_t)3 * n_q * sizeof(double)), "roc_searchsorted workspace"); if (rc) return rc;
+    cudaMemcpyAsync(d, eff_host, n_q * sizeof(double), cudaMemcpyHostToDevice, s);
+    roc::roc_searchsorted_kernel<<<cdiv(n_q, 128), 128, 0, s>>>(fpr, thr, n_points, d, n_q, d + n_q, d + 2 * n_q); LAUNCHED();
+    cudaMemcpyAsync(thr_out_host, d + n_q, n_q * sizeof(double), cudaMemcpyDeviceToHost, s);
+    if (eff_out_host) cudaMemcpyAsync(eff_out_host, d + 2 * n_q, n_q * sizeof(double), cudaMemcpyDeviceToHost, s);
+    cudaError_t e = cudaStreamSynchronize(s);
+    cudaFree(d);
+    return free_fail(e, "roc_searchsorted");
 }
 
 int64_t oevae_launch_count(void) { return g_launches.load(); }

@@ -311,10 +311,15 @@ __global__ void loss_map_kernel(float* __restrict__ v, long N, int branch) {
 // (plots.py:697-715; np.histogram semantics with float64 edges: bin k = [e_k, e_k+1), last bin closed,
 // out-of-range and NaN values dropped).  Shared-memory privatised integer counts and fp64 weighted sums
 // per CTA, flushed with one atomic per non-empty bin.
+// Weight scalings of plots.py:706-712 (normalize / density): the per-jet weight becomes, in the reference's own rounding sequence,
+//   w1 = float32(w * wscale)            `weights *= 100 / np.sum(...)`   (float32 array times float32 scalar)
+//   w2 = float32(double(w1) / width_k)  `weights /= np.take(np.diff(bins), ...)`   (float32 array by float64 widths)
+// and the bin value is the float64 sum of those float32 weights (pylab.hist sums them in float32 through a cumulative sum; the two
+// agree to float32 rounding of the sum).
 // ------------------------------------------------------------------------------------------------
 __global__ void hist_kernel(const float* __restrict__ var, const float* __restrict__ w, const float* __restrict__ jzw,
                             const float* __restrict__ score, const unsigned char* __restrict__ keep, long N, float cut,
-                            const double* __restrict__ edges, int n_edges,
+                            const double* __restrict__ edges, int n_edges, float wscale, int density,
                             unsigned long long* __restrict__ counts, double* __restrict__ wsums) {
     extern __shared__ unsigned char smem_raw[];
     const int nb = n_edges - 1;
@@ -337,7 +342,11 @@ __global__ void hist_kernel(const float* __restrict__ var, const float* __restri
         while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (s_edges[mid] <= x) lo = mid; else hi = mid; }
         int bin = lo;                                      // x == last edge lands in the last bin (lo == nb-1)
         atomicAdd(&s_c[cls * nb + bin], 1u);
-        if (w) atomicAdd(&s_w[cls * nb + bin], (double)w[i]);
+        if (w) {
+            float wi = __fmul_rn(w[i], wscale);
+            if (density) wi = (float)__ddiv_rn((double)wi, __dsub_rn(s_edges[bin + 1], s_edges[bin]));
+            atomicAdd(&s_w[cls * nb + bin], (double)wi);
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < 2 * nb; i += blockDim.x) {
@@ -346,6 +355,14 @@ __global__ void hist_kernel(const float* __restrict__ var, const float* __restri
             if (w) atomicAdd(&wsums[i], s_w[i]);
         }
     }
+}
+
+// fp64 sum of a float32 vector over the rows with keep[i] (nullable): np.sum(sample['weights']) of plots.py:707, accumulated ADDITIVELY
+__global__ void wsum_kernel(const float* __restrict__ w, const unsigned char* __restrict__ keep, long N, double* __restrict__ out) {
+    double s = 0.0;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (long)gridDim.x * blockDim.x) if (!keep || keep[i]) s += (double)w[i];
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0 && s != 0.0) atomicAdd(out, s);
 }
 
 }  // namespace oevae

@@ -1,0 +1,343 @@
+// Weighted ROC curve and cut thresholds on the device (the step right after scoring):
+//   get_rates       plots.py:228-232   sklearn.metrics.roc_curve(y_true, X_loss, pos_label=0, sample_weight=weights)
+//   best_threshold  plots.py:235-247   argmax tpr/fpr over tpr > min_tpr
+//   make_cut        plots.py:250-258   thresholds[argmin |fpr - bkg_eff|]
+//   bump_scan grid  plots.py:272-282   searchsorted(fpr, eff_val, side='right')
+// roc_curve's arithmetic (scikit-learn 1.9: _sort_inputs_and_compute_classification_thresholds, confusion_matrix_at_thresholds,
+// roc_curve) is restated step by step so that fpr / tpr / thresholds are BIT-IDENTICAL to sklearn's:
+//   1. samples with weight 0 are dropped (order-preserving compaction);
+//   2. stable sort by DESCENDING score, ties in original order: an LSD radix sort (4 passes of 8 bits) on the bit-flipped,
+//      order-preserving integer image of the float32 score, payload = sample index;
+//   3. tps = cumsum(pos * w), fps = cumsum((1 - pos) * w) in float64 in np.cumsum's SEQUENTIAL order.  Floating-point addition
+//      is not associative, so a parallel scan would round differently and drop_intermediate (step 5) would keep other points.
+//      When every weight is an integer the partial sums are exact in any order and a parallel scan is used; otherwise one
+//      thread walks the chain (two independent chains interleaved), fed through shared memory by the rest of its block;
+//   4. one point per distinct score (last index of each run of ties);
+//   5. drop_intermediate: keep k iff it is an end point or diff(fps, 2)[k-1] != 0 or diff(tps, 2)[k-1] != 0 (same float64
+//      expression (f[k+1] - f[k]) - (f[k] - f[k-1]) as np.diff(f, 2));
+//   6. prepend (0, 0, inf); fpr = fps / fps[-1], tpr = tps / tps[-1].
+// HBM-bound integer / byte work: ~50 bytes per sample and radix pass; no tensor cores.
+#pragma once
+#include "common.cuh"
+
+namespace oevae {
+namespace roc {
+
+constexpr int kTile = 4096, kThreads = 256, kItems = kTile / kThreads;       // one block = one tile of 4096 elements
+
+// ---- order-preserving integer image of a float32 (ascending), -0.0 folded onto +0.0 like the float comparison
+__device__ __forceinline__ uint32_t orderable(float f) {
+    uint32_t u = __float_as_uint(f);
+    if (u == 0x80000000u) u = 0u;
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// ================================================================================================ scans
+// exclusive scan of uint32 [n] -> out [n], total in *total.  scan_tiles: per-tile sums; scan_block: in-place exclusive scan of the
+// tile sums by one block; scan_apply: per-tile rescan + tile offset.
+__global__ void __launch_bounds__(kThreads) scan_tiles_kernel(const uint32_t* __restrict__ in, long n, uint32_t* __restrict__ tile_sums) {
+    __shared__ uint32_t red[kThreads / 32];
+    const long base = (long)blockIdx.x * kTile;
+    uint32_t s = 0;
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) { const long i = base + k * kThreads + threadIdx.x; if (i < n) s += in[i]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) { uint32_t t = 0; for (int w = 0; w < kThreads / 32; ++w) t += red[w]; tile_sums[blockIdx.x] = t; }
+}
+__global__ void __launch_bounds__(1024) scan_block_kernel(uint32_t* __restrict__ data, long n, uint32_t* __restrict__ total) {
+    __shared__ uint32_t wsum[32];
+    __shared__ uint32_t carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (long c0 = 0; c0 < n; c0 += 1024) {
+        const long i = c0 + threadIdx.x;
+        const uint32_t v = i < n ? data[i] : 0u;
+        uint32_t x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += t; }
+        if (lane == 31) wsum[warp] = x;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t y = wsum[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, y, o); if (lane >= o) y += t; }
+            wsum[lane] = y;
+        }
+        __syncthreads();
+        const uint32_t carry = carry_s;
+        const uint32_t excl = carry + (warp ? wsum[warp - 1] : 0u) + x - v;
+        if (i < n) data[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = carry + wsum[31];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && total) *total = carry_s;
+}
+__global__ void __launch_bounds__(kThreads) scan_apply_kernel(const uint32_t* __restrict__ in, long n, const uint32_t* __restrict__ tile_offs,
+                                                              uint32_t* __restrict__ out) {
+    __shared__ uint32_t wsum[kThreads / 32];
+    const long base = (long)blockIdx.x * kTile + (long)threadIdx.x * kItems;     // thread owns kItems CONSECUTIVE elements
+    uint32_t v[kItems], s = 0;
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) { v[k] = base + k < n ? in[base + k] : 0u; s += v[k]; }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t x = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += t; }
+    if (lane == 31) wsum[warp] = x;
+    __syncthreads();
+    uint32_t off = tile_offs[blockIdx.x] + x - s;
+    for (int w = 0; w < warp; ++w) off += wsum[w];
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) { if (base + k < n) out[base + k] = off; off += v[k]; }
+}
+
+// ================================================================================================ radix sort (keys + index payload)
+__global__ void __launch_bounds__(kThreads) rs_hist_kernel(const uint32_t* __restrict__ keys, long n, int shift, uint32_t* __restrict__ hist, int nblk) {
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const long base = (long)blockIdx.x * kTile;
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) { const long i = base + k * kThreads + threadIdx.x; if (i < n) atomicAdd(&h[(keys[i] >> shift) & 255u], 1u); }
+    __syncthreads();
+    hist[(long)threadIdx.x * nblk + blockIdx.x] = h[threadIdx.x];              // digit-major: one exclusive scan gives the global offsets
+}
+// Stable scatter: warp w of the block owns elements [w * 512, w * 512 + 512) of the tile and walks them 32 at a time, so "earlier
+// in the tile" = (earlier warp) or (same warp, earlier iteration) or (same iteration, lower lane).
+__global__ void __launch_bounds__(kThreads) rs_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                                              uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, long n, int shift,
+                                                              const uint32_t* __restrict__ offs, int nblk) {
+    constexpr int kWarps = kThreads / 32, kPerWarp = kTile / kWarps, kIter = kPerWarp / 32;
+    __shared__ uint32_t cnt[kWarps][256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < kWarps * 256; i += kThreads) (&cnt[0][0])[i] = 0;
+    __syncthreads();
+    const long base = (long)blockIdx.x * kTile + (long)warp * kPerWarp;
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t key[kIter], pos[kIter];
+#pragma unroll
+    for (int j = 0; j < kIter; ++j) {
+        const long i = base + j * 32 + lane;
+        const bool on = i < n;
+        key[j] = on ? keys_in[i] : 0u;
+        const uint32_t d = on ? ((key[j] >> shift) & 255u) : (256u + lane);     // lanes past the end form singleton groups
+        const uint32_t m = __match_any_sync(0xffffffffu, d);
+        uint32_t before = 0;
+        if (on) before = cnt[warp][d];
+        __syncwarp();
+        if (on && (m & lt) == 0u) cnt[warp][d] = before + __popc(m);            // the lowest lane of the group publishes the new count
+        __syncwarp();
+        pos[j] = before + __popc(m & lt);
+    }
+    __syncthreads();
+    {   // digit d (one per thread): global offset of this tile's first element with that digit, then the warps' sub-ranges
+        const int d = threadIdx.x;
+        uint32_t run = offs[(long)d * nblk + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) { const uint32_t t = cnt[w][d]; cnt[w][d] = run; run += t; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < kIter; ++j) {
+        const long i = base + j * 32 + lane;
+        if (i < n) {
+            const uint32_t dst = cnt[warp][(key[j] >> shift) & 255u] + pos[j];
+            keys_out[dst] = key[j];
+            vals_out[dst] = vals_in[i];
+        }
+    }
+}
+
+// ================================================================================================ ROC stages
+// flags[i] = weight != 0 (sklearn drops zero-weight samples before sorting)
+__global__ void nonzero_flag_kernel(const float* __restrict__ w, long n, uint32_t* __restrict__ flags) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[i] = w[i] != 0.f ? 1u : 0u;
+}
+// keys[p] = ~orderable(score[i]) (ascending radix order = descending score), vals[p] = i for the kept samples; bad |= non-finite score
+__global__ void build_keys_kernel(const float* __restrict__ score, long n, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ pos,
+                                  uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, int* __restrict__ bad) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (flags && !flags[i]) return;
+    const float s = score[i];
+    if (!isfinite(s)) atomicOr(bad, 1);
+    const long p = flags ? (long)pos[i] : i;
+    keys[p] = ~orderable(s);
+    vals[p] = (uint32_t)i;
+}
+// sorted position p: a[p] = pos ? w : 0, b[p] = pos ? 0 : w (float64, exact widening), s[p] = score; bad |= 2 when a weight is not an integer
+__global__ void gather_sorted_kernel(const uint32_t* __restrict__ vals, long m, const float* __restrict__ score, const unsigned char* __restrict__ y_true,
+                                     int pos_label, const float* __restrict__ w, double* __restrict__ a, double* __restrict__ b, float* __restrict__ s,
+                                     int* __restrict__ bad) {
+    const long p = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= m) return;
+    const uint32_t i = vals[p];
+    const float wi = w ? w[i] : 1.f;
+    if (wi != floorf(wi) || fabsf(wi) > 16777216.f) atomicOr(bad, 2);
+    const bool is_pos = (int)y_true[i] == pos_label;
+    a[p] = is_pos ? (double)wi : 0.0;
+    b[p] = is_pos ? 0.0 : (double)wi;
+    s[p] = score[i];
+}
+// np.cumsum order: one thread adds, the block streams tiles through shared memory (double-buffered)
+__global__ void __launch_bounds__(kThreads) seq_cumsum2_kernel(double* __restrict__ a, double* __restrict__ b, long n) {
+    constexpr int T = 1024;                                                  // 2 x 2 x 1024 doubles = 32 KB of static shared memory
+    __shared__ double sa[2][T], sb[2][T];
+    double ra = 0.0, rb = 0.0;
+    const long ntile = (n + T - 1) / T;
+    auto load = [&](long t, int buf) {
+        for (int k = threadIdx.x; k < T; k += kThreads) { const long i = t * T + k; sa[buf][k] = i < n ? a[i] : 0.0; sb[buf][k] = i < n ? b[i] : 0.0; }
+    };
+    load(0, 0);
+    __syncthreads();
+    for (long t = 0; t < ntile; ++t) {
+        const int buf = (int)(t & 1);
+        if (threadIdx.x == 0) {
+#pragma unroll 8
+            for (int k = 0; k < T; ++k) { ra += sa[buf][k]; sa[buf][k] = ra; rb += sb[buf][k]; sb[buf][k] = rb; }
+        } else if (threadIdx.x >= 32 && t + 1 < ntile) {
+            for (int k = threadIdx.x - 32; k < T; k += kThreads - 32) { const long i = (t + 1) * T + k; sa[buf ^ 1][k] = i < n ? a[i] : 0.0; sb[buf ^ 1][k] = i < n ? b[i] : 0.0; }
+        }
+        __syncthreads();
+        for (int k = threadIdx.x; k < T; k += kThreads) { const long i = t * T + k; if (i < n) { a[i] = sa[buf][k]; b[i] = sb[buf][k]; } }
+        __syncthreads();
+    }
+}
+// exact (integer-valued) float64 inclusive scan, three kernels like the uint32 scan
+__global__ void __launch_bounds__(kThreads) dscan_tiles_kernel(const double* __restrict__ a, const double* __restrict__ b, long n, double* __restrict__ ta, double* __restrict__ tb) {
+    __shared__ double ra[kThreads / 32], rb[kThreads / 32];
+    const long base = (long)blockIdx.x * kTile;
+    double x = 0.0, y = 0.0;
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) { const long i = base + k * kThreads + threadIdx.x; if (i < n) { x += a[i]; y += b[i]; } }
+    x = warp_sum(x); y = warp_sum(y);
+    if ((threadIdx.x & 31) == 0) { ra[threadIdx.x >> 5] = x; rb[threadIdx.x >> 5] = y; }
+    __syncthreads();
+    if (threadIdx.x == 0) { double s = 0.0, t = 0.0; for (int w = 0; w < kThreads / 32; ++w) { s += ra[w]; t += rb[w]; } ta[blockIdx.x] = s; tb[blockIdx.x] = t; }
+}
+__global__ void dscan_block_kernel(double* __restrict__ ta, double* __restrict__ tb, long n) {      // exclusive, one thread (n = tiles: a few thousand)
+    if (threadIdx.x == 0 && blockIdx.x == 0) { double s = 0.0, t = 0.0; for (long i = 0; i < n; ++i) { const double x = ta[i], y = tb[i]; ta[i] = s; tb[i] = t; s += x; t += y; } }
+}
+__global__ void __launch_bounds__(kThreads) dscan_apply_kernel(double* __restrict__ a, double* __restrict__ b, long n, const double* __restrict__ ta, const double* __restrict__ tb) {
+    __shared__ double wa[kThreads / 32], wb[kThreads / 32];
+    const long base = (long)blockIdx.x * kTile + (long)threadIdx.x * kItems;
+    double va[kItems], vb[kItems], sa = 0.0, sb = 0.0;
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) { va[k] = base + k < n ? a[base + k] : 0.0; vb[k] = base + k < n ? b[base + k] : 0.0; sa += va[k]; sb += vb[k]; }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double xa = sa, xb = sb;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const double t = __shfl_up_sync(0xffffffffu, xa, o), u = __shfl_up_sync(0xffffffffu, xb, o); if (lane >= o) { xa += t; xb += u; } }
+    if (lane == 31) { wa[warp] = xa; wb[warp] = xb; }
+    __syncthreads();
+    double oa = ta[blockIdx.x] + xa - sa, ob = tb[blockIdx.x] + xb - sb;
+    for (int w = 0; w < warp; ++w) { oa += wa[w]; ob += wb[w]; }
+#pragma unroll
+    for (int k = 0; k < kItems; ++k) { oa += va[k]; ob += vb[k]; if (base + k < n) { a[base + k] = oa; b[base + k] = ob; } }
+}
+// one point per distinct score: flag the last index of every run of equal scores
+__global__ void distinct_flag_kernel(const float* __restrict__ s, long m, uint32_t* __restrict__ flags) {
+    const long p = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < m) flags[p] = (p == m - 1 || s[p] != s[p + 1]) ? 1u : 0u;
+}
+__global__ void take_points_kernel(const uint32_t* __restrict__ flags, const uint32_t* __restrict__ pos, long m, const double* __restrict__ ca,
+                                   const double* __restrict__ cb, const float* __restrict__ s, double* __restrict__ tps, double* __restrict__ fps, double* __restrict__ thr) {
+    const long p = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < m && flags[p]) { const long k = pos[p]; tps[k] = ca[p]; fps[k] = cb[p]; thr[k] = (double)s[p]; }
+}
+// drop_intermediate: keep[k] = end point or a corner in fps or in tps (np.diff(., 2) != 0)
+__global__ void corner_flag_kernel(const double* __restrict__ fps, const double* __restrict__ tps, long m, uint32_t* __restrict__ keep) {
+    const long k = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= m) return;
+    bool kp = k == 0 || k == m - 1;
+    if (!kp) {
+        const double df = __dsub_rn(__dsub_rn(fps[k + 1], fps[k]), __dsub_rn(fps[k], fps[k - 1]));
+        const double dt = __dsub_rn(__dsub_rn(tps[k + 1], tps[k]), __dsub_rn(tps[k], tps[k - 1]));
+        kp = df != 0.0 || dt != 0.0;
+    }
+    keep[k] = kp ? 1u : 0u;
+}
+// out[0] = (0, 0, inf); out[1 + j] = (fps / fps_last, tps / tps_last, thr) of the kept points
+__global__ void finish_kernel(const uint32_t* __restrict__ keep, const uint32_t* __restrict__ pos, long m, const double* __restrict__ fps,
+                              const double* __restrict__ tps, const double* __restrict__ thr, double* __restrict__ fpr_out, double* __restrict__ tpr_out,
+                              double* __restrict__ thr_out) {
+    const long k = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    const double fl = fps[m - 1], tl = tps[m - 1];
+    if (k == 0) { fpr_out[0] = fl > 0.0 ? 0.0 : NAN; tpr_out[0] = tl > 0.0 ? 0.0 : NAN; thr_out[0] = INFINITY; }   // a class without samples: all-NaN rate (sklearn warns)
+    if (k >= m || (keep && !keep[k])) return;
+    const long j = 1 + (keep ? (long)pos[k] : k);
+    fpr_out[j] = fl > 0.0 ? __ddiv_rn(fps[k], fl) : NAN;
+    tpr_out[j] = tl > 0.0 ? __ddiv_rn(tps[k], tl) : NAN;
+    thr_out[j] = thr[k];
+}
+
+// ================================================================================================ cut thresholds from the curve
+// get_rates (plots.py:230): points with fpr != 0, rates in percent.  Block e < n_eff: argmin |100 fpr - eff[e]| (make_cut, plots.py:256-258);
+// block n_eff: argmax 100 tpr / (100 fpr) over 100 tpr > min_tpr (best_threshold 'gain', plots.py:237-246).  First occurrence wins, as
+// np.argmin / np.argmax.  out[e] = {threshold, value (|fpr - eff| or the gain), index in the curve (as a double), 100 fpr there}
+__global__ void __launch_bounds__(1024) roc_cuts_kernel(const double* __restrict__ fpr, const double* __restrict__ tpr, const double* __restrict__ thr, long n,
+                                                        const double* __restrict__ eff, int n_eff, double min_tpr, double* __restrict__ out) {
+    __shared__ double bv[32]; __shared__ long bi[32];
+    const int e = blockIdx.x;
+    const bool gain = e == n_eff;
+    const double target = gain ? 0.0 : eff[e];
+    double best = gain ? -INFINITY : INFINITY; long besti = -1;
+    for (long i = threadIdx.x; i < n; i += blockDim.x) {
+        const double f = fpr[i];
+        if (!(f != 0.0)) continue;                                        // fpr != 0 (NaN != 0 is true in NumPy; a NaN curve has no cut)
+        const double F = __dmul_rn(100.0, f), T = __dmul_rn(100.0, tpr[i]);
+        // a thread visits its indices in increasing order, so a strict comparison keeps the first occurrence
+        if (gain) {
+            if (!(T > min_tpr)) continue;
+            const double v = __ddiv_rn(T, F);
+            if (besti < 0 || v > best) { best = v; besti = i; }
+        } else {
+            const double v = fabs(__dsub_rn(F, target));
+            if (besti < 0 || v < best) { best = v; besti = i; }
+        }
+    }
+    auto better = [&](double v, long i, double w, long j) {              // (v, i) beats (w, j)?
+        if (i < 0) return false;
+        if (j < 0) return true;
+        if (gain ? v > w : v < w) return true;
+        return v == w && i < j;
+    };
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, best, o); const long oi = __shfl_xor_sync(0xffffffffu, besti, o);
+        if (better(ov, oi, best, besti)) { best = ov; besti = oi; }
+    }
+    if ((threadIdx.x & 31) == 0) { bv[threadIdx.x >> 5] = best; bi[threadIdx.x >> 5] = besti; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) if (better(bv[w], bi[w], best, besti)) { best = bv[w]; besti = bi[w]; }
+        out[4 * e + 0] = besti >= 0 ? thr[besti] : NAN;
+        out[4 * e + 1] = best;
+        out[4 * e + 2] = (double)besti;                                   // index in the unfiltered curve (-1: no point qualifies)
+        out[4 * e + 3] = besti >= 0 ? __dmul_rn(100.0, fpr[besti]) : NAN;
+    }
+}
+// np.minimum(np.searchsorted(eff, v, side='right'), len(eff) - 1) over the fpr != 0 points (bump_scan, plots.py:282): eff = 100 fpr is
+// non-decreasing; returns the threshold at that index.  One thread per query.
+__global__ void roc_searchsorted_kernel(const double* __restrict__ fpr, const double* __restrict__ thr, long n, const double* __restrict__ q, int nq,
+                                        double* __restrict__ thr_out, double* __restrict__ eff_out) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nq) return;
+    const double v = q[t];
+    long lo = 0, hi = n;                                                  // first: number of leading points with fpr == 0 (get_rates drops them)
+    while (lo < hi) { const long mid = (lo + hi) >> 1; if (fpr[mid] > 0.0) hi = mid; else lo = mid + 1; }
+    hi = n;                                                               // first index in [first, n) with 100 fpr > v
+    while (lo < hi) { const long mid = (lo + hi) >> 1; if (__dmul_rn(100.0, fpr[mid]) > v) hi = mid; else lo = mid + 1; }
+    const long idx = lo < n ? lo : n - 1;
+    thr_out[t] = thr[idx];
+    eff_out[t] = __dmul_rn(100.0, fpr[idx]);
+}
+
+}  // namespace roc
+}  // namespace oevae

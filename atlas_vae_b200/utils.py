@@ -5,7 +5,8 @@
   fit_scaler      utils.py:389-405 (host sklearn fit, unchanged)   apply_scaler   utils.py:406-430
   loss_function   utils.py:346-375      latent_loss     utils.py:378-386      filtering   utils.py:532-538
   get_idx         utils.py:541-548
-HDF5 loading, OoD pairing and reweighting (utils.py:36-290) are outside the hot path.
+  QuantileTransformer / PowerTransformer apply (utils.py:393-396,411) on the device: scaler_kernels.cuh
+HDF5 loading (utils.py:36-130) needs h5py, which this image does not have.
 """
 import pickle
 
@@ -45,8 +46,54 @@ def _scaler_affine(scaler, D):
     return None
 
 
+_NDTRI_CLIP = (-5.199337582605575, 5.19933758270342)        # stats.norm.ppf(1e-7 - np.spacing(1)), stats.norm.ppf(1 - (1e-7 - np.spacing(1)))
+
+
+def transform_device(x_t, scaler, out=None):
+    """apply_scaling (utils.py:406-417) of a fitted sklearn scaler on a device float32 [N, D] tensor (in place unless `out`):
+    MaxAbs / Robust (affine, bit-exact), QuantileTransformer(normal) (bit-exact), PowerTransformer (yeo-johnson; float32 ulps)."""
+    dev = x_t.device
+    N, D = x_t.shape
+    out = x_t if out is None else out
+    lib = _ffi.lib()
+    name = type(scaler).__name__
+    aff = _scaler_affine(scaler, D)
+    if aff is not None:
+        c, sc = aff
+        if len(sc) != D or (c is not None and len(c) != D):
+            raise ValueError('scaler was fitted on %d columns, the array has %d' % (len(sc), D))
+        c_t = None if c is None else torch.as_tensor(c).to(dev)
+        s_t = torch.as_tensor(sc).to(dev)
+        check(lib.oevae_affine(ptr(x_t), ptr(out), N, D, ptr(c_t), ptr(s_t), dev.index, _stream()))
+    elif name == 'QuantileTransformer':
+        if scaler.output_distribution != 'normal':
+            raise NotImplementedError("QuantileTransformer: only output_distribution='normal' (the reference's, utils.py:394) is on the device")
+        q = np.ascontiguousarray(np.asarray(scaler.quantiles_, np.float64).T)              # [D, n_q]: a column's table is contiguous
+        if q.shape[0] != D: raise ValueError('scaler was fitted on %d columns, the array has %d' % (q.shape[0], D))
+        q_t = torch.as_tensor(q).to(dev); r_t = torch.as_tensor(np.asarray(scaler.references_, np.float64)).to(dev)
+        check(lib.oevae_quantile_normal(ptr(x_t), ptr(out), N, D, ptr(q_t), ptr(r_t), q.shape[1], _NDTRI_CLIP[0], _NDTRI_CLIP[1], dev.index, _stream()))
+    elif name == 'PowerTransformer':
+        if scaler.method != 'yeo-johnson':
+            raise NotImplementedError("PowerTransformer: only method='yeo-johnson' (the default the reference uses, utils.py:396)")
+        lam = np.asarray(scaler.lambdas_)
+        if lam.dtype != np.float32:
+            raise NotImplementedError('PowerTransformer fitted on float64 data: the reference fits on float32 constituents (utils.py:97,390-400)')
+        if len(lam) != D: raise ValueError('scaler was fitted on %d columns, the array has %d' % (len(lam), D))
+        l_t = torch.as_tensor(lam).to(dev)
+        m_t = s_t = None
+        if scaler.standardize:
+            st = scaler._scaler
+            m_t = torch.as_tensor(np.asarray(st.mean_, np.float32)).to(dev) if st.with_mean else None
+            s_t = torch.as_tensor(np.asarray(st.scale_, np.float32)).to(dev) if st.with_std else None
+        check(lib.oevae_power_yj(ptr(x_t), ptr(out), N, D, ptr(l_t), ptr(m_t), ptr(s_t), dev.index, _stream()))
+    else:
+        raise NotImplementedError('%s has no device transform' % name)
+    return out
+
+
 def preprocess_device(raw, n_const, n_dims=4, scaler=None, sort=True, device=None, want_4v=True):
-    """K0 on device tensors: raw [N, 4*n_raw] (fp32 or fp16; E,px,py,pz) -> (X [N,n_dims*n_const], pt, m)."""
+    """K0 on device tensors: raw [N, 4*n_raw] (fp32 or fp16; E,px,py,pz) -> (X [N,n_dims*n_const], pt, m).  Affine scalers are
+    folded into the K0 kernel; Quantile / Power transformers run as a second kernel on its output."""
     dev = _dev(device)
     if isinstance(raw, torch.Tensor):
         raw_t = raw.to(dev).contiguous()
@@ -59,11 +106,11 @@ def preprocess_device(raw, n_const, n_dims=4, scaler=None, sort=True, device=Non
     N, n_raw = raw_t.shape[0], raw_t.shape[1] // 4
     D = n_dims * n_const
     c_t = s_t = None
-    if scaler is not None:
-        aff = _scaler_affine(scaler, D)
-        if aff is None:
-            raise NotImplementedError('%s is not affine: apply it with sklearn on the host (SURVEY 8(f) f3)' % type(scaler).__name__)
+    aff = None if scaler is None else _scaler_affine(scaler, D)
+    if aff is not None:
         c, s = aff
+        if len(s) != D or (c is not None and len(c) != D):
+            raise ValueError('scaler was fitted on %d columns, the preprocessed input has %d (fit it with reshape=False on [N, n_dims * n_const])' % (len(s), D))
         c_t = None if c is None else torch.as_tensor(c).to(dev)
         s_t = torch.as_tensor(s).to(dev)
     x = torch.empty((N, D), dtype=torch.float32, device=dev)
@@ -71,6 +118,8 @@ def preprocess_device(raw, n_const, n_dims=4, scaler=None, sort=True, device=Non
     m = torch.empty(N, dtype=torch.float32, device=dev) if want_4v else None
     check(_ffi.lib().oevae_preprocess(ptr(raw_t), code, N, n_raw, int(n_const), int(n_dims), ptr(c_t), ptr(s_t),
                                       1 if sort else 0, ptr(x), ptr(pt), ptr(m), dev.index, _stream()))
+    if scaler is not None and aff is None:
+        transform_device(x, scaler)
     return x, pt, m
 
 
@@ -120,21 +169,14 @@ def fit_scaler(sample, n_dims, scaler_out, scaler_type='RobustScaler', reshape=F
 
 
 def apply_scaler(sample, n_dims, scaler, tag='sample', reshape=False, verbose=False):
-    """utils.py:419-430.  Affine scalers (MaxAbs / Robust) run on the device; Quantile / Power transformers
-    are not on the device path yet and use sklearn's own transform on the host."""
+    """utils.py:419-430 on the device: MaxAbs / Robust (affine), QuantileTransformer(normal) and PowerTransformer(yeo-johnson).
+    Returns a float32 host array of the input's shape (sklearn's transforms of a float32 array are float32 too)."""
     if scaler is None: return sample
     shape = np.shape(sample)
     x2 = np.reshape(sample, (-1, n_dims)) if reshape else np.asarray(sample)
-    aff = _scaler_affine(scaler, x2.shape[1])
-    if aff is None:
-        return np.reshape(scaler.transform(x2), shape)
-    dev = _dev()
-    c, s = aff
-    x_t = _to_dev(x2, dev)
-    c_t = None if c is None else torch.as_tensor(c).to(dev)
-    s_t = torch.as_tensor(s).to(dev)
-    check(_ffi.lib().oevae_affine(ptr(x_t), ptr(x_t), x_t.shape[0], x_t.shape[1], ptr(c_t), ptr(s_t), dev.index, _stream()))
-    return _host(x_t).reshape(shape)
+    x_t = _to_dev(x2, _dev())
+    if x_t.data_ptr() == np.asarray(x2).ctypes.data: x_t = x_t.clone()
+    return _host(transform_device(x_t, scaler)).reshape(shape)
 
 
 _METRIC_SLOT = {'MSE': 0, 'MAE': 1, 'MARE': 2, 'KLD': 3, 'JSD': 4, 'X-S': 5}

@@ -63,8 +63,6 @@ def parse_args(argv=None):
         a.FC_layers = list(a.FC_layers[:-1]) + [a.latent_dim]
     if a.HLVs == 'ON':
         raise SystemExit('--HLVs ON needs the 12 high-level variables of the HDF5 files; synthetic samples carry constituents only')
-    if a.decorrelation == 'ON':
-        raise SystemExit('--decorrelation ON (plots.mass_deco) is outside the hot path (SURVEY 8(f) f3)')
     if a.const_scaler_out == '':
         a.const_scaler_out = 'const_' + a.const_scaler_type + '.pkl'
     for k in ['model_in', 'model_out', 'const_scaler_in', 'const_scaler_out', 'hist_file']:   # vae.py:58-65
@@ -72,12 +70,17 @@ def parse_args(argv=None):
     return a
 
 
-def _sample(kind, n, args, scaler, seed, device):
-    """load_data + apply_scaler (vae.py:125-131,153-162) on synthetic jets -> dict of host arrays."""
+def _sample(kind, n, args, scaler, seed, device, files=False):
+    """load_data (+ apply_scaler, vae.py:125-131,153-162) on synthetic jets -> dict of host arrays.  files=True: the constituents stay
+    as the reference's files hold them -- sorted, float16, unscaled (tools/merging.py:31) -- and train_model scales them on the device."""
     import torch
     from . import synthetic as S, utils as U
     raw, jzw = S.make_jets(kind, n, max(args.n_const, 100), seed=seed, device=device)
-    x, pt, m = U.preprocess_device(raw, args.n_const, args.n_dims, scaler, True)
+    if files:
+        x, pt, m = U.preprocess_device(raw, args.n_const, args.n_dims, None, True)
+        x = x.to(torch.float16)
+    else:
+        x, pt, m = U.preprocess_device(raw.to(torch.float16), args.n_const, args.n_dims, scaler, True)   # same float16 rounding as the files
     return {'constituents': x.cpu().numpy(), 'weights': np.ones(n, np.float32), 'JZW': jzw.cpu().numpy(),
             'pt': pt.cpu().numpy(), 'm': m.cpu().numpy()}
 
@@ -98,41 +101,61 @@ def main(argv=None):
                                    precision=args.precision, max_batch=args.batch_size)
     if args.model_in != args.output_dir + '/' and os.path.isfile(args.model_in):
         model.load_weights(args.model_in)                                          # vae.py:93-102 (no dummy build call needed)
-    # scaler (vae.py:103-124): MaxAbs on the first 100k background jets unless another affine type is asked for
+    # scaler (vae.py:103-124): fitted on up to 100k background jets unless a pickled one is given; MaxAbs when no type is asked for
+    # (synthetic momenta are O(100 GeV): unscaled inputs would overflow exp(log_var))
     scaler = None
     if os.path.isfile(args.const_scaler_in):
         scaler = pickle.load(open(args.const_scaler_in, 'rb'))
     else:
         raw, _ = S.make_jets('QCD', min(args.n_train, 100_000), max(args.n_const, 100), seed=args.seed, device=device)
-        x0, _, _ = U.preprocess_device(raw, args.n_const, args.n_dims, None, True, want_4v=False)
-        if args.const_scaler_type in ('', 'MaxAbsScaler'):
-            scaler = S.MaxAbs(S.maxabs_scale(x0))
-        else:
-            scaler = U.fit_scaler({'constituents': x0.cpu().numpy()}, args.n_dims, args.const_scaler_out, args.const_scaler_type)
+        x0, _, _ = U.preprocess_device(raw.to(torch.float16), args.n_const, args.n_dims, None, True, want_4v=False)
+        stype = args.const_scaler_type or 'MaxAbsScaler'
+        scaler = U.fit_scaler(x0.cpu().numpy(), args.n_dims, args.const_scaler_out if rank == 0 else None, stype)   # utils.py:389-405 (pickles it)
+    affine = U._scaler_affine(scaler, input_dim) is not None
     if args.n_epochs > 0:
-        bkg = _sample('QCD', args.n_train, args, scaler, args.seed + 1, device)
-        ood = _sample('W', args.n_train, args, scaler, args.seed + 2, device) if args.lamb != 0 else bkg
-        vbkg = _sample('QCD', min(args.n_valid, args.n_train), args, scaler, args.seed + 3, device)
-        vood = _sample('W', len(vbkg['weights']), args, scaler, args.seed + 4, device) if args.lamb != 0 else vbkg
+        # affine scalers: the host keeps the file-format float16 rows and train_model applies the scaler on the device per batch;
+        # Quantile / Power transformers: utils.apply_scaler (device interpolation kernels) on the whole sample first, as vae.py:125-131
+        def train_sample(kind, n, seed):
+            if affine: return _sample(kind, n, args, None, seed, device, files=True)
+            smp = _sample(kind, n, args, None, seed, device, files=True)
+            smp['constituents'] = U.apply_scaler(smp['constituents'].astype(np.float32), args.n_dims, scaler)
+            return smp
+        bkg = train_sample('QCD', args.n_train, args.seed + 1)
+        ood = train_sample('W', args.n_train, args.seed + 2) if args.lamb != 0 else bkg
+        vbkg = train_sample('QCD', min(args.n_valid, args.n_train), args.seed + 3)
+        vood = train_sample('W', len(vbkg['weights']), args.seed + 4) if args.lamb != 0 else vbkg
         train_model(model, [(bkg, ood)], [(vbkg, vood)], args.OE_type, args.n_epochs, args.batch_size, args.beta, args.lamb,
-                    args.margin, args.lr, args.hist_file, args.model_in, args.model_out, patience=args.patience)
+                    args.margin, args.lr, args.hist_file, args.model_in, args.model_out, patience=args.patience,
+                    scaler=scaler if affine else None)
+        D.barrier()
+        if os.path.isfile(args.model_out):
+            model.load_weights(args.model_out)                                     # vae.py:141: score with the BEST checkpoint, not the last epoch
     # ---- anomaly-scoring pass (vae.py:145-176): QCD + top, sharded across ranks
     n_b, n_s = args.n_valid, min(args.n_sig, args.n_valid)
     lo_b, hi_b = D.shard_bounds(n_b, rank, world); lo_s, hi_s = D.shard_bounds(n_s, rank, world)
-    parts = [_sample('QCD', hi_b - lo_b, args, scaler, args.seed + 10 + rank, device), _sample('top', hi_s - lo_s, args, scaler, args.seed + 100 + rank, device)]
+    def test_sample(kind, n, seed):
+        smp = _sample(kind, n, args, scaler if affine else None, seed, device)
+        if not affine: smp['constituents'] = U.apply_scaler(smp['constituents'], args.n_dims, scaler)
+        return smp
+    parts = [test_sample('QCD', hi_b - lo_b, args.seed + 10 + rank), test_sample('top', hi_s - lo_s, args.seed + 100 + rank)]
     sample = {k: np.concatenate([p_[k] for p_ in parts]) for k in parts[0]}
     y_true = np.where(sample['JZW'] == -1, 0, 1)                                   # vae.py:150
-    losses, finite = Cu.score_sample(model, sample['constituents'], args.n_iter, normal_losses=args.normal_losses)
+    losses, finite = Cu.score_sample(model, sample['constituents'], args.n_iter, normal_losses='ON' if args.decorrelation == 'ON' else args.normal_losses)
     sample = {k: v[finite] for k, v in sample.items()}; y_true = y_true[finite]     # utils.filtering
     losses = {k: v[finite] for k, v in losses.items()}
+    if args.decorrelation == 'ON':                                                  # plots.py:36-39
+        losses['MAE'] = Cu.mass_deco(y_true, sample, losses['MAE'], deco='2d')
     if rank == 0:
         for k, v in losses.items():
             print('%-7s mean score: QCD %.4f  top %.4f' % (k, v[y_true == 1].mean(), v[y_true == 0].mean()))
-    if args.apply_cuts == 'ON' and world == 1:
+    if args.apply_cuts == 'ON':
+        # the test set is sharded: scores are gathered for the threshold search, every rank cuts its own jets, counts are reduced
         res = Cu.generate_cuts(y_true, sample, losses['MAE'], 'MAE')
-        pickle.dump(res, open(args.output_dir + '/plots/cut_histograms.pkl', 'wb'))
-        for name, r in res.items():
-            print('%-16s loss_cut %.5f  n_pass %d' % (name, r['loss_cut'], r['n_pass']))
+        if rank == 0:
+            pickle.dump(res, open(args.output_dir + '/plots/cut_histograms.pkl', 'wb'))
+            for name, r in res.items():
+                print('%-16s loss_cut %.5f  n_pass %d' % (name, r['loss_cut'], r['n_pass']))
+    D.barrier()
     return 0
 
 

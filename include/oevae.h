@@ -173,6 +173,18 @@ OEVAE_API int oevae_ingest_f16(const void* raw_f16, float* x, int64_t N, int32_t
 OEVAE_API int oevae_affine(const float* x, float* y, int64_t N, int32_t D, const double* center, const double* scale,
                  int32_t device, void* stream);
 
+/* apply_scaling for the NON-affine scalers of fit_scaler (utils.py:393-396,411) on an [N,D] float32 array; y may alias x.
+ * oevae_quantile_normal: QuantileTransformer(output_distribution='normal').transform -- quantiles_t: DEVICE double[D][n_q] (column f's
+ *   quantiles_[:, f] contiguous), references: DEVICE double[n_q], clip_min / clip_max = norm.ppf(1e-7 - eps) / norm.ppf(1 - (1e-7 - eps));
+ *   bit-identical to scikit-learn's float32 in-place transform up to the last bit of the float64 logarithm in the tails.
+ * oevae_power_yj: PowerTransformer(method='yeo-johnson', standardize=True).transform for a transformer fitted on float32 data
+ *   (float32 lambdas_; mean / scale = its StandardScaler's mean_ / scale_ as float32, nullable) -- float32 log1p / expm1, so equal
+ *   to scikit-learn's result to a few float32 ulps, not bit for bit. */
+OEVAE_API int oevae_quantile_normal(const float* x, float* y, int64_t N, int32_t D, const double* quantiles_t, const double* references, int32_t n_q,
+                          double clip_min, double clip_max, int32_t device, void* stream);
+OEVAE_API int oevae_power_yj(const float* x, float* y, int64_t N, int32_t D, const float* lambdas, const float* mean, const float* scale,
+                   int32_t device, void* stream);
+
 /* loss_function (utils.py:346-375) between two given arrays P, Q [N,D]; every output nullable [N]:
  * MSE, MAE, MARE, KLD, JSD, X-S */
 OEVAE_API int oevae_pair_metrics(const float* P, const float* Q, int64_t N, int32_t D, float* mse, float* mae, float* mare,
@@ -187,21 +199,45 @@ OEVAE_API int oevae_loss_map(float* v, int64_t N, int32_t branch, int32_t device
 /* make_cut mask (plots.py:259) + per-class histogram of plot_distributions (plots.py:697-715):
  * class 0: JZW == -1, class 1: JZW >= 0.  A jet enters iff keep[i] (nullable) and score[i] > cut
  * (score nullable => no cut).  edges: double[n_edges] (np.histogram semantics: half-open bins, last bin
- * closed).  counts int64 [2,n_edges-1] and wsums double [2,n_edges-1] are ADDED to. */
+ * closed).  counts int64 [2,n_edges-1] and wsums double [2,n_edges-1] are ADDED to.
+ * wscale / density: the weight scalings of plots.py:706-712 applied per jet in the reference's rounding sequence:
+ * w1 = fp32(w * wscale) (normalize: wscale = fp32(100) / fp32(sum of the uncut sample's weights), else 1),
+ * w2 = fp32(fp64(w1) / bin width) when density != 0; wsums accumulates the scaled weights. */
 OEVAE_API int oevae_hist(const float* var, const float* w, const float* jzw, const float* score, const uint8_t* keep,
-               int64_t N, float cut, const double* edges, int32_t n_edges,
+               int64_t N, float cut, const double* edges, int32_t n_edges, float wscale, int32_t density,
                int64_t* counts, double* wsums, int32_t device, void* stream);
+/* fp64 sum of a float32 vector over the rows with keep[i] (keep nullable), ADDED to *sum_acc (device): np.sum(sample['weights']) of
+ * plots.py:707 */
+OEVAE_API int oevae_wsum(const float* w, const uint8_t* keep, int64_t N, double* sum_acc, int32_t device, void* stream);
+
+/* ---- weighted ROC curve and cut thresholds on the device (the step right after scoring) ------------------------------------
+ * oevae_roc: get_rates (plots.py:228-232) = sklearn.metrics.roc_curve(y_true, X_loss, pos_label, sample_weight) with its default
+ * drop_intermediate=True, bit-identical to scikit-learn's float64 arithmetic (stable descending sort, zero-weight samples
+ * dropped, np.cumsum order; roc_kernels.cuh).  score [N] float32 (finite), y_true [N] uint8, w nullable [N] float32 (=> 1).
+ * fpr, tpr, thr: DEVICE double arrays of capacity N + 1; *n_points_host receives the number of points written (the first one
+ * is (0, 0, inf)).  Allocates its workspace and synchronises the stream.
+ * oevae_roc_cuts: over the points with fpr != 0, rates in percent (plots.py:230): entry e < n_eff = argmin |fpr - eff[e]|
+ * (make_cut, plots.py:256-258), entry n_eff = argmax tpr / fpr over tpr > min_tpr (best_threshold 'gain', plots.py:237-246).
+ * out_host: double[4 (n_eff + 1)] = {threshold, value, index in the curve, fpr there} per entry.
+ * oevae_roc_searchsorted: thresholds[min(searchsorted(fpr, eff, 'right'), len - 1)] over the same points (bump_scan's cut grid,
+ * plots.py:272-282). */
+OEVAE_API int oevae_roc(const float* score, const uint8_t* y_true, int32_t pos_label, const float* w, int64_t N,
+              double* fpr, double* tpr, double* thr, int64_t* n_points_host, int32_t device, void* stream);
+OEVAE_API int oevae_roc_cuts(const double* fpr, const double* tpr, const double* thr, int64_t n_points, const double* eff_host, int32_t n_eff,
+                   double min_tpr, double* out_host, int32_t device, void* stream);
+OEVAE_API int oevae_roc_searchsorted(const double* fpr, const double* thr, int64_t n_points, const double* eff_host, int32_t n_q,
+                           double* thr_out_host, double* eff_out_host, int32_t device, void* stream);
 
 /* ---- train_model's batch loop over one HOST-resident load (models.py:172-190), one call per group of batches ----------------
  * Replaces the implicit per-step host->device copies of models.py:180-182: batches [first_batch, first_batch + n_batches) of
- * `batch_size` rows are copied host->device on an internal copy stream, two batches ahead of the compute stream, and stepped with
+ * `batch_size` rows are copied host->device on an internal copy stream, up to five batches ahead of the compute stream, and stepped with
  * oevae_train_step (update 0) or oevae_train_step_dp (update 1; this rank's contiguous shard [n rank / world, n (rank+1) / world)
  * of every global batch, an empty shard joins the exchange).  Host arrays should be page-locked (oevae_host_register).
  *   x_dtype 1: x_host / xo_host hold float16 rows as the reference's files do (tools/merging.py:31); they are widened and scaled on
  *              the device (oevae_ingest_f16).  x_dtype 0 with a scaler: oevae_affine on the device.  center / scale: DEVICE double[D].
  *   x_resident (+ w_resident, xo_resident, wo_resident): nullable DEVICE buffers that receive the float32 batches, batch b at row
  *              b * resident_stride (stride >= the largest shard): the load then stays on the device and later epochs step on it
- *              without another copy.  Null: a three-slot ring inside the handle.
+ *              without another copy.  Null: a six-slot ring inside the handle.
  *   sums_acc   DEVICE double[4] (as oevae_train_step); sums_trace_host: nullable page-locked double[n_batches][4] that receives
  *              sums_acc after every step (device->host copy in stream order): the per-step metric read of models.py:187-190. */
 typedef struct {

@@ -162,3 +162,43 @@ def test_oracle_regression_vectors(golden_dir):
                                     beta=0.5, lamb=2.0, margin=0.3)
         np.testing.assert_allclose(np.stack(out), g['loss_' + oe], rtol=1e-12)
         np.testing.assert_allclose(gr, g['grad_' + oe], rtol=1e-10, atol=1e-14)
+
+
+# ---- non-affine scalers: the restatement the CUDA kernels follow, pinned against scikit-learn / SciPy / NumPy themselves
+def _jet_like(rng, N, D):
+    X = (rng.gamma(2.0, 20.0, (N, D)) * (rng.uniform(size=(N, D)) > 0.35)).astype(np.float32)
+    X[:, 1::4] *= np.where(rng.uniform(size=(N, D // 4)) < .5, -1, 1).astype(np.float32)
+    return X
+
+
+def test_ndtri_and_interp_restatements_match_scipy_numpy():
+    import scipy.special as sp
+    from oracle import scalers as Sc
+    rng = np.random.default_rng(0)
+    y = np.concatenate([rng.uniform(0, 1, 100000), 10.0 ** rng.uniform(-300, -1, 10000), 1 - 10.0 ** rng.uniform(-16, -1, 10000), [0, 1, 0.5, Sc.EXPM2, 1 - Sc.EXPM2]])
+    a, b = Sc.ndtri(y), sp.ndtri(y)
+    fin = np.isfinite(b)
+    assert np.array_equal(a[~fin], b[~fin]) and np.mean(a == b) > 0.999
+    np.testing.assert_allclose(a[fin], b[fin], rtol=2e-15, atol=0)
+    xp = np.sort(rng.normal(size=1000)); xp[100:110] = xp[100]; fp = np.linspace(0, 1, 1000)
+    x = np.concatenate([rng.normal(size=20000), xp[::7], [xp[0], xp[-1], -9, 9, np.nan]])
+    np.testing.assert_array_equal(Sc.interp(x, xp, fp), np.interp(x, xp, fp))
+    np.testing.assert_array_equal(Sc.interp(-x, -xp[::-1], -fp[::-1]), np.interp(-x, -xp[::-1], -fp[::-1]))
+
+
+def test_quantile_and_power_restatements_match_sklearn():
+    import warnings
+    from sklearn import preprocessing
+    from oracle import scalers as Sc
+    rng = np.random.default_rng(1)
+    X = _jet_like(rng, 12000, 16)
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore')
+        qt = preprocessing.QuantileTransformer(output_distribution='normal', n_quantiles=10000, random_state=0).fit(X)   # utils.py:394
+        Xn = np.concatenate([X[:3000], (X[:2000] * 1.7 + 3).astype(np.float32), np.full((1, 16), np.nan, np.float32)])
+        ref = qt.transform(Xn.copy())
+    assert ref.dtype == np.float32
+    np.testing.assert_array_equal(Sc.quantile_normal_transform(Xn, qt.quantiles_, qt.references_), ref)              # bit-exact, NaN included
+    pt = preprocessing.PowerTransformer().fit(X[:4000])                                                             # utils.py:396
+    assert pt.lambdas_.dtype == np.float32
+    np.testing.assert_array_equal(Sc.power_transform(X, pt.lambdas_, pt._scaler.mean_, pt._scaler.scale_), pt.transform(X.copy()))
