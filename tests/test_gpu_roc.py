@@ -125,8 +125,10 @@ def test_density_histograms_vs_numpy():
             ref_w = np.histogram(variable, bins, weights=weights.astype(np.float64))[0]   # float64 sum of the reference's float32 weights
             np.testing.assert_array_equal(c[row], ref_c)
             np.testing.assert_allclose(dens[row], ref_w, rtol=1e-12, atol=1e-12 * ref_w.sum())
-            ref32 = np.histogram(variable, bins, weights=weights)[0]        # what pylab.hist returns (float32 cumulative sums)
-            np.testing.assert_allclose(dens[row], ref32, rtol=2e-4, atol=1e-6 * ref32.max())
+            # what pylab.hist itself returns: np.histogram differences a float32 cumulative sum over 65536-element blocks, which
+            # carries ~1e-3 of float32 rounding per bin; the device value is the float64 sum of the same float32 weights
+            ref32 = np.histogram(variable, bins, weights=weights)[0]
+            np.testing.assert_allclose(dens[row], ref32, rtol=5e-3, atol=1e-5 * ref32.max())
 
 
 def test_generate_cuts_single_rank():
