@@ -78,6 +78,8 @@ SIGNATURES = {
     'oevae_loss_map': (C.c_int, [_vp, _i64, _i32, _i32, _vp]),
     'oevae_hist': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _i32, _f32, _i32, _vp, _vp, _i32, _vp]),
     'oevae_wsum': (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp]),
+    'oevae_argsort_f32': (C.c_int, [_vp, _i64, _vp, _i32, _vp]),
+    'oevae_ood_pairing': (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, C.c_uint64, _i32, _vp, _vp, _i32, _vp]),
     'oevae_roc': (C.c_int, [_vp, _vp, _i32, _vp, _i64, _vp, _vp, _vp, C.POINTER(_i64), _i32, _vp]),
     'oevae_roc_cuts': (C.c_int, [_vp, _vp, _vp, _i64, _vp, _i32, C.c_double, _vp, _i32, _vp]),
     'oevae_roc_searchsorted': (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _vp, _i32, _vp]),

@@ -18,39 +18,47 @@ struct AdamImgArgs {
     unsigned char* wimg; const int* pos;                    // pos: [4][n] byte offsets (fwd hi, fwd lo, dx hi, dx lo), -1 = none
 };
 
-// block = (64 parameters) x (8 slices of the partial-gradient list): slice y sums parts y, y+8, ... in order, ten
-// independent loads in flight at a time (one L2 round trip for the 79 slices of a B=5000 step: the kernel is bound by
-// L2 latency, not bandwidth), one resident wave of 512-thread blocks; the eight slice sums are
-// combined in a fixed tree, so the result does not depend on scheduling.
-constexpr int kAdamCols = 64, kAdamSlices = 8;
-__global__ void __launch_bounds__(kAdamCols * kAdamSlices, 4) adam_img_kernel(AdamImgArgs a) {
-    __shared__ float red[kAdamSlices][kAdamCols + 1];
+// Fixed-order sum of the partial-gradient list for one block of kAdamCols parameters: thread (cx, sl) owns FOUR consecutive
+// parameters (one 16-byte load per slice) and sums slices sl, sl + 8, ..., ten independent loads in flight (one L2 round trip
+// for the 79 slices of a B = 5000 step); the eight slice sums meet in shared memory and are combined in a fixed tree by the
+// thread that owns the parameter, so the result does not depend on scheduling.  One resident wave: ceil(P / 256) blocks of 512.
+constexpr int kAdamCols = 256, kAdamSlices = 8, kAdamThreads = (kAdamCols / 4) * kAdamSlices;
+__device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+// returns (for threads tid < kAdamCols) the sum over the n_parts slices of parameter blockIdx.x * kAdamCols + tid
+__device__ __forceinline__ float reduce_parts(const float* __restrict__ parts, int n_parts, long part_stride, float (*red)[kAdamCols]) {
+    const int cx = threadIdx.x & (kAdamCols / 4 - 1), sl = threadIdx.x / (kAdamCols / 4);
+    const long i4 = (long)blockIdx.x * kAdamCols + 4 * cx;            // rows are padded to a multiple of 4 floats (+ slack): always readable
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float* src = parts + i4;
+    for (int base = sl; base < n_parts; base += 10 * kAdamSlices) {
+        float4 t[10];
+#pragma unroll
+        for (int k = 0; k < 10; ++k) {
+            const int sidx = base + kAdamSlices * k;
+            t[k] = sidx < n_parts ? ldcg4(src + (long)sidx * part_stride) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        g.x += (((t[0].x + t[1].x) + (t[2].x + t[3].x)) + ((t[4].x + t[5].x) + (t[6].x + t[7].x))) + (t[8].x + t[9].x);
+        g.y += (((t[0].y + t[1].y) + (t[2].y + t[3].y)) + ((t[4].y + t[5].y) + (t[6].y + t[7].y))) + (t[8].y + t[9].y);
+        g.z += (((t[0].z + t[1].z) + (t[2].z + t[3].z)) + ((t[4].z + t[5].z) + (t[6].z + t[7].z))) + (t[8].z + t[9].z);
+        g.w += (((t[0].w + t[1].w) + (t[2].w + t[3].w)) + ((t[4].w + t[5].w) + (t[6].w + t[7].w))) + (t[8].w + t[9].w);
+    }
+    *reinterpret_cast<float4*>(&red[sl][4 * cx]) = g;
+    __syncthreads();
+    const int t = threadIdx.x;
+    return t < kAdamCols ? ((red[0][t] + red[1][t]) + (red[2][t] + red[3][t])) + ((red[4][t] + red[5][t]) + (red[6][t] + red[7][t])) : 0.f;
+}
+
+__global__ void __launch_bounds__(kAdamThreads, 2) adam_img_kernel(AdamImgArgs a) {
+    __shared__ __align__(16) float red[kAdamSlices][kAdamCols];
     // programmatic dependent launch (no-ops otherwise): let the next training kernel begin its set-up, then wait for
     // the kernel that produced the partial gradients
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    const int tx = threadIdx.x & (kAdamCols - 1), ty = threadIdx.x / kAdamCols;
-    const long i = (long)blockIdx.x * kAdamCols + tx;
-    const bool in = i < a.n;
+    const long i = (long)blockIdx.x * kAdamCols + threadIdx.x;
+    const bool in = threadIdx.x < kAdamCols && i < a.n;
     float g = 0.f;
-    if (a.parts) {
-        if (in) {
-            const float* src = a.parts + i;
-            for (int base = ty; base < a.n_parts; base += 10 * kAdamSlices) {
-                float t[10];
-#pragma unroll
-                for (int k = 0; k < 10; ++k) {
-                    const int sidx = base + kAdamSlices * k;
-                    t[k] = sidx < a.n_parts ? __ldcg(src + (long)sidx * a.part_stride) : 0.f;
-                }
-                g += (((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]))) + (t[8] + t[9]);
-            }
-        }
-        red[ty][tx] = g;
-        __syncthreads();
-        if (ty == 0) g = ((red[0][tx] + red[1][tx]) + (red[2][tx] + red[3][tx])) + ((red[4][tx] + red[5][tx]) + (red[6][tx] + red[7][tx]));
-    }
-    if (ty != 0 || !in) return;
+    if (a.parts) g = reduce_parts(a.parts, a.n_parts, a.part_stride, red);
+    if (!in) return;
     float th = a.theta[i];
     if (a.parts || a.grad_in) {
         if (a.parts) { if (a.grad_out) a.grad_out[i] = g; }

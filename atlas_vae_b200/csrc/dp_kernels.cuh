@@ -1,9 +1,9 @@
 // Data-parallel update over NVLink peer memory: ONE kernel replaces "sum the partial slices" +
 // ncclAllReduce(SUM) + "clip_values + Adam" of the NCCL path.
-//   phase 1  block b sums this rank's partial-gradient slices for its 128 parameters (fixed order) and stores the result
+//   phase 1  block b sums this rank's partial-gradient slices for its 256 parameters (fixed order, adam_kernels.cuh) and stores the result
 //            in the rank's exchange buffer, then pushes sequence number `seq` into flag [rank][b] of EVERY peer (P2P store);
 //   phase 2  it waits until flags [q][b] of all peers q have reached `seq` (they are written into LOCAL memory by the
-//            peers), reads the same 128 values from every peer's exchange buffer (P2P loads), adds the ranks in rank
+//            peers), reads the same 256 values from every peer's exchange buffer (P2P loads), adds the ranks in rank
 //            order -- every rank computes bit-identical sums, so the replicas stay bit-identical -- and applies
 //            clip_values (models.py:185) + Keras Adam (models.py:138,186) + the bf16 weight-image refresh.
 // Nothing is grid-wide: a block depends only on block b of each peer.  All blocks of the launch must be co-resident
@@ -14,10 +14,11 @@
 #pragma once
 #include "common.cuh"
 #include "umma.cuh"
+#include "adam_kernels.cuh"
 
 namespace oevae {
 
-constexpr int kDpCols = 128, kDpSlices = 4, kDpMaxWorld = 8;   // 573 blocks at cfg-2: one co-resident wave of 512-thread blocks
+constexpr int kDpMaxWorld = 8;               // blocks: ceil(P / kAdamCols) of kAdamThreads threads -- 287 at cfg-2, one co-resident wave
 
 struct DpArgs {
     const float* parts; int n_parts; long part_stride;
@@ -32,40 +33,26 @@ struct DpArgs {
     float* gsum_out;                         // nullable [n]: SUM over ranks before clip_values (parity checks)
 };
 
-__global__ void __launch_bounds__(kDpCols * kDpSlices, 4) dp_adam_kernel(DpArgs a) {
-    __shared__ float red[kDpSlices][kDpCols + 1];
-    asm volatile("griddepcontrol.wait;" ::: "memory");      // PDL: the training kernel's partial slices are complete
-    const int tx = threadIdx.x & (kDpCols - 1), ty = threadIdx.x / kDpCols;
-    const long i = (long)blockIdx.x * kDpCols + tx;
-    const bool in = i < a.n;
+__global__ void __launch_bounds__(kAdamThreads, 2) dp_adam_kernel(DpArgs a) {
+    __shared__ __align__(16) float red[kAdamSlices][kAdamCols];
+    // PDL: the next step's training kernel may begin its set-up (barriers, TMEM, zeroed tiles, X prefetch) on the SMs this kernel's
+    // blocks leave; it orders itself behind this grid with griddepcontrol.wait.  Dependents are released only once EVERY block of
+    // this grid has started, so a waiting block can never be kept off the chip by them.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");      // the training kernel's partial slices are complete
+    const long i = (long)blockIdx.x * kAdamCols + threadIdx.x;
+    const bool in = threadIdx.x < kAdamCols && i < a.n;
     // the update's own operands do not depend on the exchange: their loads fly during phase 1
     float th0 = 0.f, m0 = 0.f, v0 = 0.f;
     int p0 = -1, p1 = -1, p2 = -1, p3 = -1;
-    if (ty == 0 && in) {
+    if (in) {
         th0 = a.theta[i]; m0 = a.m[i]; v0 = a.v[i];
         if (a.wimg) { p0 = a.pos[i]; p1 = a.pos[a.n + i]; p2 = a.pos[2 * a.n + i]; p3 = a.pos[3 * a.n + i]; }
     }
-    float g = 0.f;
-    if (in) {
-        const float* src = a.parts + i;
-        for (int base = ty; base < a.n_parts; base += 10 * kDpSlices) {
-            float t[10];
-#pragma unroll
-            for (int k = 0; k < 10; ++k) {
-                const int sidx = base + kDpSlices * k;
-                t[k] = sidx < a.n_parts ? __ldcg(src + (long)sidx * a.part_stride) : 0.f;
-            }
-            g += (((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]))) + (t[8] + t[9]);
-        }
-    }
-    red[ty][tx] = g;
+    const float g = reduce_parts(a.parts, a.n_parts, a.part_stride, red);
+    if (in) __stcg(a.my_gred + i, g);
     __syncthreads();
-    if (ty == 0) {
-        g = (red[0][tx] + red[1][tx]) + (red[2][tx] + red[3][tx]);
-        if (in) __stcg(a.my_gred + i, g);
-    }
-    __syncthreads();
-    // ---- publish: this block's 128 sums are visible system-wide before any peer sees the flag
+    // ---- publish: this block's sums are visible system-wide before any peer sees the flag
     // (st.release.sys is cumulative over the block's stores ordered before it by the barrier above)
     if (threadIdx.x < a.world && (int)threadIdx.x != a.rank) {
         unsigned int* f = a.peer_flags[threadIdx.x] + (long)a.rank * gridDim.x + blockIdx.x;
@@ -82,7 +69,7 @@ __global__ void __launch_bounds__(kDpCols * kDpSlices, 4) dp_adam_kernel(DpArgs 
         } while ((int)(seen - a.seq) < 0);
     }
     __syncthreads();
-    if (ty != 0 || !in) return;
+    if (!in) return;
     float tq[kDpMaxWorld];
 #pragma unroll
     for (int q = 0; q < kDpMaxWorld; ++q) {                  // all peers' loads in flight together

@@ -176,7 +176,7 @@ int Engine::refresh_images(cudaStream_t s) {
     if (!f.img_dirty) return 0;
     AdamImgArgs ai{};
     ai.theta = theta; ai.n = P; ai.wimg = f.wimg; ai.pos = f.pos;
-    { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, kAdamCols), kAdamCols * kAdamSlices, 0, s>>>(ai); }
+    { PROF("weight_images", s); adam_img_kernel<<<cdiv(P, kAdamCols), kAdamThreads, 0, s>>>(ai); }
     CKL();
     f.img_dirty = false;
     return 0;
@@ -573,7 +573,7 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
         ai.theta = theta; ai.m = m; ai.v = v; ai.n = P;
         ai.alpha = a.alpha; ai.b1 = a.b1; ai.b2 = a.b2; ai.eps = a.eps; ai.apply = apply;
         ai.wimg = fz->wimg; ai.pos = fz->pos;
-        { PROF("adam", s); CK(launch_pdl(adam_img_kernel, dim3((unsigned)cdiv(P, kAdamCols)), dim3(kAdamCols * kAdamSlices), 0, s, ai)); }
+        { PROF("adam", s); CK(launch_pdl(adam_img_kernel, dim3((unsigned)cdiv(P, kAdamCols)), dim3(kAdamThreads), 0, s, ai)); }
         CKL();
         if (apply) fz->img_dirty = false;
         return 0;
@@ -589,7 +589,7 @@ static size_t dp_bytes(long Ppad, int nblk) { return (size_t)2 * Ppad * sizeof(f
 int Engine::dp_export(void* handle_out) {
     if (!handle_out) return fail(OEVAE_EINVAL, "dp_export: null handle");
     if (!dp_buf) {
-        dp_nblk = (int)cdiv(P, kDpCols);
+        dp_nblk = (int)cdiv(P, kAdamCols);
         CK(cudaMalloc(&dp_buf, dp_bytes(Ppad, dp_nblk)));
         CK(cudaMemset(dp_buf, 0, dp_bytes(Ppad, dp_nblk)));
         CK(cudaDeviceSynchronize());
@@ -602,7 +602,7 @@ int Engine::dp_connect(int rank, int world, const void* handles) {
     if (!dp_buf) return fail(OEVAE_EINVAL, "dp_connect before dp_export");
     if (world < 2 || world > kDpMaxWorld || rank < 0 || rank >= world || !handles) return fail(OEVAE_EINVAL, "dp_connect: bad rank/world");
     int per_sm = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dp_adam_kernel, kDpCols * kDpSlices, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dp_adam_kernel, kAdamThreads, 0));
     if ((long)per_sm * n_sm < dp_nblk)                      // all blocks must be co-resident (see dp_kernels.cuh)
         return fail(OEVAE_EUNSUPPORTED, "dp: %d blocks exceed the %d resident blocks of this GPU; use the all-reduce path", dp_nblk, per_sm * n_sm);
     const cudaIpcMemHandle_t* hs = reinterpret_cast<const cudaIpcMemHandle_t*>(handles);
@@ -640,7 +640,7 @@ int Engine::dp_update(float lr, bool have_grad, cudaStream_t s) {
     a.alpha = (float)((double)lr * std::sqrt(1.0 - std::pow(0.999, t)) / (1.0 - std::pow(0.9, t)));
     a.b1 = 0.9f; a.b2 = 0.999f; a.eps = 1e-7f;
     if (fz) { a.wimg = fz->wimg; a.pos = fz->pos; }
-    { PROF("dp_adam", s); CK(launch_pdl(dp_adam_kernel, dim3((unsigned)dp_nblk), dim3(kDpCols * kDpSlices), 0, s, a)); }
+    { PROF("dp_adam", s); CK(launch_pdl(dp_adam_kernel, dim3((unsigned)dp_nblk), dim3(kAdamThreads), 0, s, a)); }
     CKL();
     if (fz) fz->img_dirty = false;
     return 0;
@@ -1338,6 +1338,43 @@ int oevae_roc(const float* score, const uint8_t* y_true, int32_t pos_label, cons
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return done(OEVAE_ECUDA, cudaGetErrorString(e));
     return done(0, "");
+}
+
+// argsort of a float32 vector (ascending, stable) on the device: the m-sort of OoD_pairing (utils.py:195-196)
+int oevae_argsort_f32(const float* v, int64_t N, int64_t* order_out, int32_t device, void* stream) {
+    using namespace roc;
+    if (!v || !order_out || N <= 0 || N >= (1ll << 31)) { g_create_error = "argsort: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const long n = N; const unsigned nt = cdiv(n, kTile);
+    RocWs ws; ws.cap = (size_t)n * 16 + (size_t)256 * nt * 4 + (size_t)nt * 8 + (1 << 16);
+    rc = free_fail(cudaMalloc(&ws.base, ws.cap), "argsort workspace"); if (rc) return rc;
+    uint32_t* k0 = ws.take<uint32_t>(n); uint32_t* k1 = ws.take<uint32_t>(n); uint32_t* v0 = ws.take<uint32_t>(n); uint32_t* v1 = ws.take<uint32_t>(n);
+    uint32_t* hist = ws.take<uint32_t>((size_t)256 * nt); uint32_t* tiles = ws.take<uint32_t>(nt + 64);
+    asc_keys_kernel<<<cdiv(n, 256), 256, 0, s>>>(v, n, k0, v0); LAUNCHED();
+    uint32_t *kin = k0, *kout = k1, *vin = v0, *vout = v1;
+    for (int shift = 0; shift < 32; shift += 8) {
+        rs_hist_kernel<<<nt, kThreads, 0, s>>>(kin, n, shift, hist, (int)nt); LAUNCHED();
+        roc_scan(hist, hist, 256L * nt, tiles, nullptr, s);
+        rs_scatter_kernel<<<nt, kThreads, 0, s>>>(kin, vin, kout, vout, n, shift, hist, (int)nt); LAUNCHED();
+        std::swap(kin, kout); std::swap(vin, vout);
+    }
+    widen_idx_kernel<<<cdiv(n, 256), 256, 0, s>>>(vin, n, reinterpret_cast<long long*>(order_out)); LAUNCHED();
+    cudaError_t e = cudaStreamSynchronize(s);
+    cudaFree(ws.base);
+    return free_fail(e, "argsort");
+}
+
+int oevae_ood_pairing(const float* m_bkg, const float* pt_bkg, int64_t n_bkg, const float* m_ood_sorted, const float* pt_ood_sorted, int64_t n_ood,
+                      uint64_t seed, int32_t pick_first, int64_t* idx_out, float* widths_out, int32_t device, void* stream) {
+    if (n_bkg == 0) return 0;
+    if (!m_bkg || !pt_bkg || !m_ood_sorted || !pt_ood_sorted || !idx_out || n_bkg < 0 || n_ood <= 0) { g_create_error = "ood_pairing: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    { PROF("ood_pairing", (cudaStream_t)stream);
+      pair::ood_pairing_kernel<<<cdiv(n_bkg * 32, 256), 256, 0, (cudaStream_t)stream>>>(m_bkg, pt_bkg, n_bkg, m_ood_sorted, pt_ood_sorted, n_ood, seed, pick_first,
+                                                                                       reinterpret_cast<long long*>(idx_out), widths_out); }
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "ood_pairing launch");
 }
 
 int oevae_roc_cuts(const double* fpr, const double* tpr, const double* thr, int64_t n_points, const double* eff_host, int32_t n_eff,

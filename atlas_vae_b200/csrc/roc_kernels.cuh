@@ -153,6 +153,16 @@ __global__ void __launch_bounds__(kThreads) rs_scatter_kernel(const uint32_t* __
     }
 }
 
+// ascending keys for a plain argsort (payload = index), and the uint32 -> int64 widening of the sorted payload
+__global__ void asc_keys_kernel(const float* __restrict__ v, long n, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { keys[i] = orderable(v[i]); vals[i] = (uint32_t)i; }
+}
+__global__ void widen_idx_kernel(const uint32_t* __restrict__ in, long n, long long* __restrict__ out) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = (long long)in[i];
+}
+
 // ================================================================================================ ROC stages
 // flags[i] = weight != 0 (sklearn drops zero-weight samples before sorting)
 __global__ void nonzero_flag_kernel(const float* __restrict__ w, long n, uint32_t* __restrict__ flags) {
@@ -340,4 +350,67 @@ __global__ void roc_searchsorted_kernel(const double* __restrict__ fpr, const do
 }
 
 }  // namespace roc
+
+// ================================================================================================ OoD <-> background pairing
+// OoD_pairing (OE-VAE/utils.py:193-227): every background jet is paired with ONE out-of-distribution jet drawn uniformly from the OoD
+// jets inside an (m, pT) window around it -- m in [m - wm/2, m + wm/2) on the m-SORTED OoD sample (two np.searchsorted, side 'left'),
+// pT in [pT - wp/2, pT + wp/2] -- starting at 10 x 10 GeV and doubling the pT width, then the m width, alternately, until the window
+// is not empty (utils.py:203-210, same order).  One warp per background jet: the lanes scan the m-window of the sorted pT array
+// (coalesced), count the matches, then fetch the k-th one with k = floor(u * count), u from Philox4x32-10 keyed by (seed, jet).
+// The reference draws with np.random.choice under fork(), which cannot be reproduced; the candidate SET is identical (tested against
+// the reference's own function body) and the draw is uniform over it.
+namespace pair {
+
+__device__ __forceinline__ long lower_bound_f(const float* __restrict__ a, long n, double v) {   // np.searchsorted(a, v) (side 'left'), float32 a vs float64 v
+    long lo = 0, hi = n;
+    while (lo < hi) { const long mid = (lo + hi) >> 1; if ((double)a[mid] < v) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+
+__global__ void __launch_bounds__(256) ood_pairing_kernel(const float* __restrict__ m_bkg, const float* __restrict__ pt_bkg, long n_bkg,
+                                                          const float* __restrict__ m_ood, const float* __restrict__ pt_ood, long n_ood,
+                                                          unsigned long long seed, int pick_first, long long* __restrict__ idx_out,
+                                                          float* __restrict__ widths_out /* nullable [n_bkg][2] */) {
+    const long jet = ((long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (jet >= n_bkg) return;
+    // the widths are Python floats in the reference (10 -> 20.0 -> ...): float64 arithmetic on float32 jet values
+    const double mv = (double)m_bkg[jet], pv = (double)pt_bkg[jet];
+    double wm = 10.0, wp = 10.0;
+    long i0 = 0, i1 = 0; int cnt = 0;
+    for (int it = 0; it < 4096; ++it) {                                  // widths double: 4096 rounds never happen on finite inputs
+        i0 = lower_bound_f(m_ood, n_ood, mv - wm / 2); i1 = lower_bound_f(m_ood, n_ood, mv + wm / 2);
+        const double plo = pv - wp / 2, phi = pv + wp / 2;
+        int c = 0;
+        for (long i = i0 + lane; i < i1; i += 32) { const double p = (double)pt_ood[i]; c += (p >= plo && p <= phi) ? 1 : 0; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        cnt = c;
+        if (cnt > 0) break;
+        if ((it & 1) == 0) wp *= 2; else wm *= 2;                        // pT first, then m (utils.py:206,209)
+    }
+    if (cnt == 0) { if (lane == 0) idx_out[jet] = -1; return; }           // empty OoD sample (the reference would loop forever)
+    // k-th match, k uniform in [0, cnt)
+    u32x4 r = philox4x32_10(u32x4{(uint32_t)jet, (uint32_t)((unsigned long long)jet >> 32), 0x0f1u, 0u}, (uint32_t)seed, (uint32_t)(seed >> 32));
+    int k = pick_first ? 0 : (int)(((unsigned long long)r.x * (unsigned long long)cnt) >> 32);
+    const double plo = pv - wp / 2, phi = pv + wp / 2;
+    long found = -1;
+    for (long base = i0; base < i1 && found < 0; base += 32) {
+        const long i = base + lane;
+        const bool hit = i < i1 && (double)pt_ood[i] >= plo && (double)pt_ood[i] <= phi;
+        const unsigned mask = __ballot_sync(0xffffffffu, hit);
+        const int c = __popc(mask);
+        if (k < c) {                                                      // the k-th set bit of mask
+            unsigned mm = mask;
+            for (int t = 0; t < k; ++t) mm &= mm - 1;
+            found = base + (__ffs(mm) - 1);
+        } else k -= c;
+    }
+    if (lane == 0) {
+        idx_out[jet] = found;
+        if (widths_out) { widths_out[2 * jet] = (float)wm; widths_out[2 * jet + 1] = (float)wp; }
+    }
+}
+
+}  // namespace pair
 }  // namespace oevae

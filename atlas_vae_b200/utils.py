@@ -6,6 +6,8 @@
   loss_function   utils.py:346-375      latent_loss     utils.py:378-386      filtering   utils.py:532-538
   get_idx         utils.py:541-548
   QuantileTransformer / PowerTransformer apply (utils.py:393-396,411) on the device: scaler_kernels.cuh
+  OoD_pairing     utils.py:193-227 on the device (m-sort + windowed uniform draw)      OoD_sampling   utils.py:184-190
+  reweight_sample / get_weights   utils.py:230-274 (per-load host statistics on <= 10^3 bins, NumPy as in the reference)
 HDF5 loading (utils.py:36-130) needs h5py, which this image does not have.
 """
 import pickle
@@ -224,3 +226,85 @@ def get_idx(max_val, n_bins=10, bin_size=None, min_val=0, integer=True, tuples=T
     if integer: idx_list = np.int_(idx_list)
     if tuples: return list(zip(idx_list[:-1], idx_list[1:]))
     return idx_list
+
+
+# ------------------------------------------------------------------------------------------------ sample assembly (before training)
+def OoD_sampling(bkg_sample, OoD_sample, adjust_weights=False, seed=None):
+    """utils.py:184-190: resample the OoD sample to the background's size (host NumPy, as in the reference)."""
+    np.random.seed(seed)
+    source_size = len(list(OoD_sample.values())[0])
+    target_size = len(list(bkg_sample.values())[0])
+    indices = np.random.choice(source_size, target_size, replace=source_size < target_size)
+    if adjust_weights: OoD_sample['weights'] = OoD_sample['weights'] * np.float32(source_size / target_size)
+    return {key: np.take(OoD_sample[key], indices, axis=0) for key in OoD_sample}
+
+
+def OoD_pairing(bkg_sample, OoD_sample, multithread=True, verbose=True, seed=0, pick_first=False, return_indices=False):
+    """utils.py:193-227 on the device: the OoD sample is sorted by mass (radix argsort) and every background jet gets one OoD jet drawn
+    uniformly from the (m, pT) window around it -- 10 x 10 GeV, doubled alternately in pT and in m until it is not empty (utils.py:
+    198-210).  `multithread` is accepted for compatibility (the reference forks 16 processes; here one warp per background jet).
+    The draw is Philox4x32-10 keyed by (seed, jet): np.random.choice under fork() cannot be reproduced, the candidate sets are the
+    reference's (tests/test_gpu_pairing.py against its own function body).  Returns the paired OoD sample, row-aligned with bkg_sample."""
+    import ctypes as C
+    import time
+    dev = _dev()
+    t0 = time.time()
+    if verbose: print('Pairing OoD with QCD', end=' ', flush=True)
+    m_o, pt_o = _to_dev(OoD_sample['m'], dev), _to_dev(OoD_sample['pt'], dev)
+    n_o = m_o.numel()
+    order = torch.empty(n_o, dtype=torch.int64, device=dev)
+    check(_ffi.lib().oevae_argsort_f32(ptr(m_o), n_o, ptr(order), dev.index, _stream()))
+    m_s, pt_s = m_o[order].contiguous(), pt_o[order].contiguous()
+    m_b, pt_b = _to_dev(bkg_sample['m'], dev), _to_dev(bkg_sample['pt'], dev)
+    n_b = m_b.numel()
+    idx = torch.empty(n_b, dtype=torch.int64, device=dev)
+    check(_ffi.lib().oevae_ood_pairing(ptr(m_b), ptr(pt_b), n_b, ptr(m_s), ptr(pt_s), n_o, int(seed) & (2 ** 64 - 1), 1 if pick_first else 0,
+                                       ptr(idx), None, dev.index, _stream()))
+    take = order[idx.clamp_min(0)].cpu().numpy()                            # indices into the caller's (unsorted) OoD arrays
+    if bool((idx < 0).any()): raise ValueError('OoD_pairing: empty OoD sample')
+    if verbose: print('(', '\b' + format(time.time() - t0, '2.1f'), '\b' + ' s)')
+    if return_indices: return take
+    return {key: np.take(OoD_sample[key], take, axis=0) for key in OoD_sample}
+
+
+def get_weights(bkg_sample, sig_sample, bin_sizes, weight_type, max_val=1e4, density=True):
+    """utils.py:253-274: (m, pT)-histogram ratio weights.  A per-load host statistic on <= 10^3 bins: NumPy's own histogram2d /
+    digitize, as in the reference."""
+    m_size, pt_size = bin_sizes['m'], bin_sizes['pt']
+    m_bkg, pt_bkg, weights_bkg = [bkg_sample[key] for key in ['m', 'pt', 'weights']]
+    m_sig, pt_sig, weights_sig = [sig_sample[key] for key in ['m', 'pt', 'weights']]
+    m_min, pt_min = np.min(m_sig), np.min(pt_sig)
+    m_max, pt_max = np.max(m_sig), np.max(pt_sig)
+    if 'm' in weight_type: pt_size = pt_max + 1
+    if 'pt' in weight_type: m_size = m_max + 1
+    m_bins = get_idx(m_max, bin_size=m_size, min_val=m_min, integer=False, tuples=False)
+    pt_bins = get_idx(pt_max, bin_size=pt_size, min_val=pt_min, integer=False, tuples=False)
+    m_idx = np.clip(np.digitize(m_sig, m_bins, right=False), 1, len(m_bins) - 1) - 1
+    pt_idx = np.clip(np.digitize(pt_sig, pt_bins, right=False), 1, len(pt_bins) - 1) - 1
+    hist_sig = np.histogram2d(m_sig, pt_sig, bins=[m_bins, pt_bins], density=density)[0]
+    if density: hist_sig *= len(m_sig)
+    hist_sig = np.maximum(hist_sig, np.min(hist_sig[hist_sig != 0]) if density else 1)
+    if 'flat' in weight_type:
+        weights = (1 / hist_sig)[m_idx, pt_idx]
+        return weights * np.sum(weights_sig) / np.sum(weights)
+    hist_bkg = np.histogram2d(m_bkg, pt_bkg, bins=[m_bins, pt_bins], weights=weights_bkg, density=density)[0]
+    if density: hist_bkg *= len(m_bkg)
+    weights = (hist_bkg / hist_sig)[m_idx, pt_idx]
+    return np.minimum(max_val, weights * np.sum(weights_bkg) / np.sum(weights))
+
+
+def reweight_sample(bkg_sample, sig_sample, bin_sizes, weight_type='X-S'):
+    """utils.py:230-250: None / X-S / flat_m / flat_pt / flat_2d / OoD_m / OoD_pt / OoD_2d (same branches, same order)."""
+    if weight_type is None or weight_type.lower() == 'none':
+        sig_sample['weights'] = np.ones_like(sig_sample['weights'])
+        bkg_sample['weights'] = np.ones_like(bkg_sample['weights'])
+        weight_type = 'none'
+    if 'flat' in weight_type:
+        sig_sample['weights'] = get_weights(bkg_sample, sig_sample, bin_sizes, weight_type)
+        bkg_sample['weights'] = get_weights(bkg_sample, bkg_sample, bin_sizes, weight_type)
+        sig_sample['weights'] = get_weights(bkg_sample, sig_sample, bin_sizes, weight_type='2d')
+    if 'OoD' in weight_type:
+        sig_sample['weights'] = get_weights(bkg_sample, sig_sample, bin_sizes, weight_type)
+    if weight_type == 'X-S':
+        sig_sample['weights'] *= np.sum(bkg_sample['weights']) / np.sum(sig_sample['weights'])
+    return bkg_sample, sig_sample

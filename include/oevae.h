@@ -228,6 +228,17 @@ OEVAE_API int oevae_roc_cuts(const double* fpr, const double* tpr, const double*
 OEVAE_API int oevae_roc_searchsorted(const double* fpr, const double* thr, int64_t n_points, const double* eff_host, int32_t n_q,
                            double* thr_out_host, double* eff_out_host, int32_t device, void* stream);
 
+/* ---- OoD <-> background pairing (the step right before training, OE-VAE/utils.py:193-227) -------------------------------------
+ * oevae_argsort_f32: np.argsort(OoD_sample['m']) (utils.py:195; stable) -> order_out int64 [N] (device).
+ * oevae_ood_pairing: for every background jet, the index (into the m-SORTED OoD arrays) of one OoD jet drawn uniformly from the
+ *   (m, pT) window around it, the window widened x2 alternately in pT and in m, starting at 10 x 10 GeV, until it is not empty
+ *   (utils.py:198-210).  Draw: Philox4x32-10 keyed by (seed, jet) -- the reference's np.random.choice stream under fork() is not
+ *   reproducible; pick_first != 0 returns the first candidate instead (tests).  widths_out: nullable float [n_bkg][2] = final
+ *   (m_width, pt_width).  idx_out int64 [n_bkg] (device). */
+OEVAE_API int oevae_argsort_f32(const float* v, int64_t N, int64_t* order_out, int32_t device, void* stream);
+OEVAE_API int oevae_ood_pairing(const float* m_bkg, const float* pt_bkg, int64_t n_bkg, const float* m_ood_sorted, const float* pt_ood_sorted,
+                      int64_t n_ood, uint64_t seed, int32_t pick_first, int64_t* idx_out, float* widths_out, int32_t device, void* stream);
+
 /* ---- train_model's batch loop over one HOST-resident load (models.py:172-190), one call per group of batches ----------------
  * Replaces the implicit per-step host->device copies of models.py:180-182: batches [first_batch, first_batch + n_batches) of
  * `batch_size` rows are copied host->device on an internal copy stream, up to five batches ahead of the compute stream, and stepped with
