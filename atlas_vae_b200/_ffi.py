@@ -78,6 +78,8 @@ SIGNATURES = {
     'oevae_loss_map': (C.c_int, [_vp, _i64, _i32, _i32, _vp]),
     'oevae_hist': (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _f32, _vp, _i32, _f32, _i32, _vp, _vp, _i32, _vp]),
     'oevae_wsum': (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp]),
+    'oevae_digitize_count': (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _i32, _vp]),
+    'oevae_mass_deco': (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _i32, _vp, _vp, _i32, _vp]),
     'oevae_argsort_f32': (C.c_int, [_vp, _i64, _vp, _i32, _vp]),
     'oevae_ood_pairing': (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, C.c_uint64, _i32, _vp, _vp, _i32, _vp]),
     'oevae_roc': (C.c_int, [_vp, _vp, _i32, _vp, _i64, _vp, _vp, _vp, C.POINTER(_i64), _i32, _vp]),
@@ -90,6 +92,7 @@ SIGNATURES = {
     'oevae_profile_report': (C.c_int, [C.c_char_p, _i32]),
 }
 TEST_SIGNATURES = {
+    'oevae_dp_stamps_host': (C.c_int, [_vp, _vp, _i64]),
     'oevae_gemm': (C.c_int, [_vp, _i32, _vp, _i64, _i64, _vp, _i64, _i64, _vp, _i32, _i32, _i32, _i32, _vp, _i32, _vp]),
     'oevae_probe_mn': (C.c_int, [_vp, _vp, _i32, _i32, _i32, _vp, _i32, _vp]),
     'oevae_probe_latency': (C.c_int, [_i32, _i32, C.POINTER(_i64), _i32]),

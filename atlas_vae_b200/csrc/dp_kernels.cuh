@@ -31,6 +31,8 @@ struct DpArgs {
     float alpha, b1, b2, eps;
     unsigned char* wimg; const int* pos;
     float* gsum_out;                         // nullable [n]: SUM over ranks before clip_values (parity checks)
+    long long* stamps;                       // nullable [gridDim.x][6] globaltimer ns (OEVAE_DP_STAMPS=1): entry, dependency met, local sum published,
+                                             // all peer flags seen, peer loads done, exit
 };
 
 __global__ void __launch_bounds__(kAdamThreads, 2) dp_adam_kernel(DpArgs a) {
@@ -38,8 +40,11 @@ __global__ void __launch_bounds__(kAdamThreads, 2) dp_adam_kernel(DpArgs a) {
     // PDL: the next step's training kernel may begin its set-up (barriers, TMEM, zeroed tiles, X prefetch) on the SMs this kernel's
     // blocks leave; it orders itself behind this grid with griddepcontrol.wait.  Dependents are released only once EVERY block of
     // this grid has started, so a waiting block can never be kept off the chip by them.
+    auto stamp = [&](int k) { if (a.stamps && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); a.stamps[6 * blockIdx.x + k] = (long long)t; } };
+    stamp(0);
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");      // the training kernel's partial slices are complete
+    stamp(1);
     const long i = (long)blockIdx.x * kAdamCols + threadIdx.x;
     const bool in = threadIdx.x < kAdamCols && i < a.n;
     // the update's own operands do not depend on the exchange: their loads fly during phase 1
@@ -58,6 +63,7 @@ __global__ void __launch_bounds__(kAdamThreads, 2) dp_adam_kernel(DpArgs a) {
         unsigned int* f = a.peer_flags[threadIdx.x] + (long)a.rank * gridDim.x + blockIdx.x;
         asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(a.seq) : "memory");
     }
+    stamp(2);
     // ---- wait for block blockIdx.x of every peer
     if (threadIdx.x < a.world && (int)threadIdx.x != a.rank) {
         const unsigned int* f = a.my_flags + (long)threadIdx.x * gridDim.x + blockIdx.x;
@@ -69,7 +75,8 @@ __global__ void __launch_bounds__(kAdamThreads, 2) dp_adam_kernel(DpArgs a) {
         } while ((int)(seen - a.seq) < 0);
     }
     __syncthreads();
-    if (!in) return;
+    stamp(3);
+    if (!in) { return; }
     float tq[kDpMaxWorld];
 #pragma unroll
     for (int q = 0; q < kDpMaxWorld; ++q) {                  // all peers' loads in flight together
@@ -79,6 +86,7 @@ __global__ void __launch_bounds__(kAdamThreads, 2) dp_adam_kernel(DpArgs a) {
     float gs = 0.f;
 #pragma unroll
     for (int q = 0; q < kDpMaxWorld; ++q) if (q < a.world) gs += (q == a.rank) ? g : tq[q];
+    stamp(4);
     if (a.gsum_out) a.gsum_out[i] = gs;
     gs = clipv(gs);
     float m = m0, v = v0;
@@ -95,6 +103,7 @@ __global__ void __launch_bounds__(kAdamThreads, 2) dp_adam_kernel(DpArgs a) {
         if (p2 >= 0) *reinterpret_cast<__nv_bfloat16*>(a.wimg + p2) = hi;
         if (p3 >= 0) *reinterpret_cast<__nv_bfloat16*>(a.wimg + p3) = lo;
     }
+    stamp(5);
 }
 
 }  // namespace oevae

@@ -31,7 +31,7 @@ struct Pass {
 //   OEVAE_SCORE_STATIC=1   round-robin tiles in the scoring pass                 OEVAE_SCORE_HEADS_T=1 scoring heads with the jets on the lanes
 //   OEVAE_FUSED_DBG=1      phase stamps of CTA 0 to stderr (synchronises)        OEVAE_DBG_SKIP=k      stamps from the k-th tile of CTA 0 on
 struct Knobs {
-    bool fused = true, oe_layered = false, score_layered = false, score_static = false, fused_dbg = false;
+    bool fused = true, oe_layered = false, score_layered = false, score_static = false, fused_dbg = false, dp_stamps = false;
     int fused_v = 3, score_heads_t = 0;
     long long dbg_skip = 0;
     void read_env();
@@ -62,6 +62,7 @@ struct Engine {
     // data-parallel exchange over NVLink peer memory (dp_kernels.cuh): [2][Ppad] reduced gradients + [8][dp_nblk] flags
     float* dp_buf = nullptr; void* dp_peer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     int dp_rank = -1, dp_world = 0, dp_nblk = 0; unsigned int dp_seq = 0;
+    long long* dp_stamps = nullptr;   // OEVAE_DP_STAMPS=1: per-block phase stamps of the last update kernel (oevae_dp_stamps_host)
     float* dp_gsum = nullptr;     // [P] SUM over ranks of the last step's gradient, before clip_values (parity checks: oevae_dp_last_grad_host)
 
     // host-load loop (oevae_train_batches_host): copy stream, per-slot events, staging ring of kHlSlots batches; the copies run

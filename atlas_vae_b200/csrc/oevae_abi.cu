@@ -63,6 +63,7 @@ void Knobs::read_env() {
     score_heads_t = (int)geti("OEVAE_SCORE_HEADS_T", 0);
     fused_dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
     dbg_skip = geti("OEVAE_DBG_SKIP", 0);
+    dp_stamps = geti("OEVAE_DP_STAMPS", 0) != 0;
 }
 
 int Engine::init(const oevae_config& c) {
@@ -120,6 +121,7 @@ Engine::~Engine() {
     if (theta) cudaFree(theta);
     if (arena) cudaFree(arena);
     if (dp_gsum) cudaFree(dp_gsum);
+    if (dp_stamps) cudaFree(dp_stamps);
     if (hl_ring) cudaFree(hl_ring);
     for (int k = 0; k < kHlSlots; ++k) { if (hl_ready[k]) cudaEventDestroy(hl_ready[k]); if (hl_freed[k]) cudaEventDestroy(hl_freed[k]); }
     if (hl_copy) cudaStreamDestroy(hl_copy);
@@ -611,6 +613,7 @@ int Engine::dp_connect(int rank, int world, const void* handles) {
         CK(cudaIpcOpenMemHandle(&dp_peer[q], hs[q], cudaIpcMemLazyEnablePeerAccess));
     }
     if (!dp_gsum) CK(cudaMalloc(&dp_gsum, Ppad * sizeof(float)));
+    if (knobs.dp_stamps && !dp_stamps) { CK(cudaMalloc(&dp_stamps, (size_t)dp_nblk * 6 * sizeof(long long))); CK(cudaMemset(dp_stamps, 0, (size_t)dp_nblk * 6 * sizeof(long long))); }
     dp_rank = rank; dp_world = world; dp_seq = 0;
     return 0;
 }
@@ -623,7 +626,7 @@ int Engine::dp_update(float lr, bool have_grad, cudaStream_t s) {
     if (!have_grad) { a.parts = fz ? fz->parts : parts; a.n_parts = 0; }
     else if (fz && fz->last_fused) { a.parts = fz->parts; a.n_parts = fz->last_grid; }
     else { a.parts = parts; a.n_parts = n_slots_used; }
-    a.gsum_out = dp_gsum;
+    a.gsum_out = dp_gsum; a.stamps = dp_stamps;
     a.part_stride = Ppad;
     ++step; ++dp_seq;
     const int b = (int)(dp_seq & 1u);
@@ -904,6 +907,18 @@ int roc_scan(const uint32_t* in, uint32_t* out, long n, uint32_t* tiles, uint32_
     scan_apply_kernel<<<nt, kThreads, 0, s>>>(in, n, tiles, out); LAUNCHED();
     return 0;
 }
+// stable LSD radix sort of (key, value) pairs by key, ascending; the sorted pairs end up in (k0, v0) (four ping-pong passes)
+void roc_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, long n, uint32_t* hist, uint32_t* tiles, cudaStream_t s) {
+    using namespace roc;
+    const unsigned nt = cdiv(n, kTile);
+    uint32_t *kin = k0, *kout = k1, *vin = v0, *vout = v1;
+    for (int shift = 0; shift < 32; shift += 8) {
+        rs_hist_kernel<<<nt, kThreads, 0, s>>>(kin, n, shift, hist, (int)nt); LAUNCHED();
+        roc_scan(hist, hist, 256L * nt, tiles, nullptr, s);
+        rs_scatter_kernel<<<nt, kThreads, 0, s>>>(kin, vin, kout, vout, n, shift, hist, (int)nt); LAUNCHED();
+        std::swap(kin, kout); std::swap(vin, vout);
+    }
+}
 }  // namespace
 
 // ================================================================================================ C ABI
@@ -1000,6 +1015,15 @@ int oevae_dp_last_grad_host(oevae_t h, float* grad_host, int64_t nn) {
     if (!grad_host || nn != e->P) return e->fail(OEVAE_EINVAL, "dp_last_grad: expected %ld floats", e->P);
     if (!e->dp_gsum) return e->fail(OEVAE_EINVAL, "dp_last_grad: not connected");
     return e->cuda_check(cudaMemcpy(grad_host, e->dp_gsum, nn * 4, cudaMemcpyDeviceToHost), "dp_last_grad");
+}
+
+int oevae_dp_stamps_host(oevae_t h, int64_t* out_host, int64_t cap) {
+    H(h);
+    if (!e->dp_stamps) return e->fail(OEVAE_EINVAL, "dp_stamps: set OEVAE_DP_STAMPS=1 before oevae_create and connect first");
+    const int64_t nn = std::min<int64_t>(cap, (int64_t)e->dp_nblk * 6);
+    if (!out_host || nn <= 0) return e->fail(OEVAE_EINVAL, "dp_stamps: bad arguments");
+    int rc = e->cuda_check(cudaMemcpy(out_host, e->dp_stamps, nn * sizeof(long long), cudaMemcpyDeviceToHost), "dp_stamps");
+    return rc ? rc : (int)(nn / 6);
 }
 
 int oevae_reset_opt_state(oevae_t h) { H(h); return e->reset_opt(); }
@@ -1375,6 +1399,54 @@ int oevae_ood_pairing(const float* m_bkg, const float* pt_bkg, int64_t n_bkg, co
                                                                                        reinterpret_cast<long long*>(idx_out), widths_out); }
     LAUNCHED();
     return free_fail(cudaGetLastError(), "ood_pairing launch");
+}
+
+int oevae_digitize_count(const float* var, const uint8_t* keep, int64_t N, const double* edges, int32_t n_edges, uint32_t* counts, int32_t device, void* stream) {
+    if (!edges || !counts || n_edges < 2 || N < 0 || (N > 0 && !var)) { g_create_error = "digitize_count: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    if (N == 0) return 0;
+    deco::digitize_count_kernel<<<std::min<unsigned>(cdiv(N, 256), 148 * 8), 256, 0, (cudaStream_t)stream>>>(var, keep, N, edges, n_edges, counts);
+    LAUNCHED();
+    return free_fail(cudaGetLastError(), "digitize_count launch");
+}
+
+// mass_deco's device half (plots.py:74-84): cells of all jets, background scores sorted by (cell, score), CDF evaluation in place
+int oevae_mass_deco(float* loss, const float* m, const float* pt, const uint8_t* is_bkg, int64_t N, const double* m_edges, int32_t n_m_edges,
+                    const double* pt_edges, const int32_t* pt_off, int32_t device, void* stream) {
+    using namespace roc;
+    if (!loss || !m || !pt || !is_bkg || !m_edges || !pt_edges || !pt_off || N <= 0 || N >= (1ll << 31) || n_m_edges < 2 || n_m_edges > 256) { g_create_error = "mass_deco: bad arguments"; return OEVAE_EINVAL; }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const long n = N; const unsigned nt = cdiv(n, kTile);
+    const int n_cells = 256 * 256;
+    RocWs ws; ws.cap = (size_t)n * (4 * 8 + 8 + 4) + (size_t)256 * nt * 4 + (size_t)nt * 8 + (size_t)n_cells * 8 + (1 << 16);
+    rc = free_fail(cudaMalloc(&ws.base, ws.cap), "mass_deco workspace"); if (rc) return rc;
+    uint32_t* cell = ws.take<uint32_t>(n); uint32_t* flags = ws.take<uint32_t>(n); uint32_t* posn = ws.take<uint32_t>(n);
+    uint32_t* k0 = ws.take<uint32_t>(n); uint32_t* k1 = ws.take<uint32_t>(n); uint32_t* v0 = ws.take<uint32_t>(n); uint32_t* v1 = ws.take<uint32_t>(n);
+    float* sorted = ws.take<float>(n);
+    uint32_t* hist = ws.take<uint32_t>((size_t)256 * nt); uint32_t* tiles = ws.take<uint32_t>(nt + 64);
+    uint32_t* ccount = ws.take<uint32_t>(n_cells + 1); uint32_t* ctiles = ws.take<uint32_t>(64); uint32_t* total = ws.take<uint32_t>(4);
+    auto done = [&](int code, const char* msg) { cudaStreamSynchronize(s); cudaFree(ws.base); if (code) g_create_error = msg; return code; };
+    const unsigned g256 = cdiv(n, 256);
+    deco::cell_index_kernel<<<g256, 256, 0, s>>>(m, pt, n, m_edges, n_m_edges, pt_edges, pt_off, cell); LAUNCHED();
+    // background jets: compact their indices, sort by score, then (stable) by cell
+    u8_flag_kernel<<<g256, 256, 0, s>>>(is_bkg, n, flags); LAUNCHED();
+    roc_scan(flags, posn, n, tiles, total, s);
+    uint32_t nb = 0;
+    if (cudaMemcpyAsync(&nb, total, 4, cudaMemcpyDeviceToHost, s) != cudaSuccess || cudaStreamSynchronize(s) != cudaSuccess) return done(OEVAE_ECUDA, "mass_deco: scan failed");
+    if (nb == 0) return done(OEVAE_EINVAL, "mass_deco: no background jet");
+    compact_score_keys_kernel<<<g256, 256, 0, s>>>(loss, n, flags, posn, k0, v0); LAUNCHED();
+    roc_sort_pairs(k0, v0, k1, v1, nb, hist, tiles, s);
+    gather_u32_kernel<<<cdiv(nb, 256), 256, 0, s>>>(v0, cell, nb, k0); LAUNCHED();                    // keys = cell of the score-sorted jets
+    roc_sort_pairs(k0, v0, k1, v1, nb, hist, tiles, s);
+    deco::gather_f32_kernel<<<cdiv(nb, 256), 256, 0, s>>>(v0, loss, nb, sorted); LAUNCHED();
+    cudaMemsetAsync(ccount, 0, (n_cells + 1) * sizeof(uint32_t), s);
+    deco::cell_count_kernel<<<cdiv(nb, 256), 256, 0, s>>>(k0, nb, ccount); LAUNCHED();
+    roc_scan(ccount, ccount, n_cells + 1, ctiles, nullptr, s);                                       // start[c] = #background jets in cells < c
+    deco::cdf_apply_kernel<<<g256, 256, 0, s>>>(loss, cell, n, sorted, ccount); LAUNCHED();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return done(OEVAE_ECUDA, cudaGetErrorString(e));
+    return done(0, "");
 }
 
 int oevae_roc_cuts(const double* fpr, const double* tpr, const double* thr, int64_t n_points, const double* eff_host, int32_t n_eff,

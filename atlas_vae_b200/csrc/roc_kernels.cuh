@@ -153,6 +153,20 @@ __global__ void __launch_bounds__(kThreads) rs_scatter_kernel(const uint32_t* __
     }
 }
 
+__global__ void u8_flag_kernel(const unsigned char* __restrict__ f, long n, uint32_t* __restrict__ flags) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[i] = f[i] ? 1u : 0u;
+}
+// flagged samples, compacted in order: keys = ascending image of the score, vals = sample index
+__global__ void compact_score_keys_kernel(const float* __restrict__ score, long n, const uint32_t* __restrict__ flags, const uint32_t* __restrict__ pos,
+                                          uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && flags[i]) { keys[pos[i]] = orderable(score[i]); vals[pos[i]] = (uint32_t)i; }
+}
+__global__ void gather_u32_kernel(const uint32_t* __restrict__ idx, const uint32_t* __restrict__ src, long n, uint32_t* __restrict__ dst) {
+    const long p = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) dst[p] = src[idx[p]];
+}
 // ascending keys for a plain argsort (payload = index), and the uint32 -> int64 widening of the sorted payload
 __global__ void asc_keys_kernel(const float* __restrict__ v, long n, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
     const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -413,4 +427,75 @@ __global__ void __launch_bounds__(256) ood_pairing_kernel(const float* __restric
 }
 
 }  // namespace pair
+
+// ================================================================================================ mass decorrelation
+// mass_deco (OE-VAE/plots.py:54-85): the score of every jet is replaced by its empirical CDF value among the BACKGROUND jets of the same
+// (mass, pT) cell, which flattens the score in every cell.  The bin construction (get_bins, plots.py:54-63: 100 log-spaced edges,
+// neighbouring bins merged until each holds >= 2 jets) is host logic on <= 100 counts; the device supplies the counts
+// (digitize_count_kernel), the cell of every jet (cell_index_kernel), the background scores sorted by (cell, score) (the radix sort
+// above, twice: LSD over the composite key) and the CDF evaluation (cdf_apply_kernel), which restates cum_distribution (plots.py:64-66:
+// np.unique + cumsum / len, a 0 prepended to values and counts) and scipy.interpolate.interp1d's linear rule
+//   y = ((y_hi - y_lo) / float64(x_hi -f32 x_lo)) * float64(x -f32 x_lo) + y_lo,   0 below the first value, 1 above the last
+// without materialising the per-cell unique arrays: inside the cell's sorted segment, pos = first score >= x gives x_hi, the end of
+// its run of ties gives y_hi = (#scores <= x_hi) / len, and pos itself gives x_lo (the previous score, or the prepended 0) and y_lo.
+namespace deco {
+
+// np.clip(np.digitize(x, edges), 1, len(edges) - 1) - 1   (digitize = searchsorted(edges, x, 'right'), float64 compare)
+__device__ __forceinline__ int clip_digitize(double x, const double* __restrict__ e, int ne) {
+    int lo = 0, hi = ne;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (e[mid] <= x) lo = mid + 1; else hi = mid; }
+    return min(max(lo, 1), ne - 1) - 1;
+}
+__global__ void digitize_count_kernel(const float* __restrict__ var, const unsigned char* __restrict__ keep, long n, const double* __restrict__ edges, int ne,
+                                      unsigned int* __restrict__ counts) {
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+        if (!keep || keep[i]) atomicAdd(&counts[clip_digitize((double)var[i], edges, ne)], 1u);
+}
+// cell = m_bin * 256 + pt_bin, the pT edges being those of the jet's mass bin (pt_off[m_bin] .. pt_off[m_bin + 1] in pt_edges)
+__global__ void cell_index_kernel(const float* __restrict__ m, const float* __restrict__ pt, long n, const double* __restrict__ m_edges, int n_me,
+                                  const double* __restrict__ pt_edges, const int* __restrict__ pt_off, uint32_t* __restrict__ cell) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int mi = clip_digitize((double)m[i], m_edges, n_me);
+    const int o = pt_off[mi], npe = pt_off[mi + 1] - o;
+    cell[i] = (uint32_t)(mi * 256 + clip_digitize((double)pt[i], pt_edges + o, npe));
+}
+__global__ void cell_count_kernel(const uint32_t* __restrict__ cell, long n, uint32_t* __restrict__ counts) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) atomicAdd(&counts[cell[i]], 1u);
+}
+// keys for the second (cell) pass of the composite sort: keys[p] = cell[order[p]], vals[p] = order[p]
+__global__ void gather_cell_keys_kernel(const long long* __restrict__ order, const uint32_t* __restrict__ cell, long n, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const long p = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) { const long long i = order[p]; keys[p] = cell[i]; vals[p] = (uint32_t)i; }
+}
+__global__ void gather_f32_kernel(const uint32_t* __restrict__ idx, const float* __restrict__ src, long n, float* __restrict__ dst) {
+    const long p = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) dst[p] = src[idx[p]];
+}
+// loss[i] <- CDF of its cell at loss[i]; sorted: background scores ordered by (cell, score); start[c] .. start[c + 1]: cell c's segment
+__global__ void cdf_apply_kernel(float* __restrict__ loss, const uint32_t* __restrict__ cell, long n, const float* __restrict__ sorted, const uint32_t* __restrict__ start) {
+    const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t c = cell[i];
+    const long s0 = start[c], s1 = start[c + 1], len = s1 - s0;
+    const float x = loss[i];
+    if (len <= 0) { loss[i] = NAN; return; }                              // no background jet in the cell (the reference raises)
+    const float last = sorted[s1 - 1];
+    if (x < 0.f) { loss[i] = 0.f; return; }                               // below values[0] = 0 (the prepended point)
+    if (x > fmaxf(last, 0.f)) { loss[i] = 1.f; return; }                  // above the last value
+    long lo = s0, hi = s1;                                                // pos = first index with sorted[pos] >= x
+    while (lo < hi) { const long mid = (lo + hi) >> 1; if (sorted[mid] < x) lo = mid + 1; else hi = mid; }
+    // (x > last was excluded, so pos < s1 unless every score is negative, which loss_mapping rules out)
+    const long pos = lo < s1 ? lo : s1 - 1;
+    const float x_hi = sorted[pos];
+    long l2 = pos, h2 = s1;                                               // end of the run of ties of x_hi
+    while (l2 < h2) { const long mid = (l2 + h2) >> 1; if (sorted[mid] <= x_hi) l2 = mid + 1; else h2 = mid; }
+    const float x_lo = pos > s0 ? sorted[pos - 1] : 0.f;
+    const double y_lo = __ddiv_rn((double)(pos - s0), (double)len), y_hi = __ddiv_rn((double)(l2 - s0), (double)len);
+    const double slope = __ddiv_rn(__dsub_rn(y_hi, y_lo), (double)__fsub_rn(x_hi, x_lo));
+    loss[i] = (float)__dadd_rn(__dmul_rn(slope, (double)__fsub_rn(x, x_lo)), y_lo);
+}
+
+}  // namespace deco
 }  // namespace oevae

@@ -8,6 +8,7 @@
   make_cut           plots.py:250-259
   bump_scan_cuts     plots.py:272-282   (the cut grid of bump_scan; the BumpHunter statistics themselves are out of scope)
   mass_histograms    plots.py:697-715   (bin edges from get_idx, per-class weighted histogram, normalize / density scalings)
+  mass_deco          plots.py:54-85     (score -> its empirical CDF among the background jets of the same (m, pT) cell)
   generate_cuts      plots.py:88-104    (the six bkg_eff working points + best gain; returns histograms); works on a test set
                                          sharded across ranks: scores are gathered for the threshold search, histogram counts reduced
 """
@@ -185,6 +186,61 @@ def bump_scan_cuts(roc, n_cuts=100):
     x_min = 10 ** np.ceil(np.log10(np.min(fpr)))
     eff_val = np.append(100 * inverse_logit(np.linspace(logit(x_min / 100), -logit(x_min / 100), n_cuts)), 100)
     return roc.searchsorted_cuts(eff_val)
+
+
+# ------------------------------------------------------------------------------------------------ mass decorrelation
+def _merge_bins(edges, counts, min_bin_count=2):
+    """The merging loop of get_bins (plots.py:58-63) on the occupancy of the 99 initial bins: walking down from the last bin, the first
+    bin with fewer than max(2, min_bin_count) jets loses its LEFT edge (it merges into its left neighbour; bin 0 into its right one),
+    until the walk reaches bin 0."""
+    edges, counts = np.array(edges), [int(c) for c in counts]
+    while True:
+        idx = 0
+        for idx in range(len(edges) - 1)[::-1]:
+            if counts[idx] < max(2, min_bin_count):
+                edges = np.delete(edges, idx)
+                if idx >= 1: counts[idx - 1] += counts[idx]; del counts[idx]
+                elif len(counts) > 1: counts[1] += counts[0]; del counts[0]
+                else: del counts[0]
+                break
+        if idx == 0: return edges
+
+
+def get_bins_device(var_t, keep_t, deco, max_bins=100, min_bin_count=2):
+    """get_bins (plots.py:54-63) for the rows of var_t with keep_t: [min, max], or 100 log-spaced edges merged until every bin holds
+    at least two of those jets.  Edge arithmetic is NumPy's on the float32 extrema (as the reference's); the device counts."""
+    dev = var_t.device
+    mm = torch.tensor([np.inf, -np.inf, 0.0], dtype=torch.float64, device=dev)
+    check(_ffi.lib().oevae_minmax(ptr(var_t), ptr(keep_t), var_t.numel(), ptr(mm), dev.index, _stream()))
+    lo, hi = np.float32(mm[0].item()), np.float32(mm[1].item())
+    if not deco: return np.array([lo, hi])
+    edges = np.logspace(np.log10(lo), np.log10(hi), num=max_bins)
+    e_t = torch.as_tensor(np.asarray(edges, np.float64)).to(dev)
+    counts = torch.zeros(len(edges) - 1, dtype=torch.int32, device=dev)
+    check(_ffi.lib().oevae_digitize_count(ptr(var_t), ptr(keep_t), var_t.numel(), ptr(e_t), len(edges), ptr(counts), dev.index, _stream()))
+    return _merge_bins(edges, counts.cpu().numpy(), min_bin_count)
+
+
+def mass_deco(y_true, sample, X_loss, deco='2d'):
+    """plots.py:68-85: every jet's score becomes its empirical CDF value among the background jets (y_true == 1) of the same (mass, pT)
+    cell ('m' / 'pt': one-dimensional binning).  Bin construction on the host from device counts, everything per jet on the device.
+    Returns a float32 host array (the reference overwrites X_loss in place and returns it)."""
+    dev = _dev()
+    m_t, pt_t = _to_dev(sample['m'], dev), _to_dev(sample['pt'], dev)
+    loss_t = _to_dev(np.asarray(X_loss, np.float32), dev).clone()
+    bkg_t = torch.as_tensor(np.ascontiguousarray(np.asarray(y_true) == 1)).to(dev).to(torch.uint8)
+    m_bins = get_bins_device(m_t, bkg_t, deco != 'pt')
+    pt_bins = []
+    for lo, hi in zip(m_bins[:-1], m_bins[1:]):                                  # get_pt_bins (plots.py:69-70)
+        sel = (bkg_t.bool() & (m_t >= float(lo)) & (m_t < float(hi))).to(torch.uint8)
+        pt_bins.append(get_bins_device(pt_t, sel, deco != 'm'))
+    off = np.zeros(len(m_bins), np.int32); off[1:] = np.cumsum([len(b) for b in pt_bins])
+    me_t = torch.as_tensor(np.asarray(m_bins, np.float64)).to(dev)
+    pe_t = torch.as_tensor(np.concatenate(pt_bins).astype(np.float64)).to(dev)
+    off_t = torch.as_tensor(off).to(dev)
+    check(_ffi.lib().oevae_mass_deco(ptr(loss_t), ptr(m_t), ptr(pt_t), ptr(bkg_t), loss_t.numel(), ptr(me_t), len(m_bins), ptr(pe_t), ptr(off_t),
+                                     dev.index, _stream()))
+    return _host(loss_t)
 
 
 # ------------------------------------------------------------------------------------------------ histograms

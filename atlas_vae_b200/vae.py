@@ -63,8 +63,6 @@ def parse_args(argv=None):
         a.FC_layers = list(a.FC_layers[:-1]) + [a.latent_dim]
     if a.HLVs == 'ON':
         raise SystemExit('--HLVs ON needs the 12 high-level variables of the HDF5 files; synthetic samples carry constituents only')
-    if a.decorrelation == 'ON':
-        raise SystemExit('--decorrelation ON (plots.mass_deco) is not on the device path yet (SURVEY 8(f) f3)')
     if a.const_scaler_out == '':
         a.const_scaler_out = 'const_' + a.const_scaler_type + '.pkl'
     for k in ['model_in', 'model_out', 'const_scaler_in', 'const_scaler_out', 'hist_file']:   # vae.py:58-65

@@ -228,6 +228,17 @@ OEVAE_API int oevae_roc_cuts(const double* fpr, const double* tpr, const double*
 OEVAE_API int oevae_roc_searchsorted(const double* fpr, const double* thr, int64_t n_points, const double* eff_host, int32_t n_q,
                            double* thr_out_host, double* eff_out_host, int32_t device, void* stream);
 
+/* ---- mass decorrelation (plots.py:54-85, --decorrelation ON) -----------------------------------------------------------------
+ * oevae_digitize_count: counts[clip(np.digitize(var, edges), 1, n_edges - 1) - 1] += 1 over the rows with keep[i] (nullable): the
+ *   occupancy get_bins (plots.py:54-63) merges bins on; edges DEVICE double[n_edges], counts DEVICE uint32[n_edges - 1] (ADDED to).
+ * oevae_mass_deco: loss[i] <- empirical CDF (cum_distribution, plots.py:64-66, scipy interp1d linear rule) of the BACKGROUND scores of
+ *   jet i's (mass, pT) cell, in place; the pT edges of mass bin k are pt_edges[pt_off[k] .. pt_off[k + 1]) (DEVICE; int32 pt_off
+ *   [n_m_edges]).  Allocates its workspace and synchronises the stream. */
+OEVAE_API int oevae_digitize_count(const float* var, const uint8_t* keep, int64_t N, const double* edges, int32_t n_edges, uint32_t* counts,
+                         int32_t device, void* stream);
+OEVAE_API int oevae_mass_deco(float* loss, const float* m, const float* pt, const uint8_t* is_bkg, int64_t N, const double* m_edges,
+                    int32_t n_m_edges, const double* pt_edges, const int32_t* pt_off, int32_t device, void* stream);
+
 /* ---- OoD <-> background pairing (the step right before training, OE-VAE/utils.py:193-227) -------------------------------------
  * oevae_argsort_f32: np.argsort(OoD_sample['m']) (utils.py:195; stable) -> order_out int64 [N] (device).
  * oevae_ood_pairing: for every background jet, the index (into the m-SORTED OoD arrays) of one OoD jet drawn uniformly from the
