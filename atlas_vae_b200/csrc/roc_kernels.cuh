@@ -435,7 +435,7 @@ __global__ void __launch_bounds__(256) ood_pairing_kernel(const float* __restric
 // (digitize_count_kernel), the cell of every jet (cell_index_kernel), the background scores sorted by (cell, score) (the radix sort
 // above, twice: LSD over the composite key) and the CDF evaluation (cdf_apply_kernel), which restates cum_distribution (plots.py:64-66:
 // np.unique + cumsum / len, a 0 prepended to values and counts) and scipy.interpolate.interp1d's linear rule
-//   y = ((y_hi - y_lo) / float64(x_hi -f32 x_lo)) * float64(x -f32 x_lo) + y_lo,   0 below the first value, 1 above the last
+//   y = f32((x - x_lo) / (x_hi - x_lo)) * y_hi + f32((x_hi - x) / (x_hi - x_lo)) * y_lo   (SciPy 1.18),   0 below the first value, 1 above the last
 // without materialising the per-cell unique arrays: inside the cell's sorted segment, pos = first score >= x gives x_hi, the end of
 // its run of ties gives y_hi = (#scores <= x_hi) / len, and pos itself gives x_lo (the previous score, or the prepended 0) and y_lo.
 namespace deco {
@@ -493,8 +493,10 @@ __global__ void cdf_apply_kernel(float* __restrict__ loss, const uint32_t* __res
     while (l2 < h2) { const long mid = (l2 + h2) >> 1; if (sorted[mid] <= x_hi) l2 = mid + 1; else h2 = mid; }
     const float x_lo = pos > s0 ? sorted[pos - 1] : 0.f;
     const double y_lo = __ddiv_rn((double)(pos - s0), (double)len), y_hi = __ddiv_rn((double)(l2 - s0), (double)len);
-    const double slope = __ddiv_rn(__dsub_rn(y_hi, y_lo), (double)__fsub_rn(x_hi, x_lo));
-    loss[i] = (float)__dadd_rn(__dmul_rn(slope, (double)__fsub_rn(x, x_lo)), y_lo);
+    // SciPy 1.18 _call_linear: ((x - x_lo) / (x_hi - x_lo)) * y_hi + ((x_hi - x) / (x_hi - x_lo)) * y_lo, the two ratios in float32
+    const float dx = __fsub_rn(x_hi, x_lo);
+    const float a = __fdiv_rn(__fsub_rn(x, x_lo), dx), b = __fdiv_rn(__fsub_rn(x_hi, x), dx);
+    loss[i] = (float)__dadd_rn(__dmul_rn((double)a, y_hi), __dmul_rn((double)b, y_lo));
 }
 
 }  // namespace deco
