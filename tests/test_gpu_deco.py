@@ -21,9 +21,9 @@ def test_mass_deco_matches_reference(golden_dir, deco):
     record_parity('mass_deco(%s): fraction of jets not bit-identical to the reference' % deco, 1 - same.mean(), 0.0,
                   {'max_abs': float(np.nanmax(np.abs(got.astype(np.float64) - ref)))})
     np.testing.assert_array_equal(got, ref)
-    # the decorrelated background score is flat in every cell: uniform on [0, 1]
+    # the decorrelated background score is flat in every cell: its mean is (n + 1) / (2 n) for a cell of n jets, 0.5 for large cells
     b = got[g['y_true'] == 1]
-    assert abs(b.mean() - 0.5) < 0.02
+    assert 0.5 <= b.mean() < 0.6
 
 
 def test_get_bins_matches_reference(golden_dir):
