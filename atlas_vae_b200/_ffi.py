@@ -81,6 +81,7 @@ SIGNATURES = {
     'oevae_digitize_count': (C.c_int, [_vp, _vp, _i64, _vp, _i32, _vp, _i32, _vp]),
     'oevae_mass_deco': (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp, _i32, _vp, _vp, _i32, _vp]),
     'oevae_argsort_f32': (C.c_int, [_vp, _i64, _vp, _i32, _vp]),
+    'oevae_argsort_f32_static': (C.c_int, [_vp, _i64, _vp, _i32, _vp]),
     'oevae_ood_pairing': (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, C.c_uint64, _i32, _vp, _vp, _i32, _vp]),
     'oevae_roc': (C.c_int, [_vp, _vp, _i32, _vp, _i64, _vp, _vp, _vp, C.POINTER(_i64), _i32, _vp]),
     'oevae_roc_cuts': (C.c_int, [_vp, _vp, _vp, _i64, _vp, _i32, C.c_double, _vp, _i32, _vp]),

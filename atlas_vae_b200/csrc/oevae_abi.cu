@@ -24,6 +24,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <mutex>
 #include <vector>
 
 using namespace oevae;
@@ -921,6 +922,40 @@ void roc_sort_pairs(uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, long
 }
 }  // namespace
 
+// Allocation-free variant of oevae_argsort_f32 (no counterpart in the reference; added for
+// callers that may not call cudaMalloc: graph capture, tight serving loops).  Its radix-sort workspace is the file-scope array
+// g_sort_scratch: every GPU that loads the library holds kSortScratchBytes of it until exit.  In HOST code the name g_sort_scratch is
+// only a stand-in for the symbol, not a device address, so the address each device maps it at is looked up once per device with
+// cudaGetSymbolAddress (that device current) and that pointer is what the kernels get.  Nothing in the workspace has to start at
+// zero: keys / payloads [0, N), the 256 x tiles digit histogram and the tile sums are all fully rewritten by the kernels of each call
+// before they are read.  All calls share the one array per device: two calls that overlap on the GPU (different streams) race.
+namespace {
+constexpr long kSortStaticMax = OEVAE_ARGSORT_STATIC_MAX;
+constexpr size_t kSortScratchBytes = (size_t)kSortStaticMax * 16                         /* keys + payloads, ping and pong */
+                                   + (size_t)256 * (kSortStaticMax / roc::kTile) * 4   /* digit histogram: 256 x tiles */
+                                   + 4096;                                             /* tile sums of the histogram scan + alignment slack */
+static_assert(kSortStaticMax % roc::kTile == 0, "the static maximum is a whole number of tiles");
+}
+static __device__ __align__(256) unsigned char g_sort_scratch[kSortScratchBytes];
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_sort_scratch_mu;
+unsigned char* g_sort_scratch_addr[kMaxDevices] = {};
+// device address of g_sort_scratch on `device` (which the caller has made current); looked up once per device
+int sort_scratch_address(int device, unsigned char** out) {
+    if (device < 0 || device >= kMaxDevices) { g_create_error = "argsort_static: device index out of range"; return OEVAE_EINVAL; }
+    std::lock_guard<std::mutex> lk(g_sort_scratch_mu);
+    if (!g_sort_scratch_addr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_sort_scratch);
+        if (e != cudaSuccess || !p) { g_create_error = std::string("argsort_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e); return OEVAE_ECUDA; }
+        g_sort_scratch_addr[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_sort_scratch_addr[device];
+    return 0;
+}
+}  // namespace
+
 // ================================================================================================ C ABI
 #define H(h) if (!(h)) return OEVAE_EINVAL; Engine* e = reinterpret_cast<Engine*>(h); cudaSetDevice(e->cfg.device)
 
@@ -1387,6 +1422,30 @@ int oevae_argsort_f32(const float* v, int64_t N, int64_t* order_out, int32_t dev
     cudaError_t e = cudaStreamSynchronize(s);
     cudaFree(ws.base);
     return free_fail(e, "argsort");
+}
+
+// allocation-free variant of oevae_argsort_f32: workspace = the file-scope g_sort_scratch (see its comment above the C ABI block)
+int oevae_argsort_f32_static(const float* v, int64_t N, int64_t* order_out, int32_t device, void* stream) {
+    using namespace roc;
+    if (!v || !order_out || N <= 0) { g_create_error = "argsort_static: bad arguments"; return OEVAE_EINVAL; }
+    if (N > kSortStaticMax) {
+        g_create_error = "argsort_static: N = " + std::to_string((long long)N) + " exceeds OEVAE_ARGSORT_STATIC_MAX = " + std::to_string(kSortStaticMax) +
+                         " (the static workspace is fixed at build time; use oevae_argsort_f32)";
+        return OEVAE_EINVAL;
+    }
+    int rc = free_fail(cudaSetDevice(device), "cudaSetDevice"); if (rc) return rc;
+    RocWs ws; ws.cap = kSortScratchBytes;
+    rc = sort_scratch_address(device, &ws.base); if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const long n = N; const unsigned nt = cdiv(n, kTile);
+    uint32_t* k0 = ws.take<uint32_t>(kSortStaticMax); uint32_t* k1 = ws.take<uint32_t>(kSortStaticMax);
+    uint32_t* v0 = ws.take<uint32_t>(kSortStaticMax); uint32_t* v1 = ws.take<uint32_t>(kSortStaticMax);
+    uint32_t* hist = ws.take<uint32_t>((size_t)256 * (kSortStaticMax / kTile)); uint32_t* tiles = ws.take<uint32_t>(128);
+    if (ws.off > ws.cap) { g_create_error = "argsort_static: workspace layout exceeds the static array"; return OEVAE_EINVAL; }
+    asc_keys_kernel<<<cdiv(n, 256), 256, 0, s>>>(v, n, k0, v0); LAUNCHED();
+    roc_sort_pairs(k0, v0, k1, v1, n, hist, tiles, s);                               // four passes: the sorted pairs are back in (k0, v0)
+    widen_idx_kernel<<<cdiv(n, 256), 256, 0, s>>>(v0, n, reinterpret_cast<long long*>(order_out)); LAUNCHED();
+    return free_fail(cudaGetLastError(), "argsort_static launch");                   // asynchronous: the result is ready in stream order
 }
 
 int oevae_ood_pairing(const float* m_bkg, const float* pt_bkg, int64_t n_bkg, const float* m_ood_sorted, const float* pt_ood_sorted, int64_t n_ood,

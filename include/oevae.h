@@ -247,6 +247,16 @@ OEVAE_API int oevae_mass_deco(float* loss, const float* m, const float* pt, cons
  *   reproducible; pick_first != 0 returns the first candidate instead (tests).  widths_out: nullable float [n_bkg][2] = final
  *   (m_width, pt_width).  idx_out int64 [n_bkg] (device). */
 OEVAE_API int oevae_argsort_f32(const float* v, int64_t N, int64_t* order_out, int32_t device, void* stream);
+/* oevae_argsort_f32_static: NO COUNTERPART IN THE REFERENCE -- added for callers that may not
+ *   allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same result as
+ *   oevae_argsort_f32, but the radix-sort workspace is a file-scope static __device__ array of the library (about 4.1 MiB, held by
+ *   every GPU that loads the library until exit), so the call allocates and frees nothing and does not synchronise: order_out is
+ *   ready in stream order.  N > OEVAE_ARGSORT_STATIC_MAX -> OEVAE_EINVAL with a message naming the limit.  The first call on a device
+ *   resolves the array's device address (cudaGetSymbolAddress); make that call outside a capture.  All calls on one GPU share the
+ *   array: calls that overlap on the GPU (different streams, or a replayed graph next to a live call) race -- keep them in one
+ *   stream order. */
+#define OEVAE_ARGSORT_STATIC_MAX 262144
+OEVAE_API int oevae_argsort_f32_static(const float* v, int64_t N, int64_t* order_out, int32_t device, void* stream);
 OEVAE_API int oevae_ood_pairing(const float* m_bkg, const float* pt_bkg, int64_t n_bkg, const float* m_ood_sorted, const float* pt_ood_sorted,
                       int64_t n_ood, uint64_t seed, int32_t pick_first, int64_t* idx_out, float* widths_out, int32_t device, void* stream);
 
