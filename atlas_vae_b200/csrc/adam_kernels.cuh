@@ -10,7 +10,40 @@ namespace oevae {
 // Sum of the per-CTA partial gradients (fixed order), clip_values (models.py:185), Keras Adam (models.py:186) and
 // refresh of the bf16 hi/lo weight images consumed by the fused kernels (fused2_train.cuh / fused3_train.cuh).
 // ------------------------------------------------------------------------------------------------
+// Early parameter groups.  The training kernel's gradient for the output layer is final when ~60 % of its tile has run, and the chain
+// layers' when only the layer-0 products are left (fused3_train.cuh drain warps count themselves into ctr[0] / ctr[1]).  A block of the
+// update kernel whose 256 parameters lie inside such a group does not wait for the training GRID to finish (griddepcontrol.wait) but for
+// the group's counter to reach `target` (cumulative over the handle's launches, so nothing is ever reset): its reduce, its exchange with
+// the peers (dp_kernels.cuh) and its Adam update run on the SMs the training kernel leaves idle, under the rest of the backward pass.
+// Safe because the counter is complete only when EVERY CTA is past its last read of the group's weights / biases and its last write of the
+// group's partial slice.  Blocks are mapped to parameter chunks in REVERSE (block 0 = last chunk): the blocks that become resident first
+// are the output layer's.  ctr == nullptr: every block waits for the grid.
+struct EarlyGroups {
+    const unsigned int* ctr; unsigned int target; int dry;   // dry: poll, then wait for the grid all the same (A/B of the polling alone)
+    long lo[2], hi[2];                                      // parameter ranges [lo, hi) of group 0 (output layer) and group 1 (chain layers)
+};
+// returns true when the block's chunk belongs to an early group and that group is complete; false: the caller waits for the grid
+__device__ __forceinline__ bool early_wait(const EarlyGroups& e, long c0, long c1) {
+    if (!e.ctr) return false;
+    int g = -1;
+    if (c0 >= e.lo[0] && c1 <= e.hi[0]) g = 0; else if (c0 >= e.lo[1] && c1 <= e.hi[1]) g = 1;
+    if (g < 0) return false;
+    if (threadIdx.x == 0) {
+        const long long t0 = clock64();
+        unsigned int seen;
+        for (;;) {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(e.ctr + g) : "memory");
+            if ((int)(seen - e.target) >= 0) break;
+            __nanosleep(500);                               // ~160 resident pollers on ONE L2 sector: at 64 ns they saturated its slice and slowed the training kernel
+            if (clock64() - t0 > 20000000000ll) __trap();   // ~10 s: the training kernel died; fail loudly instead of hanging
+        }
+    }
+    __syncthreads();
+    return !e.dry;
+}
+
 struct AdamImgArgs {
+    EarlyGroups early;
     const float* parts; int n_parts; long part_stride;
     const float* grad_in; float* grad_out;
     float* theta; float* m; float* v; long n;
@@ -24,10 +57,10 @@ struct AdamImgArgs {
 // thread that owns the parameter, so the result does not depend on scheduling.  One resident wave: ceil(P / 256) blocks of 512.
 constexpr int kAdamCols = 256, kAdamSlices = 8, kAdamThreads = (kAdamCols / 4) * kAdamSlices;
 __device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
-// returns (for threads tid < kAdamCols) the sum over the n_parts slices of parameter blockIdx.x * kAdamCols + tid
-__device__ __forceinline__ float reduce_parts(const float* __restrict__ parts, int n_parts, long part_stride, float (*red)[kAdamCols]) {
+// returns (for threads tid < kAdamCols) the sum over the n_parts slices of parameter chunk * kAdamCols + tid
+__device__ __forceinline__ float reduce_parts(const float* __restrict__ parts, int n_parts, long part_stride, float (*red)[kAdamCols], int chunk) {
     const int cx = threadIdx.x & (kAdamCols / 4 - 1), sl = threadIdx.x / (kAdamCols / 4);
-    const long i4 = (long)blockIdx.x * kAdamCols + 4 * cx;            // rows are padded to a multiple of 4 floats (+ slack): always readable
+    const long i4 = (long)chunk * kAdamCols + 4 * cx;            // rows are padded to a multiple of 4 floats (+ slack): always readable
     float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
     const float* src = parts + i4;
     for (int base = sl; base < n_parts; base += 10 * kAdamSlices) {
@@ -51,13 +84,15 @@ __device__ __forceinline__ float reduce_parts(const float* __restrict__ parts, i
 __global__ void __launch_bounds__(kAdamThreads, 2) adam_img_kernel(AdamImgArgs a) {
     __shared__ __align__(16) float red[kAdamSlices][kAdamCols];
     // programmatic dependent launch (no-ops otherwise): let the next training kernel begin its set-up, then wait for
-    // the kernel that produced the partial gradients
+    // the kernel that produced the partial gradients -- or, for an early parameter group, only for that group's counter
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    const long i = (long)blockIdx.x * kAdamCols + threadIdx.x;
+    const int chunk = (int)gridDim.x - 1 - (int)blockIdx.x;
+    const long c0 = (long)chunk * kAdamCols;
+    if (!early_wait(a.early, c0, min(c0 + kAdamCols, a.n))) asm volatile("griddepcontrol.wait;" ::: "memory");
+    const long i = c0 + threadIdx.x;
     const bool in = threadIdx.x < kAdamCols && i < a.n;
     float g = 0.f;
-    if (a.parts) g = reduce_parts(a.parts, a.n_parts, a.part_stride, red);
+    if (a.parts) g = reduce_parts(a.parts, a.n_parts, a.part_stride, red, chunk);
     if (!in) return;
     float th = a.theta[i];
     if (a.parts || a.grad_in) {

@@ -1,16 +1,19 @@
 // Data-parallel update over NVLink peer memory: ONE kernel replaces "sum the partial slices" +
 // ncclAllReduce(SUM) + "clip_values + Adam" of the NCCL path.
-//   phase 1  block b sums this rank's partial-gradient slices for its 256 parameters (fixed order, adam_kernels.cuh) and stores the result
-//            in the rank's exchange buffer, then pushes sequence number `seq` into flag [rank][b] of EVERY peer (P2P store);
-//   phase 2  it waits until flags [q][b] of all peers q have reached `seq` (they are written into LOCAL memory by the
-//            peers), reads the same 256 values from every peer's exchange buffer (P2P loads), adds the ranks in rank
-//            order -- every rank computes bit-identical sums, so the replicas stay bit-identical -- and applies
-//            clip_values (models.py:185) + Keras Adam (models.py:138,186) + the bf16 weight-image refresh.
-// Nothing is grid-wide: a block depends only on block b of each peer.  All blocks of the launch must be co-resident
-// (a waiting block must never keep a producing block of this rank from being scheduled); the host checks that.
-// The exchange buffer is double-buffered by step parity: a peer overwrites buffer p of step k+2 only after its own
-// step k+1 update, which waited for this rank's step k+1 flags, which this rank raised after its step k kernel
-// (and with it every read of buffer p) had completed.
+//   phase 1  block b sums this rank's partial-gradient slices for its 256 parameters (fixed order, adam_kernels.cuh) and PUSHES
+//            every sum into slot [rank][i] of every peer's receive buffer as ONE 8-byte store {value, seq} (P2P store);
+//   phase 2  every thread polls slots [q][i] of its OWN receive buffer (local memory) until their tag is this step's `seq`,
+//            adds the ranks in rank order -- every rank computes bit-identical sums, so the replicas stay bit-identical --
+//            and applies clip_values (models.py:185) + Keras Adam (models.py:138,186) + the bf16 weight-image refresh.
+// An aligned 8-byte store is one transaction, so value and tag arrive together: no flag, no fence, no barrier, one NVLink
+// traversal.  (Round 1 published a per-block flag with st.release.sys after storing the sums locally and the peers pulled them:
+// the 287 system-scope releases alone cost a median 4.4 us per block, 8 us for the slowest, then flag wait + a load round trip --
+// profiles/r02_dp_stamps_n2_pull.txt.)
+// Nothing is grid-wide: a thread depends only on the same parameter of each peer.  All blocks of the launch must be
+// co-resident (a waiting block must never keep a producing block of this rank from being scheduled); the host checks that.
+// The receive buffer is double-buffered by step parity: a peer overwrites parity p again at step k+2, after its own step
+// k+1 update, which needed this rank's step k+1 sums, which this rank pushed after its step k kernel (and with it every
+// read of parity p) had completed.
 #pragma once
 #include "common.cuh"
 #include "umma.cuh"
@@ -18,21 +21,22 @@
 
 namespace oevae {
 
+constexpr int kDpStamps = 8;                 // globaltimer stamps per block (OEVAE_DP_STAMPS=1)
 constexpr int kDpMaxWorld = 8;               // blocks: ceil(P / kAdamCols) of kAdamThreads threads -- 287 at cfg-2, one co-resident wave
 
 struct DpArgs {
+    EarlyGroups early;                       // adam_kernels.cuh: blocks of early parameter groups start before the training grid ends
     const float* parts; int n_parts; long part_stride;
-    float* my_gred;                          // this rank's exchange buffer of the step (local)
-    const float* peer_gred[kDpMaxWorld];     // the same buffer of every rank (own entry = my_gred)
-    unsigned int* my_flags;                  // [world][gridDim.x], written by the peers
-    unsigned int* peer_flags[kDpMaxWorld];   // every rank's flag array (own entry unused)
-    int rank, world; unsigned int seq;
+    const uint2* my_recv;                    // this rank's receive buffer of the step's parity: [world][stride] {value bits, seq}, written by the peers
+    uint2* peer_recv[kDpMaxWorld];           // the same buffer of every rank (own entry unused)
+    long stride;                             // slots per rank in a receive buffer (>= n)
+    int rank, world; unsigned int seq;       // seq: this step's tag, never 0 (the buffers start zeroed)
     float* theta; float* m; float* v; long n;
     float alpha, b1, b2, eps;
     unsigned char* wimg; const int* pos;
     float* gsum_out;                         // nullable [n]: SUM over ranks before clip_values (parity checks)
-    long long* stamps;                       // nullable [gridDim.x][6] globaltimer ns (OEVAE_DP_STAMPS=1): entry, dependency met, local sum published,
-                                             // all peer flags seen, peer loads done, exit
+    long long* stamps;                       // nullable [gridDim.x][kDpStamps] globaltimer ns (OEVAE_DP_STAMPS=1): entry, dependency met, local sum ready,
+                                             // sums pushed, all peer sums seen, exit
 };
 
 __global__ void __launch_bounds__(kAdamThreads, 2) dp_adam_kernel(DpArgs a) {
@@ -40,48 +44,49 @@ __global__ void __launch_bounds__(kAdamThreads, 2) dp_adam_kernel(DpArgs a) {
     // PDL: the next step's training kernel may begin its set-up (barriers, TMEM, zeroed tiles, X prefetch) on the SMs this kernel's
     // blocks leave; it orders itself behind this grid with griddepcontrol.wait.  Dependents are released only once EVERY block of
     // this grid has started, so a waiting block can never be kept off the chip by them.
-    auto stamp = [&](int k) { if (a.stamps && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); a.stamps[6 * blockIdx.x + k] = (long long)t; } };
+    auto stamp = [&](int k) { if (a.stamps && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); a.stamps[kDpStamps * blockIdx.x + k] = (long long)t; } };
     stamp(0);
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    asm volatile("griddepcontrol.wait;" ::: "memory");      // the training kernel's partial slices are complete
+    const int chunk = (int)gridDim.x - 1 - (int)blockIdx.x;  // reversed: the first-resident blocks own the output layer (EarlyGroups)
+    const long c0 = (long)chunk * kAdamCols;
+    // the training kernel's partial slices are complete -- for the whole grid, or for this block's early parameter group
+    if (!early_wait(a.early, c0, min(c0 + kAdamCols, a.n))) asm volatile("griddepcontrol.wait;" ::: "memory");
     stamp(1);
-    const long i = (long)blockIdx.x * kAdamCols + threadIdx.x;
+    const long i = c0 + threadIdx.x;
     const bool in = threadIdx.x < kAdamCols && i < a.n;
-    // the update's own operands do not depend on the exchange: their loads fly during phase 1
+    // the update's own operands do not depend on the exchange: their loads fly during phase 1 (issued only now: an early block may
+    // be resident while the PREVIOUS update kernel is still writing them)
     float th0 = 0.f, m0 = 0.f, v0 = 0.f;
     int p0 = -1, p1 = -1, p2 = -1, p3 = -1;
     if (in) {
         th0 = a.theta[i]; m0 = a.m[i]; v0 = a.v[i];
         if (a.wimg) { p0 = a.pos[i]; p1 = a.pos[a.n + i]; p2 = a.pos[2 * a.n + i]; p3 = a.pos[3 * a.n + i]; }
     }
-    const float g = reduce_parts(a.parts, a.n_parts, a.part_stride, red);
-    if (in) __stcg(a.my_gred + i, g);
-    __syncthreads();
-    // ---- publish: this block's sums are visible system-wide before any peer sees the flag
-    // (st.release.sys is cumulative over the block's stores ordered before it by the barrier above)
-    if (threadIdx.x < a.world && (int)threadIdx.x != a.rank) {
-        unsigned int* f = a.peer_flags[threadIdx.x] + (long)a.rank * gridDim.x + blockIdx.x;
-        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(a.seq) : "memory");
-    }
+    const float g = reduce_parts(a.parts, a.n_parts, a.part_stride, red, chunk);
     stamp(2);
-    // ---- wait for block blockIdx.x of every peer
-    if (threadIdx.x < a.world && (int)threadIdx.x != a.rank) {
-        const unsigned int* f = a.my_flags + (long)threadIdx.x * gridDim.x + blockIdx.x;
-        unsigned int seen;
-        const long long t0 = clock64();
-        do {
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
-            if ((int)(seen - a.seq) < 0 && clock64() - t0 > 20000000000ll) __trap();   // ~10 s: a peer died; fail loudly instead of hanging
-        } while ((int)(seen - a.seq) < 0);
-    }
-    __syncthreads();
-    stamp(3);
     if (!in) { return; }
-    float tq[kDpMaxWorld];
+    // ---- push {sum, seq} to every peer: a warp writes 256 contiguous bytes per peer
 #pragma unroll
-    for (int q = 0; q < kDpMaxWorld; ++q) {                  // all peers' loads in flight together
-        tq[q] = 0.f;
-        if (q < a.world && q != a.rank) asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(tq[q]) : "l"(a.peer_gred[q] + i) : "memory");
+    for (int q = 0; q < kDpMaxWorld; ++q)
+        if (q < a.world && q != a.rank)
+            asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(a.peer_recv[q] + (long)a.rank * a.stride + i), "r"(__float_as_uint(g)), "r"(a.seq) : "memory");
+    stamp(3);
+    // ---- collect the peers' sums of this parameter from the local receive buffer
+    float tq[kDpMaxWorld];
+    unsigned int pending = 0;
+#pragma unroll
+    for (int q = 0; q < kDpMaxWorld; ++q) { tq[q] = 0.f; if (q < a.world && q != a.rank) pending |= 1u << q; }
+    const long long t0 = clock64();
+    while (pending) {
+#pragma unroll
+        for (int q = 0; q < kDpMaxWorld; ++q) {
+            if (pending & (1u << q)) {
+                uint32_t val, tag;
+                asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(val), "=r"(tag) : "l"(a.my_recv + (long)q * a.stride + i) : "memory");
+                if (tag == a.seq) { tq[q] = __uint_as_float(val); pending &= ~(1u << q); }
+            }
+        }
+        if (pending && clock64() - t0 > 20000000000ll) __trap();   // ~10 s: a peer died; fail loudly instead of hanging
     }
     float gs = 0.f;
 #pragma unroll

@@ -10,6 +10,7 @@ namespace oevae {
 
 struct GemmArgs;
 struct FusedState;
+struct EarlyGroups;
 constexpr int kMaxSlots = 48;          // split-K partial-gradient slots (3 passes x 16)
 
 struct Layer { int in, out; long w, b; };   // offsets of kernel [in,out] and bias [out] in the flat vector
@@ -29,9 +30,11 @@ struct Pass {
 //   OEVAE_FUSED=0          layered path even where the fused kernel applies      OEVAE_FUSED_V=2       fused2 (cross-check) instead of fused3
 //   OEVAE_OE_LAYERED=1     outlier-exposure step on the layered path             OEVAE_SCORE_LAYERED=1 scoring on the layered path
 //   OEVAE_SCORE_STATIC=1   round-robin tiles in the scoring pass                 OEVAE_SCORE_HEADS_T=1 scoring heads with the jets on the lanes
+//   OEVAE_ADAM_EARLY=0     every block of the update kernel waits for the whole training grid (A/B of the early parameter groups)
 //   OEVAE_FUSED_DBG=1      phase stamps of CTA 0 to stderr (synchronises)        OEVAE_DBG_SKIP=k      stamps from the k-th tile of CTA 0 on
 struct Knobs {
     bool fused = true, oe_layered = false, score_layered = false, score_static = false, fused_dbg = false, dp_stamps = false;
+    int adam_early = 3;       // bit 0: output-layer group, bit 1: chain group, bit 2: dry run (poll only), bit 3: also in the data-parallel update
     int fused_v = 3, score_heads_t = 0;
     long long dbg_skip = 0;
     void read_env();
@@ -59,9 +62,9 @@ struct Engine {
     float *kld = nullptr, *rec = nullptr, *g_rec = nullptr, *g_kld = nullptr;
     int Sg = 1, chunk_rows = 0, n_slots_used = 0;
     FusedState* fz = nullptr;      // fused tcgen05 training kernel (bf16x3, small nets); null when not applicable
-    // data-parallel exchange over NVLink peer memory (dp_kernels.cuh): [2][Ppad] reduced gradients + [8][dp_nblk] flags
+    // data-parallel exchange over NVLink peer memory (dp_kernels.cuh): receive buffers [2 parities][8 ranks][Ppad] {value, tag}
     float* dp_buf = nullptr; void* dp_peer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    int dp_rank = -1, dp_world = 0, dp_nblk = 0; unsigned int dp_seq = 0;
+    int dp_rank = -1, dp_world = 0, dp_nblk = 0; unsigned int dp_seq = 0; unsigned long long dp_count = 0;
     long long* dp_stamps = nullptr;   // OEVAE_DP_STAMPS=1: per-block phase stamps of the last update kernel (oevae_dp_stamps_host)
     float* dp_gsum = nullptr;     // [P] SUM over ranks of the last step's gradient, before clip_values (parity checks: oevae_dp_last_grad_host)
 
@@ -99,6 +102,7 @@ struct Engine {
                      bool want_grad, cudaStream_t s);
     int fused_oe(const float* x_bkg, const float* w_bkg, const float* x_ood, const float* w_ood, const float* eps, long B,
                  float beta, float lamb, float margin, float* per_jet, double* sums, bool want_grad, cudaStream_t s);
+    EarlyGroups early_groups() const;
     int reduce_and_update(float* grad_out, const float* grad_in, bool apply, float lr, cudaStream_t s);
     int dp_export(void* handle_out64);
     int dp_connect(int rank, int world, const void* handles);

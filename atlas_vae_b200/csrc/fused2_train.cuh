@@ -151,6 +151,11 @@ struct F2Args {
     // paired mode (OE_type 'KLD'): B = number of (bkg, OoD) pairs, tile t = pairs [32 t, 32 t + 32) with the bkg rows (x, w) on jet
     // columns 0..31 and their OoD partners (x2, w2) on columns 32..63; per_jet / sums get all four loss rows of models.py:123-132
     int paired; const float* w2; float lamb, margin;
+    // fused3 training only, nullable: two monotonic counters.  Every drain warp of a CTA adds 1 to grp_ctr[0] once the CTA's slice of the
+    // OUTPUT layer's gradient is final (after the output chunks of its last tile) and 1 to grp_ctr[1] once the chain layers' gradients are
+    // (everything but layer 0).  The update kernel's blocks for those parameters start on them while the rest of the backward pass runs
+    // (adam_kernels.cuh: EarlyGroups).
+    unsigned int* grp_ctr;
 };
 
 

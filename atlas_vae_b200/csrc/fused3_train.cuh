@@ -663,6 +663,10 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                         dw_release();
                     }
                 }
+                // this CTA's share of the output layer's gradient is final: the update kernel's blocks for those parameters may start
+                // (release: every lane's stores / reductions are performed at the L2 before lane 0 counts the warp in)
+                const bool last_tile = tile + (int)gridDim.x >= a.n_tiles;
+                if (a.grp_ctr && last_tile) { __threadfence(); __syncwarp(); if (lane == 0) atomicAdd(a.grp_ctr, 1u); }
                 // ---- chain stages (bias-gradient parts of G_s are behind gready[s])
                 for (int s = 2 * n; s >= 1; --s) {
                     const F2Stage& st = P.st[s];
@@ -684,6 +688,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                     }
                     dw_release();
                 }
+                if (a.grp_ctr && last_tile) { __threadfence(); __syncwarp(); if (lane == 0) atomicAdd(a.grp_ctr + 1, 1u); }
                 // ---- layer 0: one 64-feature chunk of dW_0^T per accumulator.  Rows 64c..64c+63 of the Keras [D, out_0]
                 // kernel gradient are one contiguous block, so each chunk is transposed through shared memory (tiles 1..2n are
                 // dead) and leaves as ONE bulk copy (bulk reduce-add on later tiles) instead of 16 scalar stores per thread:

@@ -65,6 +65,7 @@ void Knobs::read_env() {
     fused_dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
     dbg_skip = geti("OEVAE_DBG_SKIP", 0);
     dp_stamps = geti("OEVAE_DP_STAMPS", 0) != 0;
+    adam_early = (int)geti("OEVAE_ADAM_EARLY", 3);
 }
 
 int Engine::init(const oevae_config& c) {
@@ -112,6 +113,9 @@ struct FusedState {
     int last_grid = 0;
     float* oe_pj = nullptr; float* oe_c = nullptr; long oe_cap = 0;   // fused outlier-exposure step: raw [4][2B] losses, [2][2B] coefficients
     int* tile_ctr = nullptr;                                // dynamic tile counter of this handle's scoring passes (on cfg.device)
+    // early parameter groups (adam_kernels.cuh EarlyGroups): counters at tile_ctr[32..33], cumulative target over this handle's fused3
+    // training launches (4 drain warps per CTA); grp_ok: the last gradient came from such a launch
+    unsigned int grp_total = 0; bool grp_ok = false;
     long long* dbg_buf = nullptr;                           // phase stamps (OEVAE_FUSED_DBG), allocated on demand
 };
 }
@@ -162,6 +166,7 @@ int Engine::fused_init() {
     CK(cudaMemcpy(f->pos, pos.data(), pos.size() * sizeof(int), cudaMemcpyHostToDevice));
     CK(cudaMalloc(&f->parts, ((size_t)n_sm * Ppad + 64) * sizeof(float)));
     CK(cudaMalloc(&f->tile_ctr, 256));
+    CK(cudaMemset(f->tile_ctr, 0, 256));
     CK(cudaFuncSetAttribute(fused2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
     CK(cudaFuncSetAttribute(fused2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
     CK(cudaFuncSetAttribute(fused3_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, f->plan2.smem_bytes));
@@ -209,11 +214,12 @@ int Engine::fused_losses(const float* x, const float* w, const float* eps, long 
     const int grid2 = std::min(b.n_tiles, n_sm);
     {
         PROF(want_grad ? "fused_train" : "fused_eval", s);
+        if (f.v3 && want_grad) b.grp_ctr = reinterpret_cast<unsigned int*>(f.tile_ctr) + 32;
         if (f.v3) CK(launch_pdl(fused3_kernel<false>, dim3(grid2), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b));
         else fused2_kernel<false><<<grid2, kF2Threads, f.plan2.smem_bytes, s>>>(f.plan2, b);
     }
     CKL();
-    if (want_grad) { f.last_fused = true; f.last_grid = grid2; }
+    if (want_grad) { f.last_fused = true; f.last_grid = grid2; f.grp_ok = f.v3; if (f.v3) f.grp_total += 4u * (unsigned)grid2; }
     if (dbg) {
         long long hbuf[1024]; cudaStreamSynchronize(s); cudaMemcpy(hbuf, dbg_buf, sizeof hbuf, cudaMemcpyDeviceToHost);
         fprintf(stderr, "[fused%d dbg] grid=%d stamps(cycles since start):", f.v3 ? 3 : 2, grid2);
@@ -517,9 +523,10 @@ int Engine::fused_oe(const float* x_bkg, const float* w_bkg, const float* x_ood,
         b.beta = beta; b.lamb = lamb; b.margin = margin; b.seed = cfg.seed; b.row_offset = row_offset; b.step = 0u;
         ++calls;
         const int grid = std::min(b.n_tiles, n_sm);
+        if (want_grad) b.grp_ctr = reinterpret_cast<unsigned int*>(f.tile_ctr) + 32;
         { PROF(want_grad ? "fused_oe_pair_train" : "fused_oe_pair_eval", s); CK(launch_pdl(fused3_kernel<false, 1>, dim3(grid), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b)); }
         CKL();
-        if (want_grad) { f.last_fused = true; f.last_grid = grid; }
+        if (want_grad) { f.last_fused = true; f.last_grid = grid; f.grp_ok = true; f.grp_total += 4u * (unsigned)grid; }
         return 0;
     }
     const long Bt = 2 * B;
@@ -551,10 +558,23 @@ int Engine::fused_oe(const float* x_bkg, const float* w_bkg, const float* x_ood,
     CKL();
     if (!want_grad) return 0;
     b.c_rec = f.oe_c; b.c_kld = f.oe_c + Bt; b.per_jet = nullptr; b.sums = nullptr; b.train = 1;
+    b.grp_ctr = reinterpret_cast<unsigned int*>(f.tile_ctr) + 32;
     { PROF("fused_oe_train", s); CK(launch_pdl(fused3_kernel<false, 2>, dim3(grid), dim3(kF3Threads), (size_t)f.plan2.smem_bytes, s, f.plan2, b)); }
     CKL();
-    f.last_fused = true; f.last_grid = grid;
+    f.last_fused = true; f.last_grid = grid; f.grp_ok = true; f.grp_total += 4u * (unsigned)grid;
     return 0;
+}
+
+// early parameter groups of the update that follows a fused3 training launch (adam_kernels.cuh); all-null when they do not apply
+EarlyGroups Engine::early_groups() const {
+    EarlyGroups e{};
+    if (!fz || !fz->grp_ok || !knobs.adam_early || n < 1) return e;
+    e.ctr = reinterpret_cast<const unsigned int*>(fz->tile_ctr) + 32;
+    e.target = fz->grp_total;
+    if (knobs.adam_early & 1) { e.lo[0] = layers.back().w; e.hi[0] = P; }                  // dense_output: kernel + bias (the last parameters of the flat vector)
+    if (knobs.adam_early & 2) { e.lo[1] = layers[1].w; e.hi[1] = layers.back().w; }        // everything between layer 0 and the output layer
+    e.dry = (knobs.adam_early & 4) != 0;
+    return e;
 }
 
 int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply, float lr, cudaStream_t s) {
@@ -571,7 +591,7 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
     if (fz) {                                               // same update + refresh of the bf16 weight images
         AdamImgArgs ai{};
         if (grad_in) ai.grad_in = grad_in;
-        else if (fz->last_fused) { ai.parts = fz->parts; ai.n_parts = fz->last_grid; ai.part_stride = Ppad; ai.grad_out = grad_out; }
+        else if (fz->last_fused) { ai.parts = fz->parts; ai.n_parts = fz->last_grid; ai.part_stride = Ppad; ai.grad_out = grad_out; ai.early = early_groups(); }
         else { ai.parts = parts; ai.n_parts = n_slots_used; ai.part_stride = Ppad; ai.grad_out = grad_out; }
         ai.theta = theta; ai.m = m; ai.v = v; ai.n = P;
         ai.alpha = a.alpha; ai.b1 = a.b1; ai.b2 = a.b2; ai.eps = a.eps; ai.apply = apply;
@@ -587,14 +607,15 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
 }
 
 // ---------------------------------------------------------------------------------------------- data parallel over peer memory
-static size_t dp_bytes(long Ppad, int nblk) { return (size_t)2 * Ppad * sizeof(float) + (size_t)kDpMaxWorld * nblk * sizeof(unsigned int); }
+// receive buffers: [2 parities][kDpMaxWorld ranks][Ppad] slots of {value bits, sequence tag} (dp_kernels.cuh)
+static size_t dp_bytes(long Ppad) { return (size_t)2 * kDpMaxWorld * Ppad * sizeof(uint2); }
 
 int Engine::dp_export(void* handle_out) {
     if (!handle_out) return fail(OEVAE_EINVAL, "dp_export: null handle");
     if (!dp_buf) {
         dp_nblk = (int)cdiv(P, kAdamCols);
-        CK(cudaMalloc(&dp_buf, dp_bytes(Ppad, dp_nblk)));
-        CK(cudaMemset(dp_buf, 0, dp_bytes(Ppad, dp_nblk)));
+        CK(cudaMalloc(&dp_buf, dp_bytes(Ppad)));
+        CK(cudaMemset(dp_buf, 0, dp_bytes(Ppad)));
         CK(cudaDeviceSynchronize());
     }
     CK(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(handle_out), dp_buf));
@@ -614,8 +635,12 @@ int Engine::dp_connect(int rank, int world, const void* handles) {
         CK(cudaIpcOpenMemHandle(&dp_peer[q], hs[q], cudaIpcMemLazyEnablePeerAccess));
     }
     if (!dp_gsum) CK(cudaMalloc(&dp_gsum, Ppad * sizeof(float)));
-    if (knobs.dp_stamps && !dp_stamps) { CK(cudaMalloc(&dp_stamps, (size_t)dp_nblk * 6 * sizeof(long long))); CK(cudaMemset(dp_stamps, 0, (size_t)dp_nblk * 6 * sizeof(long long))); }
-    dp_rank = rank; dp_world = world; dp_seq = 0;
+    if (knobs.dp_stamps && !dp_stamps) { CK(cudaMalloc(&dp_stamps, (size_t)dp_nblk * kDpStamps * sizeof(long long))); CK(cudaMemset(dp_stamps, 0, (size_t)dp_nblk * kDpStamps * sizeof(long long))); }
+    // tags restart at 1: no slot may still carry a tag of an earlier connection (the peers push only after the host-side barrier that
+    // follows this call, engine.DeviceVAE.dp_connect)
+    CK(cudaMemset(dp_buf, 0, dp_bytes(Ppad)));
+    CK(cudaDeviceSynchronize());
+    dp_rank = rank; dp_world = world; dp_seq = 0; dp_count = 0;
     return 0;
 }
 
@@ -625,19 +650,21 @@ int Engine::dp_update(float lr, bool have_grad, cudaStream_t s) {
     if (dp_world < 2) return fail(OEVAE_EINVAL, "dp_update: not connected");
     DpArgs a{};
     if (!have_grad) { a.parts = fz ? fz->parts : parts; a.n_parts = 0; }
-    else if (fz && fz->last_fused) { a.parts = fz->parts; a.n_parts = fz->last_grid; }
+    else if (fz && fz->last_fused) {
+        a.parts = fz->parts; a.n_parts = fz->last_grid;
+        // early parameter groups: measured at N = 2 they do not shorten the update's tail (it is latency: wait, reduce 2 us, push, peers' sums 1-2 us)
+        // and cost 2 us of interference with the training kernel (profiles/r02_dp_stamps_n2_push.txt): on only with OEVAE_ADAM_EARLY bit 3
+        if (knobs.adam_early & 8) a.early = early_groups();
+    }
     else { a.parts = parts; a.n_parts = n_slots_used; }
     a.gsum_out = dp_gsum; a.stamps = dp_stamps;
     a.part_stride = Ppad;
     ++step; ++dp_seq;
-    const int b = (int)(dp_seq & 1u);
-    a.my_gred = dp_buf + (size_t)b * Ppad;
-    a.my_flags = reinterpret_cast<unsigned int*>(dp_buf + (size_t)2 * Ppad);
-    for (int q = 0; q < dp_world; ++q) {
-        float* base = static_cast<float*>(dp_peer[q]);
-        a.peer_gred[q] = base + (size_t)b * Ppad;
-        a.peer_flags[q] = reinterpret_cast<unsigned int*>(base + (size_t)2 * Ppad);
-    }
+    if (dp_seq == 0) ++dp_seq;                              // 0 is the tag of an empty slot
+    const size_t par = (size_t)(++dp_count & 1) * kDpMaxWorld * Ppad;    // parity alternates with every exchange of this connection (every rank takes part in each)
+    a.my_recv = reinterpret_cast<const uint2*>(dp_buf) + par;
+    for (int q = 0; q < dp_world; ++q) a.peer_recv[q] = reinterpret_cast<uint2*>(dp_peer[q]) + par;
+    a.stride = Ppad;
     a.rank = dp_rank; a.world = dp_world; a.seq = dp_seq;
     a.theta = theta; a.m = m; a.v = v; a.n = P;
     const double t = (double)step;
@@ -1055,10 +1082,10 @@ int oevae_dp_last_grad_host(oevae_t h, float* grad_host, int64_t nn) {
 int oevae_dp_stamps_host(oevae_t h, int64_t* out_host, int64_t cap) {
     H(h);
     if (!e->dp_stamps) return e->fail(OEVAE_EINVAL, "dp_stamps: set OEVAE_DP_STAMPS=1 before oevae_create and connect first");
-    const int64_t nn = std::min<int64_t>(cap, (int64_t)e->dp_nblk * 6);
+    const int64_t nn = std::min<int64_t>(cap, (int64_t)e->dp_nblk * kDpStamps);
     if (!out_host || nn <= 0) return e->fail(OEVAE_EINVAL, "dp_stamps: bad arguments");
     int rc = e->cuda_check(cudaMemcpy(out_host, e->dp_stamps, nn * sizeof(long long), cudaMemcpyDeviceToHost), "dp_stamps");
-    return rc ? rc : (int)(nn / 6);
+    return rc ? rc : (int)(nn / kDpStamps);
 }
 
 int oevae_reset_opt_state(oevae_t h) { H(h); return e->reset_opt(); }

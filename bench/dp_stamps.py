@@ -28,17 +28,29 @@ e1.record(); torch.cuda.synchronize()
 us = e0.elapsed_time(e1) * 1e3 / 200
 rows = []
 if world > 1:
-    buf = np.zeros((4096, 6), np.int64)
+    buf = np.zeros((4096, 8), np.int64)
     n = _ffi.lib().oevae_dp_stamps_host(v.h, buf.ctypes.data, buf.size)
-    s = buf[:n].astype(np.float64)
+    s = buf[:n, :6].astype(np.float64)
     t0 = s[:, 0].min()
-    names = ['entry', 'dependency met (training kernel done)', 'local sum published', 'all peer flags seen', 'peer loads done', 'exit']
+    names = ['entry', 'dependency met (grid or early group)', 'local sum ready', 'sums pushed to the peers', 'all peer sums seen', 'exit']
     rows = ['rank %d  step %.1f us  update kernel of the last step, %d blocks (us after the first block entered)' % (rank, us, n)]
     for k, nm in enumerate(names):
         c = (s[:, k] - t0) / 1e3
         rows.append('  %-42s first %7.2f  median %7.2f  last %7.2f' % (nm, c.min(), np.median(c), c.max()))
     d = (s[:, 1:] - s[:, :-1]) / 1e3
-    rows.append('  per-block phase medians: wait for dependency %.2f, local reduce + publish %.2f, wait for peers %.2f, peer loads %.2f, Adam + image %.2f'
+    # the same phases by parameter group (block b owns chunk n - 1 - b of 256 parameters: layer 0 first in the flat vector, output layer last)
+    nb = int(n); chunk = nb - 1 - np.arange(nb)
+    P_l0, P_out = D * FC[0] + FC[0], D * FC[0] + D
+    Ptot = int(_ffi.lib().oevae_n_params(v.h))
+    grp = np.where((chunk + 1) * 256 <= P_l0, 0, np.where(chunk * 256 >= Ptot - P_out, 2, 1))
+    for gi, gname in enumerate(['layer 0', 'chain layers (+ boundary chunks)', 'output layer']):
+        sel = grp == gi
+        if not sel.any(): continue
+        dd = (s[sel, 1:] - s[sel, :-1]) / 1e3
+        rows.append('  %-34s %3d blocks: dependency met at %6.2f..%6.2f, reduce min %.2f median %.2f max %.2f, push median %.2f max %.2f, wait for peers median %.2f max %.2f, exit at %6.2f..%6.2f'
+                    % (gname, sel.sum(), (s[sel, 1].min() - t0) / 1e3, (s[sel, 1].max() - t0) / 1e3, dd[:, 1].min(), np.median(dd[:, 1]), dd[:, 1].max(), np.median(dd[:, 2]), dd[:, 2].max(),
+                       np.median(dd[:, 3]), dd[:, 3].max(), (s[sel, 5].min() - t0) / 1e3, (s[sel, 5].max() - t0) / 1e3))
+    rows.append('  per-block phase medians: wait for dependency %.2f, local reduce %.2f, push %.2f, wait for peers %.2f, Adam + image %.2f'
                 % tuple(np.median(d, 0)))
 else:
     rows = ['rank 0  step %.1f us (single rank)' % us]

@@ -30,8 +30,8 @@ OEVAE_API int oevae_probe_issue(int32_t M, int32_t N, int32_t nw, int32_t nm, in
  * out_host2 = {best of 5, first (cold)} of CTA 0. */
 OEVAE_API int oevae_probe_bulk(int32_t bytes, int32_t depth, int32_t n_cta, int32_t same_src, int64_t* out_host2, int32_t device);
 
-/* Phase stamps of the last oevae_train_step_dp update kernel (handles created with OEVAE_DP_STAMPS=1): out_host int64 [n_blocks][6] =
- * globaltimer ns at {entry, dependency met, local sum published, all peer flags seen, peer loads done, exit}; returns n_blocks. */
+/* Phase stamps of the last oevae_train_step_dp update kernel (handles created with OEVAE_DP_STAMPS=1): out_host int64 [n_blocks][8] =
+ * globaltimer ns at {entry, dependency met, local sum ready, sums pushed, all peer sums seen, exit, unused, unused}; returns n_blocks. */
 OEVAE_API int oevae_dp_stamps_host(oevae_t h, int64_t* out_host, int64_t cap);
 
 #ifdef __cplusplus
