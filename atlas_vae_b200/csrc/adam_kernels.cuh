@@ -42,8 +42,15 @@ __device__ __forceinline__ bool early_wait(const EarlyGroups& e, long c0, long c
     return !e.dry;
 }
 
+// Read-back of the step's running loss sums without a copy node in the stream: the block that owns chunk 0 (layer 0: it always waits
+// for the whole training grid) stores the four doubles into page-locked host memory mapped into the device's address space.
+struct SumsTrace { const double* src; double* dst_host; };
+__device__ __forceinline__ void write_trace(const SumsTrace& t, int chunk) {
+    if (t.dst_host && chunk == 0 && threadIdx.x < 4) t.dst_host[threadIdx.x] = __ldcg(t.src + threadIdx.x);
+}
+
 struct AdamImgArgs {
-    EarlyGroups early;
+    EarlyGroups early; SumsTrace trace;
     const float* parts; int n_parts; long part_stride;
     const float* grad_in; float* grad_out;
     float* theta; float* m; float* v; long n;
@@ -93,6 +100,7 @@ __global__ void __launch_bounds__(kAdamThreads, 2) adam_img_kernel(AdamImgArgs a
     const bool in = threadIdx.x < kAdamCols && i < a.n;
     float g = 0.f;
     if (a.parts) g = reduce_parts(a.parts, a.n_parts, a.part_stride, red, chunk);
+    write_trace(a.trace, chunk);
     if (!in) return;
     float th = a.theta[i];
     if (a.parts || a.grad_in) {

@@ -26,6 +26,7 @@ constexpr int kDpMaxWorld = 8;               // blocks: ceil(P / kAdamCols) of k
 
 struct DpArgs {
     EarlyGroups early;                       // adam_kernels.cuh: blocks of early parameter groups start before the training grid ends
+    SumsTrace trace;                         // adam_kernels.cuh: the step's running loss sums -> mapped host memory
     const float* parts; int n_parts; long part_stride;
     const uint2* my_recv;                    // this rank's receive buffer of the step's parity: [world][stride] {value bits, seq}, written by the peers
     uint2* peer_recv[kDpMaxWorld];           // the same buffer of every rank (own entry unused)
@@ -64,6 +65,7 @@ __global__ void __launch_bounds__(kAdamThreads, 2) dp_adam_kernel(DpArgs a) {
     }
     const float g = reduce_parts(a.parts, a.n_parts, a.part_stride, red, chunk);
     stamp(2);
+    write_trace(a.trace, chunk);
     if (!in) { return; }
     // ---- push {sum, seq} to every peer: a warp writes 256 contiguous bytes per peer
 #pragma unroll

@@ -72,7 +72,8 @@ struct Engine {
     // kHlSlots - 1 batches ahead of the steps, so the copy engine stays busy while the host reads the running means (a sync every
     // 10 batches, models.py:191)
     static constexpr int kHlSlots = 6;
-    cudaStream_t hl_copy = nullptr; cudaEvent_t hl_ready[kHlSlots] = {}, hl_freed[kHlSlots] = {};
+    cudaStream_t hl_copy = nullptr, hl_prep = nullptr; cudaEvent_t hl_ready[kHlSlots] = {}, hl_freed[kHlSlots] = {}, hl_copied[kHlSlots] = {};
+    const double* hl_trace_src = nullptr; double* hl_trace_dst = nullptr;   // set around the update launch of a host-load step (adam_kernels.cuh SumsTrace)
     unsigned char* hl_ring = nullptr; size_t hl_ring_bytes = 0;
     bool hl_used[kHlSlots] = {};
     const void* hl_src = nullptr; long hl_copied_upto = 0;   // batches [.., hl_copied_upto) of the load at hl_src have their copies issued

@@ -128,8 +128,9 @@ Engine::~Engine() {
     if (dp_gsum) cudaFree(dp_gsum);
     if (dp_stamps) cudaFree(dp_stamps);
     if (hl_ring) cudaFree(hl_ring);
-    for (int k = 0; k < kHlSlots; ++k) { if (hl_ready[k]) cudaEventDestroy(hl_ready[k]); if (hl_freed[k]) cudaEventDestroy(hl_freed[k]); }
+    for (int k = 0; k < kHlSlots; ++k) { if (hl_ready[k]) cudaEventDestroy(hl_ready[k]); if (hl_freed[k]) cudaEventDestroy(hl_freed[k]); if (hl_copied[k]) cudaEventDestroy(hl_copied[k]); }
     if (hl_copy) cudaStreamDestroy(hl_copy);
+    if (hl_prep) cudaStreamDestroy(hl_prep);
     if (fz) {
         if (fz->wimg) cudaFree(fz->wimg); if (fz->pos) cudaFree(fz->pos); if (fz->parts) cudaFree(fz->parts); if (fz->oe_pj) cudaFree(fz->oe_pj);
         if (fz->oe_c) cudaFree(fz->oe_c); if (fz->tile_ctr) cudaFree(fz->tile_ctr); if (fz->dbg_buf) cudaFree(fz->dbg_buf);
@@ -595,7 +596,7 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
         else { ai.parts = parts; ai.n_parts = n_slots_used; ai.part_stride = Ppad; ai.grad_out = grad_out; }
         ai.theta = theta; ai.m = m; ai.v = v; ai.n = P;
         ai.alpha = a.alpha; ai.b1 = a.b1; ai.b2 = a.b2; ai.eps = a.eps; ai.apply = apply;
-        ai.wimg = fz->wimg; ai.pos = fz->pos;
+        ai.wimg = fz->wimg; ai.pos = fz->pos; ai.trace = SumsTrace{hl_trace_src, hl_trace_dst};
         { PROF("adam", s); CK(launch_pdl(adam_img_kernel, dim3((unsigned)cdiv(P, kAdamCols)), dim3(kAdamThreads), 0, s, ai)); }
         CKL();
         if (apply) fz->img_dirty = false;
@@ -657,7 +658,7 @@ int Engine::dp_update(float lr, bool have_grad, cudaStream_t s) {
         if (knobs.adam_early & 8) a.early = early_groups();
     }
     else { a.parts = parts; a.n_parts = n_slots_used; }
-    a.gsum_out = dp_gsum; a.stamps = dp_stamps;
+    a.gsum_out = dp_gsum; a.stamps = dp_stamps; a.trace = SumsTrace{hl_trace_src, hl_trace_dst};
     a.part_stride = Ppad;
     ++step; ++dp_seq;
     if (dp_seq == 0) ++dp_seq;                              // 0 is the tag of an empty slot
@@ -694,14 +695,23 @@ int Engine::train_batches_host(oevae_host_load& a, cudaStream_t s) {
     if (resident && a.resident_stride < cap - 1) return fail(OEVAE_EINVAL, "train_batches_host: resident_stride too small");
     if (!hl_copy) {
         CK(cudaStreamCreateWithFlags(&hl_copy, cudaStreamNonBlocking));
-        for (int k = 0; k < kHlSlots; ++k) { CK(cudaEventCreateWithFlags(&hl_ready[k], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&hl_freed[k], cudaEventDisableTiming)); }
+        CK(cudaStreamCreateWithFlags(&hl_prep, cudaStreamNonBlocking));
+        for (int k = 0; k < kHlSlots; ++k) {
+            CK(cudaEventCreateWithFlags(&hl_ready[k], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&hl_freed[k], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&hl_copied[k], cudaEventDisableTiming));
+        }
     }
+    // the per-step read-back of the running sums: stored by the update kernel straight into the caller's page-locked buffer when the
+    // device can address it (no copy node between the kernels of consecutive steps), else a 32-byte copy after every step
+    double* trace_dev = nullptr;
+    const bool trace_direct = a.sums_trace_host && a.sums_acc && fz && cudaHostGetDevicePointer(reinterpret_cast<void**>(&trace_dev), a.sums_trace_host, 0) == cudaSuccess && trace_dev;
+    if (!trace_direct) cudaGetLastError();
     // ring slot: [x fp32][xo fp32][w][wo][x f16][xo f16]; with resident buffers only the f16 staging part is used
     const size_t xb = (size_t)cap * D * 4, wb = ((size_t)cap * 4 + 255) / 256 * 256, hb = ((size_t)cap * D * 2 + 255) / 256 * 256;
     const size_t slot_bytes = 2 * xb + 2 * wb + 2 * hb;
     constexpr int NS = kHlSlots, AHEAD = kHlSlots - 1;
     if (hl_ring_bytes < NS * slot_bytes) {
-        CK(cudaStreamSynchronize(s)); CK(cudaStreamSynchronize(hl_copy));
+        CK(cudaStreamSynchronize(s)); CK(cudaStreamSynchronize(hl_copy)); CK(cudaStreamSynchronize(hl_prep));
         if (hl_ring) cudaFree(hl_ring);
         hl_ring = nullptr; hl_ring_bytes = 0;
         CK(cudaMalloc(&hl_ring, NS * slot_bytes));
@@ -746,7 +756,23 @@ int Engine::train_batches_host(oevae_host_load& a, cudaStream_t s) {
                 a.h2d_bytes += (int64_t)(xbytes + (size_t)sh.n * 4);
             }
         }
-        CK(cudaEventRecord(hl_ready[k], hl_copy));
+        // float16 -> float32 + scaler (or the float32 scaler pass) on the preparation stream: off the steps' critical path, and the copy
+        // engine goes straight on to the next batch
+        if (sh.n > 0 && (f16 || a.scale)) {
+            CK(cudaEventRecord(hl_copied[k], hl_copy));
+            CK(cudaStreamWaitEvent(hl_prep, hl_copied[k], 0));
+            const long ne = sh.n * D;
+            if (f16) {
+                { PROF("ingest_f16", hl_prep); ingest_f16_kernel<<<cdiv((ne + 7) / 8, 256), 256, 0, hl_prep>>>(reinterpret_cast<const __half*>(d.hx), d.x, ne, D, a.center, a.scale); } CKL();
+                if (ood) { { PROF("ingest_f16", hl_prep); ingest_f16_kernel<<<cdiv((ne + 7) / 8, 256), 256, 0, hl_prep>>>(reinterpret_cast<const __half*>(d.hxo), d.xo, ne, D, a.center, a.scale); } CKL(); }
+            } else {
+                { PROF("affine", hl_prep); affine_kernel<<<cdiv(ne, 256), 256, 0, hl_prep>>>(d.x, d.x, sh.n, D, a.center, a.scale); } CKL();
+                if (ood) { { PROF("affine", hl_prep); affine_kernel<<<cdiv(ne, 256), 256, 0, hl_prep>>>(d.xo, d.xo, sh.n, D, a.center, a.scale); } CKL(); }
+            }
+            CK(cudaEventRecord(hl_ready[k], hl_prep));
+        } else {
+            CK(cudaEventRecord(hl_ready[k], hl_copy));
+        }
         return 0;
     };
     a.h2d_bytes = 0;
@@ -759,29 +785,24 @@ int Engine::train_batches_host(oevae_host_load& a, cudaStream_t s) {
         return 0;
     };
     TRY(copy_upto(a.first_batch + AHEAD));
+    if (a.first_batch < b_end) CK(cudaStreamWaitEvent(s, hl_ready[a.first_batch % NS], 0));
     for (long b = a.first_batch; b < b_end; ++b) {
         const int k = (int)(b % NS);
         const Shard sh = shard(b);
         const Bufs d = bufs(b);
-        CK(cudaStreamWaitEvent(s, hl_ready[k], 0));
-        if (sh.n > 0) {
-            const long ne = sh.n * D;
-            if (f16) {
-                { PROF("ingest_f16", s); ingest_f16_kernel<<<cdiv((ne + 7) / 8, 256), 256, 0, s>>>(reinterpret_cast<const __half*>(d.hx), d.x, ne, D, a.center, a.scale); } CKL();
-                if (ood) { { PROF("ingest_f16", s); ingest_f16_kernel<<<cdiv((ne + 7) / 8, 256), 256, 0, s>>>(reinterpret_cast<const __half*>(d.hxo), d.xo, ne, D, a.center, a.scale); } CKL(); }
-            } else if (a.scale) {
-                { PROF("affine", s); affine_kernel<<<cdiv(ne, 256), 256, 0, s>>>(d.x, d.x, sh.n, D, a.center, a.scale); } CKL();
-                if (ood) { { PROF("affine", s); affine_kernel<<<cdiv(ne, 256), 256, 0, s>>>(d.xo, d.xo, sh.n, D, a.center, a.scale); } CKL(); }
-            }
-        }
         row_offset = save_off + (unsigned long long)(a.noise_row0 + sh.off);        // noise of a jet does not depend on the sharding
         int rc = 0;
         if (sh.n > 0) rc = losses(d.x, d.w, ood ? d.xo : nullptr, ood ? d.wo : nullptr, nullptr, 0, sh.n, a.beta, a.lamb, a.margin, nullptr, a.sums_acc, true, s);
+        // the NEXT batch's data is awaited before this step's update kernel, so that update kernel and next training kernel stay
+        // adjacent in the stream (programmatic dependent launch: the training kernel's set-up overlaps the update)
+        if (!rc && b + 1 < b_end) CK(cudaStreamWaitEvent(s, hl_ready[(b + 1) % NS], 0));
+        if (trace_direct) { hl_trace_src = a.sums_acc; hl_trace_dst = trace_dev + 4 * (b - a.first_batch); }
         if (!rc) rc = a.update == 1 ? dp_update(a.lr, sh.n > 0, s) : (sh.n > 0 ? reduce_and_update(nullptr, nullptr, true, a.lr, s) : 0);
+        hl_trace_src = nullptr; hl_trace_dst = nullptr;
         row_offset = save_off;
         if (rc) return rc;
         CK(cudaEventRecord(hl_freed[k], s)); hl_used[k] = true;
-        if (a.sums_trace_host && a.sums_acc)
+        if (a.sums_trace_host && a.sums_acc && (!trace_direct || (a.update == 0 && sh.n == 0)))
             CK(cudaMemcpyAsync(a.sums_trace_host + 4 * (b - a.first_batch), a.sums_acc, 4 * sizeof(double), cudaMemcpyDeviceToHost, s));
         TRY(copy_upto(b + 1 + AHEAD));
     }

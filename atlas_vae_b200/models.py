@@ -440,7 +440,11 @@ def train_model(vae, train_sample, valid_sample, OE_type='KLD', n_epochs=1, batc
     use_ood = lamb != 0
     center, scale = _scaler_dev(scaler, vae.input_dim, dev.device)
     metrics_every = max(1, int(metrics_every))
-    trace = torch.zeros((metrics_every, 4), dtype=torch.float64).pin_memory()   # per-step copy of the running sums (models.py:187-190)
+    # models.py:191 reads and prints the running means every 10 batches.  With verbose=False nothing is printed, so the read (a stream
+    # synchronisation; under torchrun an all-reduce as well) happens once per load and the whole load is ONE native call.  The per-step
+    # device->host copy of the running sums (models.py:187-190) is made either way.
+    group = metrics_every if verbose else (1 << 30)
+    trace = getattr(dev, '_trace', None)                        # page-locked [steps of a group][4] float64, kept on the handle
     total_batches = 0; count = 0; n_steps = 0; h2d = 0
     beta, lamb, margin = float(beta), float(lamb), float(margin)
     loads = {}                                                # generator OFF: the load (and its resident copy) lives across epochs
@@ -480,15 +484,17 @@ def train_model(vae, train_sample, valid_sample, OE_type='KLD', n_epochs=1, batc
                                         keep_resident=(train_len == 1 and n_epochs > 1), noise_row0=rank * int(batch_size) if own else 0)
                         if train_len == 1: loads[train_idx] = ld
                     if epoch == 0: total_batches += ld.n_batches
+                    if trace is None or trace.shape[0] < min(group, ld.n_batches):
+                        trace = dev._trace = torch.zeros((min(group, max(ld.n_batches, 16)), 4), dtype=torch.float64).pin_memory()
                     try:
                         b = 0
                         while b < ld.n_batches:
-                            cnt = min(metrics_every - sum_batches % metrics_every, ld.n_batches - b)
+                            cnt = min(group - sum_batches % group, ld.n_batches - b)
                             ld.run(b, cnt, optimizer.learning_rate, beta, lamb, margin, sums, peer, trace)
                             b += cnt; sum_batches += cnt; n_steps += cnt
                             n_seen += gmul * (min(b * ld.batch_size, ld.n) - (b - cnt) * ld.batch_size)
                             last = b == ld.n_batches
-                            if sum_batches % metrics_every == 0 or last:             # models.py:191-200
+                            if sum_batches % group == 0 or last:                     # models.py:191-200
                                 report(last, last_load, trace[cnt - 1])
                     finally:
                         if train_len != 1: h2d += ld.h2d_bytes; ld.close()
@@ -513,7 +519,7 @@ def train_model(vae, train_sample, valid_sample, OE_type='KLD', n_epochs=1, batc
                             dev.apply_update(grad, optimizer.learning_rate)
                         n_seen += gmul * (min((batch_idx + 1) * stager.batch_size, stager.n) - batch_idx * stager.batch_size)
                         last = batch_idx + 1 == stager.n_batches
-                        if sum_batches % metrics_every == 0 or last:                 # models.py:191-200
+                        if sum_batches % group == 0 or last:                         # models.py:191-200
                             report(last, last_load)
                 finally:
                     h2d += stager.h2d_bytes

@@ -450,7 +450,7 @@ def run_ours(args):
 
     # ---- end to end through the public API: models.train_model on a HOST sample.  The host holds what the reference's files hold
     # (float16 constituents, tools/merging.py:31) + weights; every step's batch is copied host->device from page-locked memory inside
-    # the timed region and the loss sums are read back device->host after every step (metrics_every=1).
+    # the timed region and the running loss sums come back device->host after every step (written into page-locked memory by the update kernel).
     n_e2e = n_batches                                             # the whole 1M-jet epoch: 200 steps
     pin = lambda t: t.cpu().pin_memory().numpy()                  # page-locked host buffers, prepared before the timed region
     Xh = pin(X16[:n_e2e * BATCH]); wh = pin(torch.ones(n_e2e * BATCH))
@@ -484,7 +484,7 @@ def run_ours(args):
             'clocks': clk, 'gpu_launches': int(launches),
             'e2e': {'value': e2e_val, 'unit': UNIT, 'h2d_bytes_per_step': int(h2d_step), 'd2h_bytes_per_step': 32, 'ms_per_step': e2e_ms / n_e2e,
                     'reps_ms_per_step': [m_ / n_e2e for m_ in e2e_reps], 'steps': n_e2e,
-                    'api': 'atlas_vae_b200.models.train_model(host float16 sample in page-locked memory, scaler=MaxAbs): 1 epoch of %d steps + its validation pass, wall clock; the running sums come back device->host after every step, the host reads them every 10 batches (models.py:191)' % n_e2e},
+                    'api': 'atlas_vae_b200.models.train_model(host float16 sample in page-locked memory, scaler=MaxAbs): 1 epoch of %d steps + its validation pass, wall clock, verbose=False; the running loss sums of every step are stored into page-locked host memory by its update kernel (32 B device->host per step), the host reads them once per load (nothing is printed)' % n_e2e},
             'roofline': roof, 'kernels': kernels[:8], 'scoring': scoring, 'strong': strong, 'small_kernels': small}
     if dp_parity is not None: line['dp_parity'] = dp_parity
     line.update(extra)
