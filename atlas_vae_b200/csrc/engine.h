@@ -62,7 +62,7 @@ struct Engine {
     float *kld = nullptr, *rec = nullptr, *g_rec = nullptr, *g_kld = nullptr;
     int Sg = 1, chunk_rows = 0, n_slots_used = 0;
     FusedState* fz = nullptr;      // fused tcgen05 training kernel (bf16x3, small nets); null when not applicable
-    // data-parallel exchange over NVLink peer memory (dp_kernels.cuh): receive buffers [2 parities][8 ranks][Ppad] {value, tag}
+    // data-parallel exchange over NVLink peer memory (dp_kernels.cuh): receive buffers [2 parities][8 ranks][slots] {three sums, tag}
     float* dp_buf = nullptr; void* dp_peer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     int dp_rank = -1, dp_world = 0, dp_nblk = 0; unsigned int dp_seq = 0; unsigned long long dp_count = 0;
     long long* dp_stamps = nullptr;   // OEVAE_DP_STAMPS=1: per-block phase stamps of the last update kernel (oevae_dp_stamps_host)

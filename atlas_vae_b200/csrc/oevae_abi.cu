@@ -608,15 +608,16 @@ int Engine::reduce_and_update(float* grad_out, const float* grad_in, bool apply,
 }
 
 // ---------------------------------------------------------------------------------------------- data parallel over peer memory
-// receive buffers: [2 parities][kDpMaxWorld ranks][Ppad] slots of {value bits, sequence tag} (dp_kernels.cuh)
-static size_t dp_bytes(long Ppad) { return (size_t)2 * kDpMaxWorld * Ppad * sizeof(uint2); }
+// receive buffers: [2 parities][kDpMaxWorld ranks][slots] of {three sums, sequence tag}, kDpSlots slots per block (dp_kernels.cuh)
+static long dp_slots(long P) { return (long)cdiv(P, kAdamCols) * kDpSlots; }
+static size_t dp_bytes(long P) { return (size_t)2 * kDpMaxWorld * dp_slots(P) * sizeof(uint4); }
 
 int Engine::dp_export(void* handle_out) {
     if (!handle_out) return fail(OEVAE_EINVAL, "dp_export: null handle");
     if (!dp_buf) {
         dp_nblk = (int)cdiv(P, kAdamCols);
-        CK(cudaMalloc(&dp_buf, dp_bytes(Ppad)));
-        CK(cudaMemset(dp_buf, 0, dp_bytes(Ppad)));
+        CK(cudaMalloc(&dp_buf, dp_bytes(P)));
+        CK(cudaMemset(dp_buf, 0, dp_bytes(P)));
         CK(cudaDeviceSynchronize());
     }
     CK(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(handle_out), dp_buf));
@@ -639,7 +640,7 @@ int Engine::dp_connect(int rank, int world, const void* handles) {
     if (knobs.dp_stamps && !dp_stamps) { CK(cudaMalloc(&dp_stamps, (size_t)dp_nblk * kDpStamps * sizeof(long long))); CK(cudaMemset(dp_stamps, 0, (size_t)dp_nblk * kDpStamps * sizeof(long long))); }
     // tags restart at 1: no slot may still carry a tag of an earlier connection (the peers push only after the host-side barrier that
     // follows this call, engine.DeviceVAE.dp_connect)
-    CK(cudaMemset(dp_buf, 0, dp_bytes(Ppad)));
+    CK(cudaMemset(dp_buf, 0, dp_bytes(P)));
     CK(cudaDeviceSynchronize());
     dp_rank = rank; dp_world = world; dp_seq = 0; dp_count = 0;
     return 0;
@@ -662,10 +663,10 @@ int Engine::dp_update(float lr, bool have_grad, cudaStream_t s) {
     a.part_stride = Ppad;
     ++step; ++dp_seq;
     if (dp_seq == 0) ++dp_seq;                              // 0 is the tag of an empty slot
-    const size_t par = (size_t)(++dp_count & 1) * kDpMaxWorld * Ppad;    // parity alternates with every exchange of this connection (every rank takes part in each)
-    a.my_recv = reinterpret_cast<const uint2*>(dp_buf) + par;
-    for (int q = 0; q < dp_world; ++q) a.peer_recv[q] = reinterpret_cast<uint2*>(dp_peer[q]) + par;
-    a.stride = Ppad;
+    a.stride = dp_slots(P);
+    const size_t par = (size_t)(++dp_count & 1) * kDpMaxWorld * a.stride;    // parity alternates with every exchange of this connection (every rank takes part in each)
+    a.my_recv = reinterpret_cast<const uint4*>(dp_buf) + par;
+    for (int q = 0; q < dp_world; ++q) a.peer_recv[q] = reinterpret_cast<uint4*>(dp_peer[q]) + par;
     a.rank = dp_rank; a.world = dp_world; a.seq = dp_seq;
     a.theta = theta; a.m = m; a.v = v; a.n = P;
     const double t = (double)step;
