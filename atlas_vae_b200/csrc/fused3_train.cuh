@@ -483,12 +483,16 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                         // after issue_y(c + 1) they waited for the next product and the ring ran one chunk late)
                         if (!is_train) for (int b2 = 0; b2 < 2 && 2 * c + b2 < P.nX; ++b2) wrel(ob + 2 * c + b2);
                     };
+                    stamp2();
                     issue_y(0);
+                    stamp2();
                     for (int c = 0; c < P.nC; ++c) {
                         if (c + 1 < P.nC) issue_y(c + 1);
+                        stamp2();
                         if (is_train) {
                             mbar_wait(&gyfull[c], tp);
                             tc_fence_after();
+                            stamp2();
                             // g_dn += W_out[:, chunk] x g_y[chunk]   (A: K-major rows = in features; B: MN-major, K = chunk features)
                             for (int b = 0; b < 2 && 2 * c + b < P.nX; ++b) {
                                 const int nk = min(4, (D - 64 * (2 * c + b) + 15) >> 4);
@@ -501,6 +505,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                             issue_e(tdw, opnd_k(gy_a, 16384), opnd_k(tile_a((2 * n)), P.tile_rows[2 * n] * 128), 4, st.kin, false);
                             commit_e(&gyempty); ++gk;
                             dw_commit();
+                            stamp2();
                         }
                     }
                     if (is_train) commit_e(&accB[so]);
@@ -1030,7 +1035,9 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                     }
                     const float bias = valid ? __ldg(a.theta + st.seg_b[0] + f) : 0.f;
                     const uint32_t yb = yk & 1;
+                    stamp();
                     wait_acc(&yfull[yb], (yk >> 1) & 1);
+                    stamp();
                     float y[16];
                     tmem_ld16(t_lane + T_Y0 + 64 * yb + jc0, y);
                     tc_fence_before();

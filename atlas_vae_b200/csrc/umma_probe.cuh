@@ -131,10 +131,19 @@ __global__ void __launch_bounds__(128, 1) umma_issue_kernel(int M, int N, int nw
             if (mode == 0) {
                 for (int k = 0; k < nm; ++k)
                     mma_bf16_ss(d, smem_desc_sw128(smem_u32(smem) + (k & 3) * 32), smem_desc_sw128(smem_u32(smem) + 128 * 128 + (k & 3) * 32), idesc, k > 0);
-            } else {
+            } else if (mode == 1) {
                 const uint64_t da = smem_desc_sw128(smem_u32(smem)), db = smem_desc_sw128(smem_u32(smem) + 128 * 128);
 #pragma unroll 4
                 for (int k = 0; k < nm; ++k) mma_bf16_ss(d, da + (uint64_t)((k & 3) * 2), db + (uint64_t)((k & 3) * 2), idesc, k > 0);
+            } else {
+                // modes 2..4: MN-major operands (64-element blocks of [64 k x 64 mn], 8 KB apart): 2 = B, 3 = A and B, 4 = A
+                const int a_mn = mode == 3 || mode == 4, b_mn = mode == 2 || mode == 3;
+                const uint32_t id2 = idesc_bf16_major(M, N, a_mn, b_mn);
+                const uint32_t sa = smem_u32(smem), sb = smem_u32(smem) + 128 * 128;
+                const uint64_t da = a_mn ? smem_desc_sw128_mn(sa, 8192) : smem_desc_sw128(sa), db = b_mn ? smem_desc_sw128_mn(sb, 8192) : smem_desc_sw128(sb);
+                const uint64_t sta = a_mn ? (2048 >> 4) : 2, stb = b_mn ? (2048 >> 4) : 2;
+#pragma unroll 4
+                for (int k = 0; k < nm; ++k) mma_bf16_ss(d, da + (uint64_t)(k & 3) * sta, db + (uint64_t)(k & 3) * stb, id2, k > 0);
             }
             mma_commit(&bar[warp]);
             mbar_wait(&bar[warp], (uint32_t)(rep & 1));
