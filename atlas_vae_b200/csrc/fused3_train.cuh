@@ -216,7 +216,11 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
     // previous kernel in the stream (the Adam / weight-image kernel); its results (weight image, biases) and the partial-
     // gradient slices it reads are only touched below.  Both instructions are no-ops for an ordinary launch.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    asm volatile("griddepcontrol.wait;" ::: "memory");
+    // Training / get_losses: the worker warps first stage the first two X chunks of their tile (inputs only: nothing the previous
+    // kernel writes) and execute their griddepcontrol.wait after that, so ~3 k cycles of layer 0 also overlap the update kernel.
+    // (not MODE 2: its per-jet coefficients c_rec / c_kld are written by the combine kernel right before this launch)
+    const bool late_wait = !SCORE && MODE != 2 && warp < kF3Workers;
+    if (!late_wait) asm volatile("griddepcontrol.wait;" ::: "memory");
     const uint32_t tm = tmem_base_s;
     const uint32_t t_lane = tm + ((uint32_t)(32 * q) << 16);
     const int my_tiles = ((int)blockIdx.x < a.n_tiles) ? (a.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
@@ -910,6 +914,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                     for (int c = 0; c < P.nX; c += 2) {
                         stage_x(ra); ldx(c + 2, ra);
                         if (c + 1 < P.nX) { stage_x(rb); ldx(c + 3, rb); }
+                        if (c == 0 && tile_iter == 0) asm volatile("griddepcontrol.wait;" ::: "memory");   // see late_wait
                     }
                 }
                 const float bias0 = bias_of(0);
