@@ -21,12 +21,16 @@ namespace oevae {
 struct EarlyGroups {
     const unsigned int* ctr; unsigned int target; int dry;   // dry: poll, then wait for the grid all the same (A/B of the polling alone)
     long lo[2], hi[2];                                      // parameter ranges [lo, hi) of group 0 (output layer) and group 1 (chain layers)
+    int fin;                                                // ctr[2] counts the CTAs that have done ALL their work (stores, reductions, loss sums):
+                                                            // blocks outside groups 0 / 1 poll it instead of griddepcontrol.wait, which also waits
+                                                            // for the grid's exit and memory flush (~1 us)
 };
-// returns true when the block's chunk belongs to an early group and that group is complete; false: the caller waits for the grid
+// returns true when the block need not wait for the grid: its chunk belongs to an early group and that group is complete, or every
+// CTA of the training grid has reported itself finished; false: the caller waits for the grid (griddepcontrol.wait)
 __device__ __forceinline__ bool early_wait(const EarlyGroups& e, long c0, long c1) {
     if (!e.ctr) return false;
     int g = -1;
-    if (c0 >= e.lo[0] && c1 <= e.hi[0]) g = 0; else if (c0 >= e.lo[1] && c1 <= e.hi[1]) g = 1;
+    if (c0 >= e.lo[0] && c1 <= e.hi[0]) g = 0; else if (c0 >= e.lo[1] && c1 <= e.hi[1]) g = 1; else if (e.fin) g = 2;
     if (g < 0) return false;
     if (threadIdx.x == 0) {
         const long long t0 = clock64();
@@ -34,7 +38,7 @@ __device__ __forceinline__ bool early_wait(const EarlyGroups& e, long c0, long c
         for (;;) {
             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(e.ctr + g) : "memory");
             if ((int)(seen - e.target) >= 0) break;
-            __nanosleep(500);                               // ~160 resident pollers on ONE L2 sector: at 64 ns they saturated its slice and slowed the training kernel
+            __nanosleep(100);                               // ~290 resident pollers on one L2 sector: measured harmless down to 64 ns
             if (clock64() - t0 > 20000000000ll) __trap();   // ~10 s: the training kernel died; fail loudly instead of hanging
         }
     }

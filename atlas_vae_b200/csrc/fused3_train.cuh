@@ -1255,8 +1255,11 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
     if (a.dbg && blockIdx.x == 0 && tid == 0) { a.dbg[0] = n_dbg; a.dbg[906] = clock64(); }
     if (a.dbg && blockIdx.x == 0 && warp == kF3Workers && lane == 0) a.dbg[256] = n_dbg2;
     tc_fence_before();
+    if (!SCORE && a.grp_ctr && is_train) __threadfence();        // every thread's stores / reductions / atomics are performed before ...
     __syncthreads();
     if (warp == 0) tmem_dealloc(tm, 512);
+    // ... this CTA reports itself finished (EarlyGroups::fin; same unit as the drain warps' counters: 4 per CTA)
+    if (!SCORE && a.grp_ctr && is_train && tid == 32) { __threadfence(); atomicAdd(a.grp_ctr + 2, 4u); }
 }
 
 }  // namespace oevae

@@ -65,7 +65,7 @@ void Knobs::read_env() {
     fused_dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
     dbg_skip = geti("OEVAE_DBG_SKIP", 0);
     dp_stamps = geti("OEVAE_DP_STAMPS", 0) != 0;
-    adam_early = (int)geti("OEVAE_ADAM_EARLY", 3);
+    adam_early = (int)geti("OEVAE_ADAM_EARLY", 19);
 }
 
 int Engine::init(const oevae_config& c) {
@@ -575,6 +575,7 @@ EarlyGroups Engine::early_groups() const {
     if (knobs.adam_early & 1) { e.lo[0] = layers.back().w; e.hi[0] = P; }                  // dense_output: kernel + bias (the last parameters of the flat vector)
     if (knobs.adam_early & 2) { e.lo[1] = layers[1].w; e.hi[1] = layers.back().w; }        // everything between layer 0 and the output layer
     e.dry = (knobs.adam_early & 4) != 0;
+    e.fin = (knobs.adam_early & 16) != 0;
     return e;
 }
 
@@ -656,7 +657,9 @@ int Engine::dp_update(float lr, bool have_grad, cudaStream_t s) {
         a.parts = fz->parts; a.n_parts = fz->last_grid;
         // early parameter groups: measured at N = 2 they do not shorten the update's tail (it is latency: wait, reduce 2 us, push, peers' sums 1-2 us)
         // and cost 2 us of interference with the training kernel (profiles/r02_dp_stamps_n2_push.txt): on only with OEVAE_ADAM_EARLY bit 3
-        if (knobs.adam_early & 8) a.early = early_groups();
+        a.early = early_groups();
+        if (!(knobs.adam_early & 8)) { a.early.lo[0] = a.early.hi[0] = a.early.lo[1] = a.early.hi[1] = -1; }   // only the finished-CTA counter
+        if (!a.early.fin) a.early = EarlyGroups{};
     }
     else { a.parts = parts; a.n_parts = n_slots_used; }
     a.gsum_out = dp_gsum; a.stamps = dp_stamps; a.trace = SumsTrace{hl_trace_src, hl_trace_dst};
