@@ -98,6 +98,13 @@ inline bool build_fused2_plan(const Engine& e, F2Plan& P, std::vector<int>& pos,
         uint32_t hi = P.op_off[op] + (uint32_t)block * rows * 128u + h2_sw128_off(r, c);
         pos[param] = (int)hi; pos[Pn + param] = (int)(hi + part);
     };
+    // second copy of a latent column (table entries 2, 3 of the parameter: the update kernels write hi / lo there as well)
+    auto put_rep = [&](long param, int op, int block, int nblocks, int rows, int r, int c) {
+        uint32_t part = (uint32_t)rows * 128u * nblocks;
+        uint32_t hi = P.op_off[op] + (uint32_t)block * rows * 128u + h2_sw128_off(r, c);
+        pos[2 * Pn + param] = (int)hi; pos[3 * Pn + param] = (int)(hi + part);
+    };
+    P.heads_rep = (L <= 16 && P.st[n + 1].kind == 2 && P.st[n + 1].in <= 16) ? 1 : 0;
     for (int s = 0; s < P.S; ++s) {
         const F2Stage& st = P.st[s];
         for (int g = 0; g < st.nseg; ++g) {
@@ -108,8 +115,12 @@ inline bool build_fused2_plan(const Engine& e, F2Plan& P, std::vector<int>& pos,
                     switch (st.kind) {
                         case 0: put(prm, P.op_first[0] + i / 64, 0, 1, st.rows, j, i % 64); break;          // rows = out, K = in
                         case 1: put(prm, P.op_first[s], 0, 1, st.rows, i, j); break;                        // rows = in
-                        case 2: put(prm, P.op_first[s], 0, 1, st.rows, j, i); break;                        // rows = out
-                        case 3: put(prm, P.op_first[s], g, 2, st.rows, i, j); break;                        // rows = in, block per head
+                        case 2: put(prm, P.op_first[s], 0, 1, st.rows, j, i);                               // rows = out
+                                if (P.heads_rep && s == n + 1) put_rep(prm, P.op_first[s], 0, 1, st.rows, j, i + 16);
+                                break;
+                        case 3: put(prm, P.op_first[s], g, 2, st.rows, i, j);                               // rows = in, block per head
+                                if (P.heads_rep) put_rep(prm, P.op_first[s], g, 2, st.rows, i, j + 16);
+                                break;
                         default: put(prm, P.op_first[s] + j / 64, 0, 1, st.rows, i, j % 64); break;         // rows = in, block per 64 outputs
                     }
                 }

@@ -54,6 +54,8 @@ struct F2Plan {
     F2Stage st[kF2MaxStages];
     long P, Ppad;
     int n_dwbuf, dw_cols;            // fused3: dW^T accumulators in TMEM columns [320, 320 + n_dwbuf * dw_cols)
+    int heads_rep;                   // fused3: the heads' and stage n+1's weight images carry a second copy of their latent columns (16..31),
+                                     // so accumulator rows 16 + l replicate rows l and the Sampling / latent-backward epilogues use 32 lanes
     int stg0_off;                    // fused3: two [64 x out_0] fp32 staging buffers for the layer-0 gradient chunks inside the
                                      // tiles 1..2n (dead by then), or -1 when they do not fit / out_0 % 4 != 0 (direct stores)
 };

@@ -94,6 +94,15 @@ __device__ __forceinline__ void store16(unsigned char* t_hi, unsigned char* t_lo
     *reinterpret_cast<uint4*>(t_lo + o0) = make_uint4(l[0], l[1], l[2], l[3]);
     *reinterpret_cast<uint4*>(t_lo + o1) = make_uint4(l[4], l[5], l[6], l[7]);
 }
+// 8 consecutive jets (col0 % 8 == 0) of feature row `row`
+__device__ __forceinline__ void store8(unsigned char* t_hi, unsigned char* t_lo, int row, int col0, const float* v) {
+    uint32_t h[4], l[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) split2(v[2 * j], v[2 * j + 1], h[j], l[j]);
+    const uint32_t o = sw128_off(row, col0);
+    *reinterpret_cast<uint4*>(t_hi + o) = make_uint4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<uint4*>(t_lo + o) = make_uint4(l[0], l[1], l[2], l[3]);
+}
 // bit j set <=> hi part of (row, col0 + j) is > 0
 __device__ __forceinline__ uint32_t positive16(const unsigned char* t_hi, int row, int col0) {
     const uint4 q0 = *reinterpret_cast<const uint4*>(t_hi + sw128_off(row, col0));
@@ -120,6 +129,19 @@ __device__ __forceinline__ float transpose_reduce16(float* v, int lane) {
         }
     }
     return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 16);
+}
+// 8 values per lane summed over the 16 lanes of a half warp; every lane returns the total of index (lane & 7)
+__device__ __forceinline__ float transpose_reduce8(float* v, int lane) {
+#pragma unroll
+    for (int s = 4; s >= 1; s >>= 1) {
+        const bool up = (lane & s) != 0;
+#pragma unroll
+        for (int i = 0; i < s; ++i) {
+            const float send = up ? v[i] : v[i + s], keep = up ? v[i + s] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+        }
+    }
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 8);
 }
 // nan_to_num(p * log2(p / q)) of utils.py:347-350 on the SFU: approximate reciprocal + lg2.approx (abs error of the log
 // <= 2^-22 near 1, 2 ulp elsewhere); p/q < 0 -> NaN -> 0, q = 0 -> +-inf -> +-FLT_MAX or NaN -> 0 exactly as NumPy's

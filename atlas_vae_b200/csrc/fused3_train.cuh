@@ -929,7 +929,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                 const F2Stage& st = P.st[s];
                 float b_mu = 0.f, b_lv = 0.f;
                 if (s != n) b_mu = bias_of(s);
-                else if (!(SCORE && a.heads_t) && lane < L) { b_mu = __ldg(a.theta + st.seg_b[0] + lane); b_lv = __ldg(a.theta + st.seg_b[1] + lane); }
+                else if (!(SCORE && a.heads_t) && (lane & 15) < L) { b_mu = __ldg(a.theta + st.seg_b[0] + (lane & 15)); b_lv = __ldg(a.theta + st.seg_b[1] + (lane & 15)); }
                 if (SCORE && a.heads_t && s == n) {                      // the plan has L <= 16
                     // ---- heads, jets on the lanes (see the issuer): warp (q, h) owns jets 16 q .. 16 q + 15 and latent rows 4 h .. 4 h + 3;
                     // the four partial KLD sums of a jet meet in the per-jet write at the end of the tile
@@ -978,8 +978,36 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                 if (s != n) {
                     epi_act(s, b_mu, false);
                     stamp();
+                } else if (q == 0 && P.heads_rep) {
+                    // ---- heads: Sampling (models.py:9-15) + KLD (models.py:81-85); z -> rows 0..15 of the latent tile.
+                    // Accumulator rows 16 + l replicate rows l (second copy of the latent columns in the weight image), so lane l takes
+                    // jets 0..7 of the warp's column group and lane 16 + l jets 8..15: half the serial work of the 10-lane version.
+                    const int l = lane & 15, j0 = jc0 + 8 * (lane >> 4);
+                    float mu[8], lv[8], kl[8];
+                    {   // tcgen05.ld takes one warp-uniform address: every lane reads the 16 columns and keeps its half
+                        float m16[16], v16[16];
+                        tmem_ld16(t_lane + T_MU + jc0, m16);
+                        tmem_ld16(t_lane + T_LV + jc0, v16);
+                        const bool hi8 = lane >= 16;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) { mu[j] = hi8 ? m16[8 + j] : m16[j]; lv[j] = hi8 ? v16[8 + j] : v16[j]; }
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float zz = 0.f, kk = 0.f;
+                        if (l < L) {
+                            const float m = mu[j] + b_mu, v = lv[j] + b_lv;
+                            const float sg = __expf(v * 0.5f);                      // sigma; exp(v) = sigma^2 (SFU ex2, rel err ~1e-6)
+                            zz = m + clipv(sg) * s_eps[l * 64 + j0 + j];
+                            kk = 1.f + v - clipv(sg * sg) - m * m;
+                        }
+                        mu[j] = zz; kl[j] = kk;
+                    }
+                    store8(tile_hi(n), tile_lo(n), l, j0, mu);
+                    const float ks = transpose_reduce8(kl, lane);
+                    if ((lane & 8) == 0) s_kld[j0 + (lane & 7)] = -(ks / (float)L) / 2.f;
                 } else if (q == 0) {
-                    // ---- heads: Sampling (models.py:9-15) + KLD (models.py:81-85); z -> rows 0..15 of the latent tile
+                    // ---- the same with the latent index on lanes 0..L-1 only (no replicated rows in this plan)
                     float mu[16], lv[16], kl[16];
                     tmem_ld16(t_lane + T_MU + jc0, mu);
                     tmem_ld16(t_lane + T_LV + jc0, lv);
@@ -1156,12 +1184,54 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
             if (is_train) {
                 for (int s = 2 * n; s >= 1; --s) {
                     float b_mu = 0.f, b_lv = 0.f;
-                    if (s == n + 1 && lane < L) { b_mu = __ldg(a.theta + P.st[n].seg_b[0] + lane); b_lv = __ldg(a.theta + P.st[n].seg_b[1] + lane); }
+                    if (s == n + 1 && (lane & 15) < L) { b_mu = __ldg(a.theta + P.st[n].seg_b[0] + (lane & 15)); b_lv = __ldg(a.theta + P.st[n].seg_b[1] + (lane & 15)); }
                     wait_acc(&accB[s], tp);
                     if (s != n + 1) {
                         epi_grad(s);
+                    } else if (q == 0 && P.heads_rep) {
+                        // ---- latent backward: g_z -> g_mu (rows 0..15), g_logvar (rows 16..31) of the latent tile;
+                        // lanes l / 16 + l split the 16 jets of the column group (replicated accumulator rows, see the heads)
+                        const float inv_l = 1.f / (float)L;
+                        const int l = lane & 15, j0 = jc0 + 8 * (lane >> 4);
+                        float dbm = 0.f, dbl = 0.f;
+                        float gz[8], mu[8], lv[8];
+                        {   // one warp-uniform TMEM address per load: read the 16 columns, keep this lane's half
+                            float t16[16];
+                            const bool hi8 = lane >= 16;
+                            tmem_ld16(t_lane + T_CH + jc0, t16);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) gz[j] = hi8 ? t16[8 + j] : t16[j];
+                            tmem_ld16(t_lane + T_MU + jc0, t16);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) mu[j] = hi8 ? t16[8 + j] : t16[j];
+                            tmem_ld16(t_lane + T_LV + jc0, t16);
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) lv[j] = hi8 ? t16[8 + j] : t16[j];
+                        }
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            float gm = 0.f, gl = 0.f;
+                            if (l < L) {
+                                const float m = mu[j] + b_mu, v = lv[j] + b_lv;
+                                float gkw = s_wk[j0 + j];
+                                if (PAIRED) {
+                                    const int pc = (j0 + j) & 31;
+                                    const bool act = s_kld[pc] - s_kld[pc + 32] + a.margin > 0.f;
+                                    gkw = j0 < 32 ? gkw + (act ? s_wk[pc + 32] : 0.f) : (act ? -gkw : 0.f);
+                                }
+                                const float s_raw = __expf(v * 0.5f), e_raw = s_raw * s_raw;
+                                gm = gz[j] + gkw * m * inv_l;
+                                gl = gkw * (-(1.f - (clip_pass(e_raw) ? e_raw : 0.f)) * 0.5f * inv_l)
+                                   + gz[j] * s_eps[l * 64 + j0 + j] * (clip_pass(s_raw) ? s_raw * 0.5f : 0.f);
+                            }
+                            mu[j] = gm; lv[j] = gl; dbm += gm; dbl += gl;
+                        }
+                        dbm += __shfl_xor_sync(0xffffffffu, dbm, 16); dbl += __shfl_xor_sync(0xffffffffu, dbl, 16);
+                        store8(tile_hi(n), tile_lo(n), l, j0, mu);
+                        store8(tile_hi(n), tile_lo(n), 16 + l, j0, lv);
+                        if (lane < 16) { db_at(n % 3, h, lane) = dbm; db_at(n % 3, h, 16 + lane) = dbl; }
                     } else if (q == 0) {
-                        // ---- latent backward: g_z -> g_mu (rows 0..15), g_logvar (rows 16..31) of the latent tile
+                        // ---- the same with the latent index on lanes 0..L-1 only
                         const float inv_l = 1.f / (float)L;
                         float dbm = 0.f, dbl = 0.f;
                         float gz[16], mu[16], lv[16];
