@@ -655,10 +655,10 @@ int Engine::dp_update(float lr, bool have_grad, cudaStream_t s) {
     if (!have_grad) { a.parts = fz ? fz->parts : parts; a.n_parts = 0; }
     else if (fz && fz->last_fused) {
         a.parts = fz->parts; a.n_parts = fz->last_grid;
-        // early parameter groups: measured at N = 2 they do not shorten the update's tail (it is latency: wait, reduce 2 us, push, peers' sums 1-2 us)
-        // and cost 2 us of interference with the training kernel (profiles/r02_dp_stamps_n2_push.txt): on only with OEVAE_ADAM_EARLY bit 3
         a.early = early_groups();
-        if (!(knobs.adam_early & 8)) { a.early.lo[0] = a.early.hi[0] = a.early.lo[1] = a.early.hi[1] = -1; }   // only the finished-CTA counter
+        // output-layer / chain groups: measured -0.7 us per step at 4 GPUs and -1.8 us at 8 (the exchange is bound by the bytes a GPU pushes,
+        // the groups move 56 % of them under the backward pass), +2 us at 2 GPUs (interference, nothing to hide): on from 4 ranks, or bit 3
+        if (!(knobs.adam_early & 8) && dp_world < 4) { a.early.lo[0] = a.early.hi[0] = a.early.lo[1] = a.early.hi[1] = -1; }   // only the finished-CTA counter
         if (!a.early.fin) a.early = EarlyGroups{};
     }
     else { a.parts = parts; a.n_parts = n_slots_used; }
