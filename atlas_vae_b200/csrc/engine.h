@@ -34,7 +34,7 @@ struct Pass {
 //   OEVAE_FUSED_DBG=1      phase stamps of CTA 0 to stderr (synchronises)        OEVAE_DBG_SKIP=k      stamps from the k-th tile of CTA 0 on
 struct Knobs {
     bool fused = true, oe_layered = false, score_layered = false, score_static = false, fused_dbg = false, dp_stamps = false;
-    int adam_early = 19;      // bit 0: output-layer group, bit 1: chain group, bit 2: dry run (poll only), bit 3: groups also in the data-parallel
+    int adam_early = 27;      // bit 0: output-layer group, bit 1: chain group, bit 2: dry run (poll only), bit 3: groups also in the data-parallel
                               // update, bit 4: finished-CTA counter instead of griddepcontrol.wait (both updates)
     int fused_v = 3, score_heads_t = 0;
     long long dbg_skip = 0;

@@ -65,7 +65,7 @@ void Knobs::read_env() {
     fused_dbg = getenv("OEVAE_FUSED_DBG") != nullptr;
     dbg_skip = geti("OEVAE_DBG_SKIP", 0);
     dp_stamps = geti("OEVAE_DP_STAMPS", 0) != 0;
-    adam_early = (int)geti("OEVAE_ADAM_EARLY", 19);
+    adam_early = (int)geti("OEVAE_ADAM_EARLY", 27);
 }
 
 int Engine::init(const oevae_config& c) {
@@ -656,9 +656,9 @@ int Engine::dp_update(float lr, bool have_grad, cudaStream_t s) {
     else if (fz && fz->last_fused) {
         a.parts = fz->parts; a.n_parts = fz->last_grid;
         a.early = early_groups();
-        // output-layer / chain groups: measured -0.7 us per step at 4 GPUs and -1.8 us at 8 (the exchange is bound by the bytes a GPU pushes,
-        // the groups move 56 % of them under the backward pass), +2 us at 2 GPUs (interference, nothing to hide): on from 4 ranks, or bit 3
-        if (!(knobs.adam_early & 8) && dp_world < 4) { a.early.lo[0] = a.early.hi[0] = a.early.lo[1] = a.early.hi[1] = -1; }   // only the finished-CTA counter
+        // output-layer / chain groups in the data-parallel update (bit 3): measured -1.2 us per step at 2 GPUs, -0.7 us at 4, -1.8 us at 8 with the
+        // push exchange (they move 56 % of the pushed bytes under the backward pass); with the round-1 flag + pull exchange they cost 2 us
+        if (!(knobs.adam_early & 8)) { a.early.lo[0] = a.early.hi[0] = a.early.lo[1] = a.early.hi[1] = -1; }   // only the finished-CTA counter
         if (!a.early.fin) a.early = EarlyGroups{};
     }
     else { a.parts = parts; a.n_parts = n_slots_used; }
