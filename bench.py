@@ -42,7 +42,7 @@ BETA, LR = 1.0, 1e-3
 METRIC, UNIT = 'train jets/s (fwd+bwd+Adam)', 'jets/s'
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` captures (profiles/): a profile of an
 # earlier build of the same kernel, NOT measured in this run
-PROFILE_TRAFFIC = {'fused_train': {'bytes_per_launch': 8577792 + 1024, 'from_profile': 'profiles/r01_ncu_fused3_train_details.txt (B=5000)'},
+PROFILE_TRAFFIC = {'fused_train': {'bytes_per_launch': 8575744 + 11264, 'from_profile': 'profiles/r02b_ncu_fused3_adam_summary.txt (fused3_kernel<0,0>, B=5000: dram__bytes_read + dram__bytes_write)'},
                    'fused_score': {'bytes_per_jet': (64572160 + 1385728) / 40000.0, 'from_profile': 'profiles/r01_ncu_score_fused3_details.txt (40,000 jets)'}}
 
 
