@@ -16,3 +16,10 @@ for M in (128, 64):
                 rc = lib.oevae_probe_issue(M, N, nw, nm, mode, out.ctypes.data_as(C.POINTER(C.c_int64)), 0)
                 row.append('%6.1f' % (out[0] / nm) if rc == 0 else '   err')
         print('M=%3d N=%3d  cycles per MMA  KK %s   K.MN %s   MN.MN %s   MN.K %s' % (M, N, *row))
+
+print('issue rate with nw warps issuing concurrently, each to its own accumulator (M=128, N=64, K-major): cycles until all have completed / MMAs per warp')
+for nw in (1, 2, 3, 4):
+    for N in (64, 128):
+        nm = 240
+        rc = lib.oevae_probe_issue(128, N, nw, nm, 1, out.ctypes.data_as(C.POINTER(C.c_int64)), 0)
+        print('  nw=%d N=%3d: %6.1f cycles per MMA per warp -> %5.1f cycles per MMA overall' % (nw, N, out[0] / nm, out[0] / nm / nw))

@@ -110,11 +110,13 @@ OEVAE_API int oevae_loss_and_grad(oevae_t h, const float* x_bkg, const float* w_
                         float* per_jet_out, double* sums_acc, float* grad_out, void* stream);
 
 /* ---- data parallel over NVLink peer memory (replaces jet-ID's MirroredStrategy semantics, jet-ID/classifier.py:136-138,
- * for --n_gpus N; one process per GPU on one node).  oevae_dp_export allocates this rank's exchange buffer and writes
- * its 64-byte cudaIpcMemHandle_t; the caller gathers the handles of all ranks (any transport) and passes the
- * world x 64 bytes to oevae_dp_connect.  oevae_train_step_dp is oevae_train_step for one rank's slice of the global
- * batch: its update kernel sums this rank's partial gradients, exchanges the result with the peers through P2P loads /
- * stores and applies clip + Adam to the SUM over ranks (models.py:183), identically on every rank.  B == 0 is allowed there:
+ * for --n_gpus N; one process per GPU on one node).  oevae_dp_export allocates this rank's receive buffer and writes
+ * its 64-byte cudaIpcMemHandle_t; the caller gathers the handles of all ranks (any transport), passes the
+ * world x 64 bytes to oevae_dp_connect and synchronises the ranks once (a barrier) before the first step.
+ * oevae_train_step_dp is oevae_train_step for one rank's slice of the global batch: its update kernel sums this rank's
+ * partial gradients, pushes the sums into every peer's receive buffer (P2P stores, value and sequence tag in one 16-byte
+ * store) and applies clip + Adam to the SUM over ranks (models.py:183), added in rank order -- identically on every rank.
+ * Every rank must take part in every such step, in the same order.  B == 0 is allowed there:
  * a rank whose shard of a short last batch is empty still joins the exchange, with a zero gradient.
  * OEVAE_EUNSUPPORTED from oevae_dp_connect (network too large for a co-resident launch): use oevae_loss_and_grad +
  * all-reduce + oevae_apply_update. */
