@@ -25,7 +25,8 @@ def _data(FC, D, B, seed=11):
 
 
 @pytest.mark.parametrize('FC,D,B', [([80, 40, 10], 80, 256), ([80, 40, 20, 10], 400, 777), ([80, 40, 20, 10], 400, 5000),
-                                    ([33, 7, 5], 23, 1), ([33, 7, 5], 23, 63), ([100, 16], 130, 65), ([64, 32, 16], 64, 64 * 151 + 3)])
+                                    ([33, 7, 5], 23, 1), ([33, 7, 5], 23, 63), ([100, 16], 130, 65), ([64, 32, 16], 64, 64 * 151 + 3),
+                                    ([6, 8], 20, 100)])       # first decoder layer narrower than the latent space: no replicated latent rows (heads_rep = 0)
 @pytest.mark.parametrize('oe', ['KLD', 'MSE'])
 def test_fused_losses_and_gradient(FC, D, B, oe):
     X, w, eps = _data(FC, D, B)
