@@ -563,6 +563,8 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
             // run layer 0 of tile t+1 under the output epilogues of tile t.
             const int st_id = tid - (kF3Workers + 2) * 32;                  // 0 .. 32 kF3Stagers - 1
             uint32_t xk = 0;
+            int n_dbg3 = 0;                                                  // stager stamps (CTA 0, lane 0 of the first stager warp): a.dbg[832] = count, [833..899]
+            auto stamp3 = [&](int it_) { if (a.dbg && blockIdx.x == 0 && st_id == 0 && it_ >= dbg_skip && n_dbg3 < 66) a.dbg[833 + n_dbg3++] = clock64(); };
             if (st_id == 0 && a.tile_ctr) { tile_pub(0); tile_pub(1); }
             for (int it = 0; ; ++it) {
                 const int tile = tile_of(it);
@@ -615,13 +617,48 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                     }
                     if (hc & 1) { fence_async_smem(); warp_arrive(&xfull[b], lane); ++xk; }
                 };
+                // Fast versions for whole tiles whose rows are 16-byte aligned and chunks that lie inside D: the slot geometry of a thread is
+                // k-invariant (row r0 + 4 it + 32 half, column c4), so a load is one add + LDG.128 and a store one add + two STS.64.
+                // The stagers share their schedulers with the worker warps, whose output epilogues are issue bound: at ~40 instructions
+                // per float4 they needed 3.7-7 k cycles per chunk and paced the whole pass (bench/score_stamps.py).
+                const bool fast_tile = kSt == 64 && nvalid == kF2Jets && (D & 3) == 0 && (reinterpret_cast<uintptr_t>(xa) & 15) == 0;
+                const int r0 = st_id >> 4, c4f = (st_id & 15) << 2;
+                const float* rowbase = xa + (long)r0 * D + c4f;
+                const long d4 = 4L * D, d32 = 32L * D;
+                const uint32_t sw0 = (uint32_t)r0 * 128u + (uint32_t)(((((c4f >> 3) ^ r0) & 7) << 4) | ((c4f & 7) << 1));
+                const uint32_t sw1 = (uint32_t)r0 * 128u + (uint32_t)(((((c4f >> 3) ^ (r0 | 4)) & 7) << 4) | ((c4f & 7) << 1));
+                auto ldf = [&](int hc, float4 (&r)[kIt]) {
+                    const float* p = rowbase + (hc & 1) * d32 + 64 * (hc >> 1);
+#pragma unroll
+                    for (int it = 0; it < kIt; ++it) r[it] = __ldg(reinterpret_cast<const float4*>(p + it * d4));
+                };
+                auto stf = [&](int hc, const float4 (&r)[kIt]) {
+                    const uint32_t b = xk & xs_mask, rnd = xk >> xs_log;
+                    if (!(hc & 1) && rnd >= 1) mbar_wait(&xempty[b], (rnd - 1) & 1);
+                    unsigned char* hi = xslot((int)b) + (hc & 1) * 4096; unsigned char* lo = hi + 8192;
+#pragma unroll
+                    for (int it = 0; it < kIt; ++it) {
+                        uint32_t ha, la, hb, lb;
+                        split2(r[it].x, r[it].y, ha, la); split2(r[it].z, r[it].w, hb, lb);
+                        const uint32_t off = (uint32_t)it * 512u + ((it & 1) ? sw1 : sw0);
+                        *reinterpret_cast<uint2*>(hi + off) = make_uint2(ha, hb);
+                        *reinterpret_cast<uint2*>(lo + off) = make_uint2(la, lb);
+                    }
+                    if (hc & 1) { fence_async_smem(); warp_arrive(&xfull[b], lane); ++xk; }
+                };
+                auto chunk_fast = [&](int hc) { return fast_tile && 64 * (hc >> 1) + 64 <= D && (hc >> 1) < P.nX; };
+                auto ld = [&](int hc, float4 (&r)[kIt]) { if (chunk_fast(hc)) ldf(hc, r); else ldh(hc, r); };
+                auto st = [&](int hc, const float4 (&r)[kIt]) { if (chunk_fast(hc)) stf(hc, r); else sth(hc, r); };
                 float4 ra[kIt], rb[kIt];
-                ldh(0, ra);
+                stamp3(it);
+                ld(0, ra);
                 for (int hc = 0; hc < 2 * P.nX; hc += 2) {
-                    ldh(hc + 1, rb); sth(hc, ra);
-                    ldh(hc + 2, ra); sth(hc + 1, rb);
+                    ld(hc + 1, rb); st(hc, ra);
+                    ld(hc + 2, ra); st(hc + 1, rb);
+                    stamp3(it);
                 }
             }
+            if (a.dbg && blockIdx.x == 0 && st_id == 0) a.dbg[832] = n_dbg3;
         }
         // ======================================================================================= drain warps
         // dW^T accumulators (lane = output feature, column = input feature) -> rows of the Keras [in, out] kernel gradients

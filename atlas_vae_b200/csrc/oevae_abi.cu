@@ -873,6 +873,9 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
             fprintf(stderr, "\n[score dbg] issuer stamps:");
             for (int i = 0; i < (int)hbuf[256]; ++i) fprintf(stderr, " %lld", hbuf[257 + i] - hbuf[1]);
             fprintf(stderr, "\n");
+            fprintf(stderr, "[score dbg] stager stamps (tile start, then one per X chunk):");
+            for (int i = 0; i < (int)hbuf[832] && i < 66; ++i) fprintf(stderr, " %lld", hbuf[833 + i] - hbuf[1]);
+            fprintf(stderr, "\n");
         }
         return 0;
     }
