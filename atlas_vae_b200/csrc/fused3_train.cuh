@@ -1117,7 +1117,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                     if constexpr (SCORE) {
                         // loss_function (utils.py:346-375) terms of this thread's feature for its 16 jets; Q = clip_values(X_hat)
                         // Columns j >= nj accumulate values that are never written.  Pass 1 forms y + bias and four cheap range
-                        // checks over the thread's 16 elements; when they hold (|y|, |x| < 1e5, |y| and |x + y| > 1e-30 -- anything a
+                        // checks over the thread's 16 elements; when they hold (|y|, |x| < 1e6 = the clip bound, |y| and |x + y| > 1e-30 -- anything a
                         // trained model produces) clip_values is the identity, every logarithm below is finite or belongs to a
                         // term that nan_to_num zeroes, and pass 2 is ~20 instructions per element.  Otherwise the thread takes the
                         // exact path (clip_values + the quotient form with its NaN / infinity rules) for this chunk.
@@ -1129,7 +1129,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                                 ssx = fmaf(y[j], y[j], ssx); ssp = fmaf(xv[j], xv[j], ssp);
                                 mnx = fminf(mnx, fabsf(y[j])); mns = fminf(mns, fabsf(xv[j] + y[j]));
                             }
-                            const bool tame = ssx < 1e10f && ssp < 1e10f;
+                            const bool tame = ssx < 1e12f && ssp < 1e12f;     // every |y| and |x| below 1e6: clip_values is the identity
                             if (tame && (!want_kj || (mnx > 1e-30f && mns > 4e-30f))) {
                                 if (want_kj) {
 #pragma unroll
@@ -1148,6 +1148,13 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                                     }
                                 }
                             } else {
+                                if (a.dbg) {   // diagnostics: thread-chunks on the exact path, by failed condition
+                                    atomicAdd(reinterpret_cast<unsigned long long*>(&a.dbg[950]), 1ull);
+                                    if (!(ssx < 1e12f)) atomicAdd(reinterpret_cast<unsigned long long*>(&a.dbg[951]), 1ull);
+                                    if (!(ssp < 1e12f)) atomicAdd(reinterpret_cast<unsigned long long*>(&a.dbg[952]), 1ull);
+                                    if (!(mnx > 1e-30f)) atomicAdd(reinterpret_cast<unsigned long long*>(&a.dbg[953]), 1ull);
+                                    if (!(mns > 4e-30f)) atomicAdd(reinterpret_cast<unsigned long long*>(&a.dbg[954]), 1ull);
+                                }
 #pragma unroll
                                 for (int j = 0; j < 16; ++j) {
                                     const float p = xv[j], qv = clipv(y[j]), d = p - qv;

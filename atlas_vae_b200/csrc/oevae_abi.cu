@@ -873,6 +873,9 @@ int Engine::score(const float* x, long N, int n_iter, const float* eps, float* o
             fprintf(stderr, "\n[score dbg] issuer stamps:");
             for (int i = 0; i < (int)hbuf[256]; ++i) fprintf(stderr, " %lld", hbuf[257 + i] - hbuf[1]);
             fprintf(stderr, "\n");
+            fprintf(stderr, "[score dbg] exact-path thread-chunks: %lld of %lld (sum y^2 >= 1e12: %lld, sum x^2 >= 1e12: %lld, min|y| <= 1e-30: %lld, min|x+y| <= 4e-30: %lld)\n",
+                    hbuf[950], (long long)((N + 63) / 64) * 512 * f.plan2.nC, hbuf[951], hbuf[952], hbuf[953], hbuf[954]);
+            cudaMemset(sdbg + 950, 0, 5 * sizeof(long long));
             fprintf(stderr, "[score dbg] stager stamps (tile start, then one per X chunk):");
             for (int i = 0; i < (int)hbuf[832] && i < 66; ++i) fprintf(stderr, " %lld", hbuf[833 + i] - hbuf[1]);
             fprintf(stderr, "\n");

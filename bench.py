@@ -377,6 +377,34 @@ def run_ours(args):
                             'kernel_frac': (N_SCORE * SC_ALG / (1e-3 * sc_top[2] / sc_top[1]) / 1e9 / hbm_peak) if sc_top else None,
                             'traffic': PROFILE_TRAFFIC['fused_score']['bytes_per_jet'] * N_SCORE, 'traffic_from_profile': PROFILE_TRAFFIC['fused_score']['from_profile']},
                'kernels': [{'name': r_[0], 'launches_per_pass': r_[1], 'us_per_launch': 1e3 * r_[2] / r_[1], 'share': r_[2] / stot} for r_ in srows[:6]]}
+    if os.environ.get('BENCH_DEBUG_SCORE'):                       # diagnostic: the scoring kernel alone, as bench/score_sweep.py times it
+        for tag, xs in (('Xs', Xs), ('Xs.clone()', Xs.clone())):
+            for _ in range(2): vae.score(xs, 1, None, metrics=('Latent', 'MAE', 'KLD', 'JSD'))
+            torch.cuda.synchronize(); e0.record()
+            for _ in range(4): vae.score(xs, 1, None, metrics=('Latent', 'MAE', 'KLD', 'JSD'))
+            e1.record(); torch.cuda.synchronize()
+            print('[bench debug] vae.score(%s) alone: %.3f ms per pass' % (tag, e0.elapsed_time(e1) / 4), file=sys.stderr)
+        v2 = DeviceVAE(FC, D, 'KLD', args.precision, 'fixed', 0, local, BATCH); v2.set_params(vae.get_params())
+        for _ in range(2): v2.score(Xs, 1, None, metrics=('Latent', 'MAE', 'KLD', 'JSD'))
+        torch.cuda.synchronize(); e0.record()
+        for _ in range(4): v2.score(Xs, 1, None, metrics=('Latent', 'MAE', 'KLD', 'JSD'))
+        e1.record(); torch.cuda.synchronize()
+        print('[bench debug] fresh handle, same weights: %.3f ms per pass' % (e0.elapsed_time(e1) / 4), file=sys.stderr)
+        from atlas_vae_b200.models import init_params as _ip
+        v2.set_params(_ip(FC, D, 0))
+        for tag, xs in (('init weights, Xs', Xs), ('init weights, randn', torch.randn_like(Xs) * 0.3)):
+            for _ in range(2): v2.score(xs, 1, None, metrics=('Latent', 'MAE', 'KLD', 'JSD'))
+            torch.cuda.synchronize(); e0.record()
+            for _ in range(4): v2.score(xs, 1, None, metrics=('Latent', 'MAE', 'KLD', 'JSD'))
+            e1.record(); torch.cuda.synchronize()
+            print('[bench debug] %s: %.3f ms per pass' % (tag, e0.elapsed_time(e1) / 4), file=sys.stderr)
+        v2.set_params(vae.get_params())
+        xs = torch.randn_like(Xs) * 0.3
+        for _ in range(2): v2.score(xs, 1, None, metrics=('Latent', 'MAE', 'KLD', 'JSD'))
+        torch.cuda.synchronize(); e0.record()
+        for _ in range(4): v2.score(xs, 1, None, metrics=('Latent', 'MAE', 'KLD', 'JSD'))
+        e1.record(); torch.cuda.synchronize()
+        print('[bench debug] trained weights, randn: %.3f ms per pass' % (e0.elapsed_time(e1) / 4), file=sys.stderr)
     clk = clocks.stop() if clocks else None
 
     # ---- small kernels, each with its own roofline (device-timed on this rank's data)

@@ -10,6 +10,7 @@ FC, D = [80, 40, 20, 10], 400
 dev = torch.device('cuda', 0)
 v = DeviceVAE(FC, D, 'KLD', 'bf16x3', 'fixed', 0, 0, 5000); v.set_params(init_params(FC, D, 0))
 g = torch.Generator(device=dev); g.manual_seed(0)
+_pre = [torch.empty(int(float(os.environ['SWEEP_PREALLOC']) * (1 << 28)), device=dev) for _ in range(1)] if os.environ.get('SWEEP_PREALLOC') else None   # GiB of other live allocations
 NMAX = 5_000_000
 if os.environ.get('SWEEP_DATA', 'randn') == 'jets':        # bench.py's scoring sample: synthetic QCD + top jets, MaxAbs-scaled float16 rows
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
