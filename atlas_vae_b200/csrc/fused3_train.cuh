@@ -617,7 +617,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                     }
                     if (hc & 1) { fence_async_smem(); warp_arrive(&xfull[b], lane); ++xk; }
                 };
-                // Fast versions for whole tiles whose rows are 16-byte aligned and chunks that lie inside D: the slot geometry of a thread is
+                // Fast versions for whole tiles whose rows are 16-byte aligned (D % 4 == 0): the slot geometry of a thread is
                 // k-invariant (row r0 + 4 it + 32 half, column c4), so a load is one add + LDG.128 and a store one add + two STS.64.
                 // The stagers share their schedulers with the worker warps, whose output epilogues are issue bound: at ~40 instructions
                 // per float4 they needed 3.7-7 k cycles per chunk and paced the whole pass (bench/score_stamps.py).
@@ -629,8 +629,9 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                 const uint32_t sw1 = (uint32_t)r0 * 128u + (uint32_t)(((((c4f >> 3) ^ (r0 | 4)) & 7) << 4) | ((c4f & 7) << 1));
                 auto ldf = [&](int hc, float4 (&r)[kIt]) {
                     const float* p = rowbase + (hc & 1) * d32 + 64 * (hc >> 1);
+                    const bool on = 64 * (hc >> 1) + c4f < D;                 // last chunk: columns beyond D are zero (D % 4 == 0 here)
 #pragma unroll
-                    for (int it = 0; it < kIt; ++it) r[it] = __ldg(reinterpret_cast<const float4*>(p + it * d4));
+                    for (int it = 0; it < kIt; ++it) r[it] = on ? __ldg(reinterpret_cast<const float4*>(p + it * d4)) : make_float4(0.f, 0.f, 0.f, 0.f);
                 };
                 auto stf = [&](int hc, const float4 (&r)[kIt]) {
                     const uint32_t b = xk & xs_mask, rnd = xk >> xs_log;
@@ -646,7 +647,7 @@ __global__ void __launch_bounds__(SCORE ? kF3ScoreThreads : kF3Threads, 1) fused
                     }
                     if (hc & 1) { fence_async_smem(); warp_arrive(&xfull[b], lane); ++xk; }
                 };
-                auto chunk_fast = [&](int hc) { return fast_tile && 64 * (hc >> 1) + 64 <= D && (hc >> 1) < P.nX; };
+                auto chunk_fast = [&](int hc) { return fast_tile && (hc >> 1) < P.nX; };
                 auto ld = [&](int hc, float4 (&r)[kIt]) { if (chunk_fast(hc)) ldf(hc, r); else ldh(hc, r); };
                 auto st = [&](int hc, const float4 (&r)[kIt]) { if (chunk_fast(hc)) stf(hc, r); else sth(hc, r); };
                 float4 ra[kIt], rb[kIt];
