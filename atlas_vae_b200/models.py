@@ -449,6 +449,26 @@ def train_model(vae, train_sample, valid_sample, OE_type='KLD', n_epochs=1, batc
     beta, lamb, margin = float(beta), float(lamb), float(margin)
     loads = {}                                                # generator OFF: the load (and its resident copy) lives across epochs
     vcache = {}
+    vready = {}                                               # validation load uploaded while the last training steps of the epoch still run
+
+    def upload_valid(vidx):
+        nonlocal h2d
+        bkg, ood = valid_sample[vidx]
+        arrays = [_pick_X(bkg), bkg['weights']] + ([_pick_X(ood), ood['weights']] if use_ood else [None, None])
+        stager = _BatchStager(arrays, int(1e6), dev, shard, center, scale)
+        chunks = []
+        try:
+            for batch_idx, ts in stager:
+                lo, hi, glo = stager.bounds(batch_idx)
+                chunks.append((lo - glo, ts))
+            nv = stager.n
+        finally:
+            h2d += stager.h2d_bytes
+            stager.close()
+        chunks = (nv, chunks)
+        free, _ = torch.cuda.mem_get_info(dev.device)
+        if valid_len == 1 and n_epochs > 1 and free > (8 << 30): vcache[vidx] = chunks
+        return chunks
     try:
         for epoch in range(n_epochs):
             sum_batches = 0; n_seen = 0; start_time = time.time()
@@ -494,6 +514,10 @@ def train_model(vae, train_sample, valid_sample, OE_type='KLD', n_epochs=1, batc
                             b += cnt; sum_batches += cnt; n_steps += cnt
                             n_seen += gmul * (min(b * ld.batch_size, ld.n) - (b - cnt) * ld.batch_size)
                             last = b == ld.n_batches
+                            if last and last_load and valid_len == 1 and 0 not in vcache:
+                                # the epoch's steps are all enqueued: upload the validation load now, under them, instead of after the
+                                # read of the running means below (a stream synchronisation)
+                                vready[0] = upload_valid(0)
                             if sum_batches % group == 0 or last:                     # models.py:191-200
                                 report(last, last_load, trace[cnt - 1])
                     finally:
@@ -526,23 +550,8 @@ def train_model(vae, train_sample, valid_sample, OE_type='KLD', n_epochs=1, batc
                     stager.close()
             n_valid = 0
             for vidx, valid_data in enumerate(valid_sample):                         # models.py:201-211
-                chunks = vcache.get(vidx)
-                if chunks is None:
-                    bkg, ood = valid_data
-                    arrays = [_pick_X(bkg), bkg['weights']] + ([_pick_X(ood), ood['weights']] if use_ood else [None, None])
-                    stager = _BatchStager(arrays, int(1e6), dev, shard, center, scale)
-                    chunks = []
-                    try:
-                        for batch_idx, ts in stager:
-                            lo, hi, glo = stager.bounds(batch_idx)
-                            chunks.append((lo - glo, ts))
-                        nv = stager.n
-                    finally:
-                        h2d += stager.h2d_bytes
-                        stager.close()
-                    chunks = (nv, chunks)
-                    free, _ = torch.cuda.mem_get_info(dev.device)
-                    if valid_len == 1 and n_epochs > 1 and free > (8 << 30): vcache[vidx] = chunks
+                chunks = vcache.get(vidx) or vready.pop(vidx, None)
+                if chunks is None: chunks = upload_valid(vidx)
                 nv, parts = chunks
                 for off, (x, w, xo, wo) in parts:
                     if x.shape[0] == 0: continue
